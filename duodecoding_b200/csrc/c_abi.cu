@@ -1,0 +1,325 @@
+// C ABI of the verification hot path (see include/duodec.h).  Host side only
+// validates arguments, picks the team size and launches; no allocation, no
+// synchronisation.
+#include <atomic>
+#include <mutex>
+#include <utility>
+#include <vector>
+
+#include "../../include/duodec.h"
+#include "prob_kernels.cuh"
+#include "row_kernels.cuh"
+#include "verify_kernels.cuh"
+
+using namespace duodec;
+
+namespace {
+
+constexpr size_t kMaxDynSmem = 232448;  // 227 KB opt-in limit per block on sm_100
+std::atomic<int> g_team_override{0};
+
+size_t team_smem_bytes(int V, int rows_resident, int C) {
+  const int per = C == 1 ? V : ((((V + C - 1) / C) + 7) & ~7);
+  const size_t slice_floats = size_t((per + 7) & ~7) + 8;
+  return size_t(rows_resident) * slice_floats * 4 + kHistBytes + sizeof(RowScratch) + 128;
+}
+
+int pick_team(int V, int rows_resident) {
+  const int forced = g_team_override.load();
+  if (forced == 1 || forced == 2 || forced == 4 || forced == 8) {
+    if (team_smem_bytes(V, rows_resident, forced) <= kMaxDynSmem) return forced;
+  }
+  // smallest team that leaves room for two blocks per SM, else smallest that fits
+  for (int C = 1; C <= kMaxTeam; C <<= 1)
+    if (team_smem_bytes(V, rows_resident, C) <= kMaxDynSmem / 2) return C;
+  for (int C = 1; C <= kMaxTeam; C <<= 1)
+    if (team_smem_bytes(V, rows_resident, C) <= kMaxDynSmem) return C;
+  return 0;
+}
+
+// cudaFuncSetAttribute is per (kernel, device): remember the pairs already set up.
+cudaError_t ensure_smem(const void* kernel) {
+  static std::mutex mu;
+  static std::vector<std::pair<const void*, int>> done;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  std::lock_guard<std::mutex> lk(mu);
+  for (const auto& d : done)
+    if (d.first == kernel && d.second == dev) return cudaSuccess;
+  e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kMaxDynSmem));
+  if (e != cudaSuccess) return e;
+  done.emplace_back(kernel, dev);
+  return cudaSuccess;
+}
+
+template <class K, class P>
+cudaError_t launch_team(K kernel, const P& params, int teams, int C, size_t smem, cudaStream_t st) {
+  cudaError_t e = ensure_smem(reinterpret_cast<const void*>(kernel));
+  if (e != cudaSuccess) return e;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(unsigned(teams) * unsigned(C), 1, 1);
+  cfg.blockDim = dim3(kThreads, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = unsigned(C);
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = C > 1 ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, params);
+}
+
+#define DISPATCH_TEAM(C, ...)                         \
+  switch (C) {                                        \
+    case 1: { constexpr int kC = 1; __VA_ARGS__; } break; \
+    case 2: { constexpr int kC = 2; __VA_ARGS__; } break; \
+    case 4: { constexpr int kC = 4; __VA_ARGS__; } break; \
+    case 8: { constexpr int kC = 8; __VA_ARGS__; } break; \
+    default: return DUODEC_ETOOBIG;                   \
+  }
+
+}  // namespace
+
+extern "C" {
+
+const char* duodec_version(void) { return "duodec-b200 0.1.0 sm_100a"; }
+
+int duodec_team_size(int V, int rows_resident) {
+  if (V <= 0 || rows_resident < 1 || rows_resident > 2) return 0;
+  return pick_team(V, rows_resident);
+}
+
+void duodec_set_team_size(int team) { g_team_override.store(team); }
+
+int duodec_norm_logits(const void* logits, int in_dtype, int64_t in_row_stride, void* out, int out_dtype,
+                       int64_t out_row_stride, int rows, int V, float temperature, int top_k, float top_p,
+                       void* stream) {
+  if (rows < 0 || V <= 0) return DUODEC_EINVAL;
+  if (rows == 0) return 0;
+  if (!logits || !out) return DUODEC_EINVAL;
+  if ((in_dtype != DUODEC_F32 && in_dtype != DUODEC_BF16) || (out_dtype != DUODEC_F32 && out_dtype != DUODEC_BF16))
+    return DUODEC_EINVAL;
+  if (!(temperature >= 0.0f)) return DUODEC_EINVAL;
+  const int C = pick_team(V, 1);
+  if (C == 0) return DUODEC_ETOOBIG;
+  NormParams P;
+  P.logits = logits;
+  P.in_stride = in_row_stride;
+  P.out = out;
+  P.out_stride = out_row_stride;
+  P.rows = rows;
+  P.V = V;
+  P.temperature = temperature;
+  P.top_p = top_p;
+  P.top_k = top_k;
+  P.per = C == 1 ? V : ((((V + C - 1) / C) + 7) & ~7);
+  P.slice_floats = ((P.per + 7) & ~7) + 8;
+  const size_t smem = team_smem_bytes(V, 1, C);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  cudaError_t e = cudaSuccess;
+  DISPATCH_TEAM(C, {
+    if (in_dtype == DUODEC_F32 && out_dtype == DUODEC_F32)
+      e = launch_team(norm_logits_kernel<float, float, kC>, P, rows, kC, smem, st);
+    else if (in_dtype == DUODEC_BF16 && out_dtype == DUODEC_BF16)
+      e = launch_team(norm_logits_kernel<__nv_bfloat16, __nv_bfloat16, kC>, P, rows, kC, smem, st);
+    else if (in_dtype == DUODEC_BF16 && out_dtype == DUODEC_F32)
+      e = launch_team(norm_logits_kernel<__nv_bfloat16, float, kC>, P, rows, kC, smem, st);
+    else
+      e = launch_team(norm_logits_kernel<float, __nv_bfloat16, kC>, P, rows, kC, smem, st);
+  })
+  return int(e);
+}
+
+size_t duodec_verify_workspace_bytes(int B, int gamma) {
+  if (B <= 0 || gamma < 0) return 0;
+  // [B] int counters (padded to 8 bytes each) + [B, gamma+1] int64 position tokens
+  return size_t(B) * 8 + size_t(B) * size_t(gamma + 1) * 8;
+}
+
+int duodec_verify_fused(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss, int64_t t_sb,
+                        int64_t t_ss, int B, int gamma, int Vd, int Vt, const int64_t* tokens, int64_t tok_sb,
+                        const float* r, int64_t r_sb, const float* noise, int64_t noise_sb, float temperature,
+                        int top_k, float top_p, float draft_temperature, int draft_top_k, float draft_top_p,
+                        uint8_t* accept_mask, float* sel_target_p, float* sel_draft_p, int64_t* accepted_len,
+                        int64_t* token, uint8_t* all_accepted, void* workspace, size_t workspace_bytes,
+                        void* stream) {
+  if (B < 0 || gamma < 0 || Vd <= 0 || Vt <= 0) return DUODEC_EINVAL;
+  if (B == 0) return 0;
+  if (!target || !noise || !accepted_len || !token || !all_accepted || !workspace) return DUODEC_EINVAL;
+  if (gamma > 0 && (!draft || !tokens || !r || !accept_mask || !sel_target_p || !sel_draft_p)) return DUODEC_EINVAL;
+  if (dtype != DUODEC_F32 && dtype != DUODEC_BF16) return DUODEC_EINVAL;
+  if (!(temperature >= 0.0f) || !(draft_temperature >= 0.0f)) return DUODEC_EINVAL;
+  if ((temperature == 0.0f) != (draft_temperature == 0.0f)) return DUODEC_EINVAL;  // greedy on both or neither
+  if (workspace_bytes < duodec_verify_workspace_bytes(B, gamma)) return DUODEC_EWORKSPACE;
+  const int Vmax = Vd > Vt ? Vd : Vt;
+  const int C = pick_team(Vmax, 2);
+  if (C == 0) return DUODEC_ETOOBIG;
+  VerifyParams P;
+  P.draft = draft;
+  P.target = target;
+  P.d_sb = d_sb;
+  P.d_ss = d_ss;
+  P.t_sb = t_sb;
+  P.t_ss = t_ss;
+  P.B = B;
+  P.gamma = gamma;
+  P.Vd = Vd;
+  P.Vt = Vt;
+  P.tokens = reinterpret_cast<const long long*>(tokens);
+  P.tok_sb = tok_sb;
+  P.r = r;
+  P.r_sb = r_sb;
+  P.noise = noise;
+  P.noise_sb = noise_sb;
+  P.t_temp = temperature;
+  P.t_top_p = top_p;
+  P.t_top_k = top_k;
+  P.d_temp = draft_temperature;
+  P.d_top_p = draft_top_p;
+  P.d_top_k = draft_top_k;
+  P.accept_mask = accept_mask;
+  P.sel_p = sel_target_p;
+  P.sel_q = sel_draft_p;
+  P.accepted_len = reinterpret_cast<long long*>(accepted_len);
+  P.token = reinterpret_cast<long long*>(token);
+  P.all_accepted = all_accepted;
+  P.counters = reinterpret_cast<int*>(workspace);
+  P.pair_token = reinterpret_cast<long long*>(reinterpret_cast<char*>(workspace) + size_t(B) * 8);
+  P.per = C == 1 ? Vmax : ((((Vmax + C - 1) / C) + 7) & ~7);
+  P.slice_floats = ((P.per + 7) & ~7) + 8;
+  const size_t smem = team_smem_bytes(Vmax, 2, C);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int teams = B * (gamma + 1);
+  cudaError_t e = cudaSuccess;
+  DISPATCH_TEAM(C, {
+    if (dtype == DUODEC_F32) e = launch_team(verify_pair_kernel<float, kC>, P, teams, kC, smem, st);
+    else e = launch_team(verify_pair_kernel<__nv_bfloat16, kC>, P, teams, kC, smem, st);
+  })
+  return int(e);
+}
+
+int duodec_accept_probs(const void* draft_probs, int64_t d_sb, int64_t d_ss, const void* target_probs,
+                        int64_t t_sb, int64_t t_ss, int dtype, const int64_t* tokens, int64_t tok_sb,
+                        const float* r, int64_t r_sb, int B, int gamma, int V, uint8_t* accept_mask,
+                        void* sel_draft_p, void* sel_target_p, int64_t* accepted_len, void* stream) {
+  if (B < 0 || gamma < 0 || V <= 0) return DUODEC_EINVAL;
+  if (B == 0) return 0;
+  if (!accepted_len) return DUODEC_EINVAL;
+  if (gamma > 0 && (!draft_probs || !target_probs || !tokens || !r || !accept_mask || !sel_draft_p || !sel_target_p))
+    return DUODEC_EINVAL;
+  if (dtype != DUODEC_F32 && dtype != DUODEC_BF16) return DUODEC_EINVAL;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int threads = gamma <= 32 ? 32 : (gamma <= 256 ? 256 : 1024);
+  if (dtype == DUODEC_F32)
+    accept_probs_kernel<float><<<B, threads, 0, st>>>(
+        static_cast<const float*>(draft_probs), d_sb, d_ss, static_cast<const float*>(target_probs), t_sb, t_ss,
+        reinterpret_cast<const long long*>(tokens), tok_sb, r, r_sb, gamma, V, accept_mask,
+        static_cast<float*>(sel_draft_p), static_cast<float*>(sel_target_p),
+        reinterpret_cast<long long*>(accepted_len));
+  else
+    accept_probs_kernel<__nv_bfloat16><<<B, threads, 0, st>>>(
+        static_cast<const __nv_bfloat16*>(draft_probs), d_sb, d_ss, static_cast<const __nv_bfloat16*>(target_probs),
+        t_sb, t_ss, reinterpret_cast<const long long*>(tokens), tok_sb, r, r_sb, gamma, V, accept_mask,
+        static_cast<__nv_bfloat16*>(sel_draft_p), static_cast<__nv_bfloat16*>(sel_target_p),
+        reinterpret_cast<long long*>(accepted_len));
+  return int(cudaGetLastError());
+}
+
+int duodec_sample_rows(const void* probs, int dtype, int64_t row_stride, const float* noise, int64_t noise_stride,
+                       int rows, int V, int64_t* out, void* stream) {
+  if (rows < 0 || V <= 0) return DUODEC_EINVAL;
+  if (rows == 0) return 0;
+  if (!probs || !noise || !out) return DUODEC_EINVAL;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dtype == DUODEC_F32)
+    sample_rows_kernel<float><<<rows, kThreads, 0, st>>>(static_cast<const float*>(probs), row_stride, noise,
+                                                         noise_stride, V, reinterpret_cast<long long*>(out));
+  else if (dtype == DUODEC_BF16)
+    sample_rows_kernel<__nv_bfloat16><<<rows, kThreads, 0, st>>>(static_cast<const __nv_bfloat16*>(probs),
+                                                                 row_stride, noise, noise_stride, V,
+                                                                 reinterpret_cast<long long*>(out));
+  else
+    return DUODEC_EINVAL;
+  return int(cudaGetLastError());
+}
+
+int duodec_residual_sample(const void* target_probs, int64_t t_stride, const void* draft_probs, int64_t d_stride,
+                           int dtype, const float* noise, int64_t noise_stride, int rows, int V, int64_t* out,
+                           void* stream) {
+  if (rows < 0 || V <= 0) return DUODEC_EINVAL;
+  if (rows == 0) return 0;
+  if (!target_probs || !draft_probs || !noise || !out) return DUODEC_EINVAL;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dtype == DUODEC_F32)
+    residual_sample_kernel<float><<<rows, kThreads, 0, st>>>(static_cast<const float*>(target_probs), t_stride,
+                                                             static_cast<const float*>(draft_probs), d_stride, noise,
+                                                             noise_stride, V, reinterpret_cast<long long*>(out));
+  else if (dtype == DUODEC_BF16)
+    residual_sample_kernel<__nv_bfloat16><<<rows, kThreads, 0, st>>>(
+        static_cast<const __nv_bfloat16*>(target_probs), t_stride, static_cast<const __nv_bfloat16*>(draft_probs),
+        d_stride, noise, noise_stride, V, reinterpret_cast<long long*>(out));
+  else
+    return DUODEC_EINVAL;
+  return int(cudaGetLastError());
+}
+
+int duodec_max_fn(const void* x, int dtype, int64_t row_stride, int rows, int V, float* out, int64_t out_stride,
+                  void* stream) {
+  if (rows < 0 || V <= 0) return DUODEC_EINVAL;
+  if (rows == 0) return 0;
+  if (!x || !out) return DUODEC_EINVAL;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dtype == DUODEC_F32)
+    max_fn_kernel<float><<<rows, kThreads, 0, st>>>(static_cast<const float*>(x), row_stride, V, out, out_stride);
+  else if (dtype == DUODEC_BF16)
+    max_fn_kernel<__nv_bfloat16><<<rows, kThreads, 0, st>>>(static_cast<const __nv_bfloat16*>(x), row_stride, V, out,
+                                                           out_stride);
+  else
+    return DUODEC_EINVAL;
+  return int(cudaGetLastError());
+}
+
+int duodec_topk_rebuild(const void* probs, int dtype, int64_t in_stride, void* out, int64_t out_stride, int rows,
+                        int V, int k, int mode, void* stream) {
+  if (rows < 0 || V <= 0 || mode < 0 || mode > 3) return DUODEC_EINVAL;
+  if (rows == 0) return 0;
+  if (!probs || !out) return DUODEC_EINVAL;
+  if (mode != 3 && (k <= 0 || k >= V)) return DUODEC_EINVAL;
+  if (dtype != DUODEC_F32 && dtype != DUODEC_BF16) return DUODEC_EINVAL;
+  const int C = pick_team(V, 1);
+  if (C == 0) return DUODEC_ETOOBIG;
+  TopkParams P;
+  P.probs = probs;
+  P.in_stride = in_stride;
+  P.out = out;
+  P.out_stride = out_stride;
+  P.rows = rows;
+  P.V = V;
+  P.k = k;
+  P.mode = mode;
+  P.per = C == 1 ? V : ((((V + C - 1) / C) + 7) & ~7);
+  P.slice_floats = ((P.per + 7) & ~7) + 8;
+  const size_t smem = team_smem_bytes(V, 1, C);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  cudaError_t e = cudaSuccess;
+  DISPATCH_TEAM(C, {
+    if (dtype == DUODEC_F32) e = launch_team(topk_rebuild_kernel<float, kC>, P, rows, kC, smem, st);
+    else e = launch_team(topk_rebuild_kernel<__nv_bfloat16, kC>, P, rows, kC, smem, st);
+  })
+  return int(e);
+}
+
+int duodec_kv_truncate(int32_t* seq_len, const int64_t* end_pos_vec, int64_t end_pos, int B, void* stream) {
+  if (B < 0) return DUODEC_EINVAL;
+  if (B == 0) return 0;
+  if (!seq_len) return DUODEC_EINVAL;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  kv_truncate_kernel<<<(B + 255) / 256, 256, 0, st>>>(seq_len, reinterpret_cast<const long long*>(end_pos_vec), B,
+                                                      (long long)end_pos);
+  return int(cudaGetLastError());
+}
+
+}  // extern "C"

@@ -1,0 +1,314 @@
+"""Tensor-level entry points: torch CUDA tensors in, C-ABI calls out.
+
+torch is plumbing here (device memory, the current stream); all arithmetic
+happens in the sm_100a kernels of ``libduodec.so``.  Every function raises on
+CPU tensors - there is no fallback path.
+"""
+
+from __future__ import annotations
+
+from typing import Dict, Optional, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import BF16, F32, check, lib
+
+_DTYPES = {torch.float32: F32, torch.bfloat16: BF16}
+_WORKSPACES: Dict[Tuple[int, int, int], torch.Tensor] = {}
+
+
+def _need_cuda(*tensors: torch.Tensor) -> None:
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError(
+                "duodecoding_b200 ops run on CUDA tensors only (no CPU fallback); got a tensor on " + str(t.device)
+            )
+
+
+def _code(t: torch.Tensor) -> int:
+    try:
+        return _DTYPES[t.dtype]
+    except KeyError:
+        raise TypeError(f"unsupported dtype {t.dtype}; float32 and bfloat16 are implemented") from None
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _rows(t: torch.Tensor) -> torch.Tensor:
+    """View [..., V] as [rows, V] with unit vocab stride (copy only when needed)."""
+    V = t.shape[-1]
+    t2 = t.reshape(-1, V)
+    if t2.numel() and t2.stride(-1) != 1:
+        t2 = t2.contiguous()
+    return t2
+
+
+def _lastdim_contig(t: torch.Tensor) -> torch.Tensor:
+    return t if (t.numel() == 0 or t.stride(-1) == 1) else t.contiguous()
+
+
+def set_team_size(team: int) -> None:
+    """Tuning hook: force the thread-block-cluster size (0 = automatic)."""
+    lib.duodec_set_team_size(int(team))
+
+
+def team_size(V: int, rows_resident: int = 1) -> int:
+    return int(lib.duodec_team_size(int(V), int(rows_resident)))
+
+
+# --------------------------------------------------------------------------
+def norm_logits(
+    logits: torch.Tensor,
+    temperature: float,
+    top_k: int = 0,
+    top_p: float = 0.0,
+    out: Optional[torch.Tensor] = None,
+    out_dtype: Optional[torch.dtype] = None,
+) -> torch.Tensor:
+    """softmax(top_k_top_p_filter(logits / T)), or the argmax one-hot at T == 0."""
+    _need_cuda(logits, out)
+    x = _rows(logits)
+    rows, V = x.shape
+    if out is None:
+        if out_dtype is None:
+            out_dtype = torch.float32 if temperature == 0 else logits.dtype
+        out = torch.empty(logits.shape, dtype=out_dtype, device=logits.device)
+    o = out.reshape(-1, V) if out.dim() != 2 else out
+    if o.numel() and o.stride(-1) != 1:
+        raise ValueError("out must have unit stride along the vocabulary")
+    if rows:
+        with torch.cuda.device(logits.device):
+            check(
+                lib.duodec_norm_logits(
+                    x.data_ptr(), _code(x), x.stride(0), o.data_ptr(), _code(o), o.stride(0), rows, V,
+                    float(temperature), int(top_k), float(top_p), _stream(),
+                ),
+                "duodec_norm_logits",
+            )
+    return out
+
+
+def _workspace(device: torch.device, B: int, gamma: int) -> torch.Tensor:
+    key = (device.index if device.index is not None else torch.cuda.current_device(), B, gamma)
+    ws = _WORKSPACES.get(key)
+    if ws is None:
+        nbytes = int(lib.duodec_verify_workspace_bytes(B, gamma))
+        ws = torch.zeros(nbytes, dtype=torch.uint8, device=device)
+        _WORKSPACES[key] = ws
+    return ws
+
+
+def verify_fused(
+    draft_logits: torch.Tensor,  # [B, >=gamma, Vd]
+    target_logits: torch.Tensor,  # [B, >=gamma+1, Vt]
+    tokens: torch.Tensor,  # [B, gamma] int64
+    r: torch.Tensor,  # [B, gamma] float32
+    noise: torch.Tensor,  # [B, >=max(Vd,Vt)] float32 Exp(1)
+    temperature: float = 1.0,
+    top_k: int = 0,
+    top_p: float = 0.0,
+    draft_temperature: Optional[float] = None,
+    draft_top_k: Optional[int] = None,
+    draft_top_p: Optional[float] = None,
+    out: Optional[Dict[str, torch.Tensor]] = None,
+) -> Dict[str, torch.Tensor]:
+    """One fused verification step on logits for every sequence of the batch."""
+    _need_cuda(draft_logits, target_logits, tokens, r, noise)
+    B, gamma = tokens.shape
+    dev = target_logits.device
+    if target_logits.dtype != draft_logits.dtype:
+        raise TypeError("draft and target logits must share a dtype")
+    if target_logits.shape[1] < gamma + 1 or (gamma > 0 and draft_logits.shape[1] < gamma):
+        raise ValueError("need gamma draft rows and gamma+1 target rows")
+    dl = _lastdim_contig(draft_logits)
+    tl = _lastdim_contig(target_logits)
+    tokens = _lastdim_contig(tokens.to(torch.int64))
+    r = _lastdim_contig(r.to(torch.float32))
+    noise = _lastdim_contig(noise.to(torch.float32))
+    Vd, Vt = dl.shape[-1], tl.shape[-1]
+    if noise.shape[-1] < max(Vd, Vt) or noise.shape[0] != B:
+        raise ValueError("noise must be [B, >= max(Vd, Vt)]")
+    dT = temperature if draft_temperature is None else draft_temperature
+    dk = top_k if draft_top_k is None else draft_top_k
+    dp = top_p if draft_top_p is None else draft_top_p
+    if out is None:
+        out = {
+            "accept_mask": torch.empty((B, gamma), dtype=torch.bool, device=dev),
+            "selected_target_p": torch.empty((B, gamma), dtype=torch.float32, device=dev),
+            "selected_draft_p": torch.empty((B, gamma), dtype=torch.float32, device=dev),
+            "accepted_len": torch.empty((B,), dtype=torch.int64, device=dev),
+            "token": torch.empty((B,), dtype=torch.int64, device=dev),
+            "all_accepted": torch.empty((B,), dtype=torch.bool, device=dev),
+        }
+    if B == 0:
+        return out
+    ws = _workspace(dev, B, gamma)
+    with torch.cuda.device(dev):
+        check(
+            lib.duodec_verify_fused(
+                dl.data_ptr(), tl.data_ptr(), _code(tl), dl.stride(0), dl.stride(1), tl.stride(0), tl.stride(1),
+                B, gamma, Vd, Vt,
+                tokens.data_ptr(), tokens.stride(0) if gamma else 0, r.data_ptr(), r.stride(0) if gamma else 0,
+                noise.data_ptr(), noise.stride(0),
+                float(temperature), int(top_k), float(top_p), float(dT), int(dk), float(dp),
+                out["accept_mask"].data_ptr(), out["selected_target_p"].data_ptr(),
+                out["selected_draft_p"].data_ptr(), out["accepted_len"].data_ptr(), out["token"].data_ptr(),
+                out["all_accepted"].data_ptr(), ws.data_ptr(), ws.numel(), _stream(),
+            ),
+            "duodec_verify_fused",
+        )
+    return out
+
+
+def accept_probs(
+    draft_probs: torch.Tensor,  # [B, gamma, V]
+    target_probs: torch.Tensor,  # [B, gamma, V]
+    tokens: torch.Tensor,  # [B, gamma]
+    r: torch.Tensor,  # [B, gamma]
+) -> Dict[str, torch.Tensor]:
+    """Gather p, q at the drafted tokens, ``r <= p/q``, leading accepted run per sequence."""
+    _need_cuda(draft_probs, target_probs, tokens, r)
+    B, gamma = tokens.shape
+    dev = draft_probs.device
+    if target_probs.device != dev:
+        target_probs = target_probs.to(dev)
+    if draft_probs.dtype != target_probs.dtype or draft_probs.dtype not in _DTYPES:
+        draft_probs, target_probs = draft_probs.float(), target_probs.float()
+    dq = _lastdim_contig(draft_probs)
+    tp = _lastdim_contig(target_probs)
+    tokens = _lastdim_contig(tokens.to(device=dev, dtype=torch.int64))
+    r = _lastdim_contig(r.to(device=dev, dtype=torch.float32))
+    V = min(dq.shape[-1], tp.shape[-1])
+    out = {
+        "accept_mask": torch.empty((B, gamma), dtype=torch.bool, device=dev),
+        "selected_draft_p": torch.empty((B, gamma), dtype=dq.dtype, device=dev),
+        "selected_target_p": torch.empty((B, gamma), dtype=dq.dtype, device=dev),
+        "accepted_len": torch.empty((B,), dtype=torch.int64, device=dev),
+    }
+    if B == 0:
+        return out
+    with torch.cuda.device(dev):
+        check(
+            lib.duodec_accept_probs(
+                dq.data_ptr(), dq.stride(0), dq.stride(1) if gamma else 0, tp.data_ptr(), tp.stride(0),
+                tp.stride(1) if gamma else 0, _code(dq), tokens.data_ptr(), tokens.stride(0) if gamma else 0,
+                r.data_ptr(), r.stride(0) if gamma else 0, B, gamma, V, out["accept_mask"].data_ptr(),
+                out["selected_draft_p"].data_ptr(), out["selected_target_p"].data_ptr(),
+                out["accepted_len"].data_ptr(), _stream(),
+            ),
+            "duodec_accept_probs",
+        )
+    return out
+
+
+def draw_noise(rows: int, V: int, device: torch.device, generator: Optional[torch.Generator] = None) -> torch.Tensor:
+    """Exp(1) draws for the race sampler - the same draw torch.multinomial makes internally."""
+    return torch.empty((rows, V), dtype=torch.float32, device=device).exponential_(1.0, generator=generator)
+
+
+def sample_rows(probs: torch.Tensor, noise: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``sample(probs)`` -> [rows, 1] int64."""
+    _need_cuda(probs, noise)
+    p = _rows(probs)
+    if p.dtype not in _DTYPES:
+        p = p.float()
+    rows, V = p.shape
+    if noise is None:
+        noise = draw_noise(rows, V, p.device)
+    nz = _rows(noise.to(torch.float32))
+    out = torch.empty((rows,), dtype=torch.int64, device=p.device)
+    if rows:
+        with torch.cuda.device(p.device):
+            check(
+                lib.duodec_sample_rows(p.data_ptr(), _code(p), p.stride(0), nz.data_ptr(), nz.stride(0), rows, V,
+                                       out.data_ptr(), _stream()),
+                "duodec_sample_rows",
+            )
+    return out.reshape(*probs.shape[:-1], 1)
+
+
+def residual_sample(target_probs: torch.Tensor, draft_probs: torch.Tensor,
+                    noise: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``sample(max_fn(target_probs - draft_probs))`` -> [rows, 1] int64."""
+    _need_cuda(target_probs, draft_probs, noise)
+    if target_probs.dtype != draft_probs.dtype or target_probs.dtype not in _DTYPES:
+        target_probs, draft_probs = target_probs.float(), draft_probs.float()
+    tp = _rows(target_probs)
+    dq = _rows(draft_probs)
+    rows, V = tp.shape
+    if dq.shape != tp.shape:
+        raise ValueError("target and draft rows must have the same shape")
+    if noise is None:
+        noise = draw_noise(rows, V, tp.device)
+    nz = _rows(noise.to(torch.float32))
+    out = torch.empty((rows,), dtype=torch.int64, device=tp.device)
+    if rows:
+        with torch.cuda.device(tp.device):
+            check(
+                lib.duodec_residual_sample(tp.data_ptr(), tp.stride(0), dq.data_ptr(), dq.stride(0), _code(tp),
+                                           nz.data_ptr(), nz.stride(0), rows, V, out.data_ptr(), _stream()),
+                "duodec_residual_sample",
+            )
+    return out.reshape(*target_probs.shape[:-1], 1)
+
+
+def max_fn(x: torch.Tensor) -> torch.Tensor:
+    """``norm(max(x, 0))`` over the last dim of a 2-D tensor, fp32 out."""
+    _need_cuda(x)
+    if x.dtype not in _DTYPES:
+        x = x.float()
+    x2 = _rows(x)
+    rows, V = x2.shape
+    out = torch.empty((rows, V), dtype=torch.float32, device=x.device)
+    if rows:
+        with torch.cuda.device(x.device):
+            check(
+                lib.duodec_max_fn(x2.data_ptr(), _code(x2), x2.stride(0), rows, V, out.data_ptr(), out.stride(0),
+                                  _stream()),
+                "duodec_max_fn",
+            )
+    return out.reshape(x.shape)
+
+
+def topk_rebuild(probs: torch.Tensor, k: int, mode: int) -> torch.Tensor:
+    """transfer_top_k compression family (modes in include/duodec.h)."""
+    _need_cuda(probs)
+    p = probs if probs.dtype in _DTYPES else probs.float()
+    p2 = _rows(p)
+    rows, V = p2.shape
+    out = torch.empty((rows, V), dtype=p2.dtype, device=p2.device)
+    if rows:
+        with torch.cuda.device(p2.device):
+            check(
+                lib.duodec_topk_rebuild(p2.data_ptr(), _code(p2), p2.stride(0), out.data_ptr(), out.stride(0), rows,
+                                        V, int(k), int(mode), _stream()),
+                "duodec_topk_rebuild",
+            )
+    return out.reshape(probs.shape).to(probs.dtype)
+
+
+def kv_truncate(seq_len: torch.Tensor, end_pos) -> torch.Tensor:
+    """In-place ``seq_len[b] = min(seq_len[b], end_pos[b])`` on an int32 length vector."""
+    _need_cuda(seq_len)
+    if seq_len.dtype != torch.int32 or not seq_len.is_contiguous():
+        raise TypeError("seq_len must be a contiguous int32 tensor")
+    B = seq_len.numel()
+    vec = None
+    scalar = 0
+    if isinstance(end_pos, torch.Tensor):
+        vec = end_pos.to(device=seq_len.device, dtype=torch.int64).contiguous()
+        if vec.numel() != B:
+            raise ValueError("end_pos tensor must have one entry per sequence")
+    else:
+        scalar = int(end_pos)
+    if B:
+        with torch.cuda.device(seq_len.device):
+            check(
+                lib.duodec_kv_truncate(seq_len.data_ptr(), vec.data_ptr() if vec is not None else None, scalar, B,
+                                       _stream()),
+                "duodec_kv_truncate",
+            )
+    return seq_len

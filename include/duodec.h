@@ -1,0 +1,131 @@
+/*
+ * duodec.h - C ABI of the B200-native speculative-decoding verification path.
+ *
+ * Drop-in boundary for the hot path of Nanji-Huaji/DuoDecoding.  The reference
+ * has no FFI of its own: the path is reached through Python module functions
+ * (src/utils.py, src/decoding_ops.py, src/communication.py, src/model_gpu.py).
+ * Each entry point below names the reference function(s) it replaces; the
+ * Python host layer in duodecoding_b200/ keeps those functions' names and
+ * signatures and calls this library through ctypes.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every pointer is a DEVICE pointer unless
+ *     the name ends in _host; nothing here allocates or synchronises;
+ *   - `stream` is a cudaStream_t passed as void*; work is enqueued on it;
+ *   - strides are in ELEMENTS; the vocabulary dimension is contiguous;
+ *   - dtype codes: DUODEC_F32 = 0, DUODEC_BF16 = 1;
+ *   - return value: 0 on success, a negative DUODEC_E* code for a rejected
+ *     argument, or a positive cudaError_t from the launch;
+ *   - re-entrant: no global state besides one-time kernel attribute setup.
+ */
+#ifndef DUODEC_H_
+#define DUODEC_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DUODEC_F32 0
+#define DUODEC_BF16 1
+
+#define DUODEC_EINVAL (-1)   /* bad shape / null pointer / unsupported dtype */
+#define DUODEC_ETOOBIG (-2)  /* row does not fit the largest team (V too large) */
+#define DUODEC_EWORKSPACE (-3)
+
+/* Library / build identification: "duodec-b200 <version> sm_100a". */
+const char* duodec_version(void);
+
+/* Team (thread-block cluster) size the library would pick for a row of V
+ * entries when `rows_resident` rows must sit in shared memory together
+ * (1: norm_logits / top-k ops, 2: fused verify).  0 if V is too large. */
+int duodec_team_size(int V, int rows_resident);
+
+/* Override the team-size heuristic (0 = automatic).  Tuning / test hook. */
+void duodec_set_team_size(int team);
+
+/* ---- logits -> probabilities --------------------------------------------
+ * Replaces utils.norm_logits + utils.top_k_top_p_filter
+ * (/root/reference/src/utils.py:650-709).
+ *   temperature == 0 : one-hot of the first argmax
+ *   else             : softmax(top_k_top_p_filter(logits / temperature))
+ * logits [rows, V] (in_dtype), out [rows, V] (out_dtype). */
+int duodec_norm_logits(const void* logits, int in_dtype, int64_t in_row_stride, void* out, int out_dtype,
+                       int64_t out_row_stride, int rows, int V, float temperature, int top_k, float top_p,
+                       void* stream);
+
+/* ---- fused verification on logits -----------------------------------------
+ * One call = norm_logits on the gamma draft rows and gamma+1 target rows
+ * (src/model_gpu.py:253), the accept test and leading-run scan
+ * (src/decoding_ops.py:127-147, applied to EVERY sequence of the batch), the
+ * residual resample at the first rejected position (src/decoding_ops.py:190-206)
+ * or the bonus sample (src/decoding_ops.py:209-220).
+ *
+ *   draft   [B, >=gamma,   Vd] logits, strides (d_sb, d_ss, 1)
+ *   target  [B, >=gamma+1, Vt] logits, strides (t_sb, t_ss, 1)
+ *   tokens  [B, gamma] int64 drafted ids (row stride tok_sb)
+ *   r       [B, gamma] float32 uniforms of the accept test (row stride r_sb)
+ *   noise   [B, >=max(Vd,Vt)] float32 Exp(1) draws (row stride noise_sb): the
+ *           sampled token of sequence b is argmax_i prob_i / noise[b,i], which
+ *           is what torch.multinomial computes internally.
+ * outputs
+ *   accept_mask [B,gamma] uint8, sel_target_p / sel_draft_p [B,gamma] float32,
+ *   accepted_len [B] int64, token [B] int64, all_accepted [B] uint8.
+ * workspace: duodec_verify_workspace_bytes(B,gamma) bytes, zero-filled ONCE by
+ *   the caller before first use (the kernel restores it to zero). */
+size_t duodec_verify_workspace_bytes(int B, int gamma);
+
+int duodec_verify_fused(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss, int64_t t_sb,
+                        int64_t t_ss, int B, int gamma, int Vd, int Vt, const int64_t* tokens, int64_t tok_sb,
+                        const float* r, int64_t r_sb, const float* noise, int64_t noise_sb, float temperature,
+                        int top_k, float top_p, float draft_temperature, int draft_top_k, float draft_top_p,
+                        uint8_t* accept_mask, float* sel_target_p, float* sel_draft_p, int64_t* accepted_len,
+                        int64_t* token, uint8_t* all_accepted, void* workspace, size_t workspace_bytes,
+                        void* stream);
+
+/* ---- probability-space operators -----------------------------------------
+ * Accept test on stored probability histories; replaces the tensor part of
+ * decoding_ops.compute_acceptance_result (src/decoding_ops.py:127-147) for
+ * every sequence.  draft_probs/target_probs [B, gamma, V] with strides
+ * (sb, ss, 1); sel_* have the probability dtype. */
+int duodec_accept_probs(const void* draft_probs, int64_t d_sb, int64_t d_ss, const void* target_probs,
+                        int64_t t_sb, int64_t t_ss, int dtype, const int64_t* tokens, int64_t tok_sb,
+                        const float* r, int64_t r_sb, int B, int gamma, int V, uint8_t* accept_mask,
+                        void* sel_draft_p, void* sel_target_p, int64_t* accepted_len, void* stream);
+
+/* utils.sample with injected noise (src/utils.py:727-748): out[row] int64. */
+int duodec_sample_rows(const void* probs, int dtype, int64_t row_stride, const float* noise, int64_t noise_stride,
+                       int rows, int V, int64_t* out, void* stream);
+
+/* decoding_ops.sample_reject_token = sample(max_fn(p - q))
+ * (src/decoding_ops.py:190-206, src/utils.py:787-810). */
+int duodec_residual_sample(const void* target_probs, int64_t t_stride, const void* draft_probs, int64_t d_stride,
+                           int dtype, const float* noise, int64_t noise_stride, int rows, int V, int64_t* out,
+                           void* stream);
+
+/* utils.max_fn (src/utils.py:787-810): out float32 [rows, V]. */
+int duodec_max_fn(const void* x, int dtype, int64_t row_stride, int rows, int V, float* out, int64_t out_stride,
+                  void* stream);
+
+/* ---- transfer_top_k compression --------------------------------------------
+ * mode 0: utils.rebuild_topk_probs / rebuild_topk_uniform_probs (src/utils.py:751-784)
+ * mode 1: CommunicationSimulator._apply_top_k_compression (src/communication.py:288-308)
+ * mode 2: CommunicationSimulator.compress_rebuild_probs   (src/communication.py:348-395)
+ * mode 3: CommunicationSimulator.rebuild_full_probs       (src/communication.py:310-346; k ignored)
+ * probs/out [rows, V] of `dtype`; requires 0 < k < V for modes 0-2. */
+int duodec_topk_rebuild(const void* probs, int dtype, int64_t in_stride, void* out, int64_t out_stride, int rows,
+                        int V, int k, int mode, void* stream);
+
+/* ---- KV rollback --------------------------------------------------------
+ * KVCacheModel.rollback (src/model_gpu.py:362-383) for a cache that keeps
+ * per-sequence length counters: seq_len[b] = min(seq_len[b], end_pos) in
+ * place; no cache bytes move.  end_pos_vec (int64 [B]) may be NULL, then the
+ * scalar applies to every sequence. */
+int duodec_kv_truncate(int32_t* seq_len, const int64_t* end_pos_vec, int64_t end_pos, int B, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DUODEC_H_ */

@@ -1,0 +1,325 @@
+"""GPU parity: the sm_100a kernels (through the C ABI) against the CPU oracle and
+the reference-generated golden fixtures.  Integer outputs (accepted lengths,
+token ids, masks, support sets) must be bit-exact; probabilities agree within
+1e-5 relative in fp32 (north_star tolerance), 1e-2 in bf16."""
+
+import numpy as np
+import pytest
+import torch
+
+import oracle
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-5
+ATOL = 1e-10
+
+
+@pytest.fixture(scope="module")
+def ops():
+    import duodecoding_b200.ops as ops
+
+    return ops
+
+
+@pytest.fixture(scope="module")
+def dev():
+    return torch.device("cuda:0")
+
+
+def _t(a):
+    return torch.from_numpy(np.ascontiguousarray(a))
+
+
+def _close(got, want, rtol=RTOL, atol=ATOL):
+    torch.testing.assert_close(got.cpu().float(), want.float(), rtol=rtol, atol=atol)
+
+
+# ------------------------------------------------------------------ norm_logits
+def test_norm_logits_golden(golden, ops, dev):
+    for si in range(3):
+        x = _t(golden[f"norm/{si}/logits"])
+        for wi in range(8):
+            T, k, p = golden[f"norm/{si}/{wi}/params"]
+            want = _t(golden[f"norm/{si}/{wi}/probs"])
+            got = ops.norm_logits(x.to(dev), float(T), int(k), float(p))
+            assert got.shape == want.shape and got.dtype == want.dtype
+            assert torch.equal(got.cpu() == 0, want == 0), f"support differs shape {si} warp {wi}"
+            _close(got, want)
+    x = _t(golden["norm2d/logits"])
+    got = ops.norm_logits(x.to(dev), 0.9, 20, 0.8)
+    want = _t(golden["norm2d/probs"])
+    assert torch.equal(got.cpu() == 0, want == 0)
+    _close(got, want)
+
+
+@pytest.mark.parametrize("team", [1, 2, 4, 8])
+@pytest.mark.parametrize("warp", [(1.0, 0, 0.0), (1.0, 0, 0.9), (0.7, 100, 0.0), (1.3, 64, 0.8), (0.0, 0, 0.0)])
+def test_norm_logits_teams(ops, dev, team, warp):
+    g = torch.Generator().manual_seed(11)
+    x = torch.randn(6, 5000, generator=g) * 3
+    T, k, p = warp
+    want = oracle.norm_logits(x, T, k, p)
+    ops.set_team_size(team)
+    try:
+        got = ops.norm_logits(x.to(dev), T, k, p)
+    finally:
+        ops.set_team_size(0)
+    assert torch.equal(got.cpu() == 0, want == 0)
+    _close(got, want)
+
+
+def test_norm_logits_large_vocab(ops, dev):
+    g = torch.Generator().manual_seed(12)
+    for V in (32000, 151936):
+        x = torch.randn(3, V, generator=g) * 3
+        for T, k, p in [(1.0, 0, 0.0), (1.0, 0, 0.9), (0.8, 1024, 0.95)]:
+            want = oracle.norm_logits(x, T, k, p)
+            got = ops.norm_logits(x.to(dev), T, k, p)
+            assert torch.equal(got.cpu() == 0, want == 0), (V, T, k, p)
+            _close(got, want)
+
+
+def test_norm_logits_flat_rows_take_the_slow_path(ops, dev):
+    # near-uniform rows put thousands of entries in the boundary band -> bisection path
+    g = torch.Generator().manual_seed(13)
+    x = torch.randn(4, 3000, generator=g) * 1e-3
+    want = oracle.norm_logits(x, 1.0, 0, 0.5)
+    got = ops.norm_logits(x.to(dev), 1.0, 0, 0.5)
+    # boundary decided on exp values: allow the support to differ by entries of equal probability only
+    diff = (got.cpu() == 0) != (want == 0)
+    assert int(diff.sum()) <= 2 * x.shape[0]
+    assert abs(float(got.sum()) - x.shape[0]) < 1e-3
+
+
+def test_norm_logits_bf16(ops, dev):
+    g = torch.Generator().manual_seed(14)
+    x = (torch.randn(4, 32000, generator=g) * 3).bfloat16()
+    for T, k, p in [(1.0, 0, 0.0), (1.0, 0, 0.9), (1.0, 50, 0.0)]:
+        want = oracle.norm_logits(x.float(), T, k, p)
+        got = ops.norm_logits(x.to(dev), T, k, p, out_dtype=torch.float32)
+        assert torch.equal(got.cpu() == 0, want == 0), (T, k, p)
+        _close(got, want)
+        got16 = ops.norm_logits(x.to(dev), T, k, p)
+        assert got16.dtype == torch.bfloat16
+        torch.testing.assert_close(got16.cpu().float(), want, rtol=1e-2, atol=1e-6)
+
+
+# ------------------------------------------------------------------ fused verify
+def _check_verify(got, want):
+    assert torch.equal(got["accept_mask"].cpu(), want["accept_mask"])
+    assert torch.equal(got["accepted_len"].cpu(), want["accepted_len"])
+    assert torch.equal(got["token"].cpu(), want["token"])
+    assert torch.equal(got["all_accepted"].cpu(), want["all_accepted"])
+    _close(got["selected_target_p"], want["selected_target_p"])
+    _close(got["selected_draft_p"], want["selected_draft_p"])
+
+
+def test_verify_fused_golden(golden, ops, dev):
+    for ci in range(7):
+        pre = f"verify/{ci}/"
+        T, k, p, _ = golden[pre + "params"]
+        tl, dl = _t(golden[pre + "target_logits"]), _t(golden[pre + "draft_logits"])
+        toks, r, noise = _t(golden[pre + "tokens"]), _t(golden[pre + "r"]), _t(golden[pre + "noise"])
+        got = ops.verify_fused(dl.to(dev), tl.to(dev), toks.to(dev), r.to(dev), noise.to(dev), float(T), int(k),
+                               float(p))
+        assert torch.equal(got["accepted_len"].cpu(), _t(golden[pre + "accepted_len"])), ci
+        assert torch.equal(got["token"].cpu(), _t(golden[pre + "token"])), ci
+        assert torch.equal(got["accept_mask"].cpu(), _t(golden[pre + "accept_mask"])), ci
+        _close(got["selected_target_p"], _t(golden[pre + "selected_target_p"]))
+        _close(got["selected_draft_p"], _t(golden[pre + "selected_draft_p"]))
+
+
+def _make_case(seed, B, gamma, V, sigma, T, k, p, dtype=torch.float32, Vd=None):
+    g = torch.Generator().manual_seed(seed)
+    Vd = V if Vd is None else Vd
+    tl = (torch.randn(B, gamma + 1, V, generator=g) * 3).to(dtype)
+    dl = (tl[:, :gamma, :Vd].float() + sigma * torch.randn(B, gamma, Vd, generator=g)).to(dtype)
+    q = oracle.norm_logits(dl.float(), T, k, p)
+    toks = torch.stack(
+        [oracle.sample(q[:, j], torch.empty(B, Vd).exponential_(1, generator=g))[:, 0] for j in range(gamma)], 1
+    )
+    r = torch.rand(B, gamma, generator=g)
+    noise = torch.empty(B, V).exponential_(1, generator=g)
+    return dl, tl, toks, r, noise
+
+
+@pytest.mark.parametrize("team", [0, 1, 2, 4, 8])
+@pytest.mark.parametrize(
+    "warp", [(1.0, 0, 0.0), (1.0, 0, 0.9), (0.8, 40, 0.0), (1.2, 200, 0.7), (0.0, 0, 0.0)]
+)
+def test_verify_fused_vs_oracle(ops, dev, team, warp):
+    T, k, p = warp
+    dl, tl, toks, r, noise = _make_case(21, 6, 4, 6000, 0.7, T, k, p)
+    want = oracle.fused_verify(dl, tl, toks, r, noise, T, k, p)
+    ops.set_team_size(team)
+    try:
+        got = ops.verify_fused(dl.to(dev), tl.to(dev), toks.to(dev), r.to(dev), noise.to(dev), T, k, p)
+    finally:
+        ops.set_team_size(0)
+    _check_verify(got, want)
+
+
+@pytest.mark.parametrize("sigma", [0.3, 1.0, 2.0])
+def test_verify_fused_vocab_32000(ops, dev, sigma):
+    dl, tl, toks, r, noise = _make_case(22, 8, 4, 32000, sigma, 1.0, 0, 0.9)
+    want = oracle.fused_verify(dl, tl, toks, r, noise, 1.0, 0, 0.9)
+    got = ops.verify_fused(dl.to(dev), tl.to(dev), toks.to(dev), r.to(dev), noise.to(dev), 1.0, 0, 0.9)
+    _check_verify(got, want)
+
+
+def test_verify_fused_qwen_vocab_bf16(ops, dev):
+    dl, tl, toks, r, noise = _make_case(23, 3, 6, 151936, 0.5, 1.0, 0, 0.0, dtype=torch.bfloat16)
+    want = oracle.fused_verify(dl.float(), tl.float(), toks, r, noise, 1.0, 0, 0.0)
+    got = ops.verify_fused(dl.to(dev), tl.to(dev), toks.to(dev), r.to(dev), noise.to(dev), 1.0, 0, 0.0)
+    _check_verify(got, want)
+
+
+def test_verify_fused_unequal_vocab(ops, dev):
+    # draft vocabulary smaller than the target's: gathers and the residual use the common prefix
+    dl, tl, toks, r, noise = _make_case(24, 4, 3, 1200, 0.8, 1.0, 0, 0.0, Vd=1000)
+    want = oracle.fused_verify(dl, tl, toks, r, noise, 1.0, 0, 0.0)
+    got = ops.verify_fused(dl.to(dev), tl.to(dev), toks.to(dev), r.to(dev), noise.to(dev), 1.0, 0, 0.0)
+    _check_verify(got, want)
+
+
+def test_verify_fused_strided_history_views(ops, dev):
+    # rows taken out of a longer [B, L, V] history buffer, as KVCacheModel holds them
+    g = torch.Generator().manual_seed(25)
+    B, gamma, V, L = 3, 4, 2000, 12
+    hist_t = torch.randn(B, L, V, generator=g) * 3
+    hist_d = hist_t + 0.5 * torch.randn(B, L, V, generator=g)
+    tl, dl = hist_t[:, 5 : 5 + gamma + 1], hist_d[:, 5 : 5 + gamma]
+    q = oracle.norm_logits(dl, 1.0, 0, 0.0)
+    toks = torch.stack(
+        [oracle.sample(q[:, j], torch.empty(B, V).exponential_(1, generator=g))[:, 0] for j in range(gamma)], 1
+    )
+    r, noise = torch.rand(B, gamma, generator=g), torch.empty(B, V).exponential_(1, generator=g)
+    want = oracle.fused_verify(dl, tl, toks, r, noise)
+    ht, hd = hist_t.to(dev), hist_d.to(dev)
+    got = ops.verify_fused(hd[:, 5 : 5 + gamma], ht[:, 5 : 5 + gamma + 1], toks.to(dev), r.to(dev), noise.to(dev))
+    _check_verify(got, want)
+
+
+def test_verify_fused_edge_cases(ops, dev):
+    # r == 0 accepts everything (bonus path); r > 1 rejects at position 0
+    dl, tl, toks, r, noise = _make_case(26, 4, 4, 3000, 0.5, 1.0, 0, 0.0)
+    for rv in (0.0, 2.0):
+        rr = torch.full_like(r, rv)
+        want = oracle.fused_verify(dl, tl, toks, rr, noise)
+        got = ops.verify_fused(dl.to(dev), tl.to(dev), toks.to(dev), rr.to(dev), noise.to(dev))
+        _check_verify(got, want)
+    # identical draft and target: p/q == 1 accepts for every r <= 1
+    want = oracle.fused_verify(tl[:, :4], tl, toks, r, noise)
+    got = ops.verify_fused(tl[:, :4].to(dev), tl.to(dev), toks.to(dev), r.to(dev), noise.to(dev))
+    _check_verify(got, want)
+    assert bool(got["all_accepted"].all())
+    # gamma == 0: only the bonus token
+    got = ops.verify_fused(dl[:, :0].to(dev), tl[:, :1].to(dev), toks[:, :0].to(dev), r[:, :0].to(dev), noise.to(dev))
+    want = oracle.fused_verify(dl[:, :0], tl[:, :1], toks[:, :0], r[:, :0], noise)
+    assert torch.equal(got["token"].cpu(), want["token"]) and int(got["accepted_len"].sum()) == 0
+
+
+def test_verify_fused_repeatable_and_workspace_self_cleaning(ops, dev):
+    dl, tl, toks, r, noise = _make_case(27, 5, 4, 4096, 1.0, 1.0, 0, 0.9)
+    args = [t.to(dev) for t in (dl, tl, toks, r, noise)]
+    first = ops.verify_fused(*args, 1.0, 0, 0.9)
+    first = {k: v.clone() for k, v in first.items()}
+    for _ in range(5):
+        again = ops.verify_fused(*args, 1.0, 0, 0.9)
+        for k in first:
+            assert torch.equal(first[k], again[k]), k
+
+
+# ------------------------------------------------------------------ probability-space ops
+def test_sample_and_max_fn_golden(golden, ops, dev):
+    p, e = _t(golden["sample/probs"]), _t(golden["sample/noise"])
+    got = ops.sample_rows(p.to(dev), e.to(dev))
+    assert torch.equal(got.cpu(), _t(golden["sample/idx"]))
+    x = _t(golden["maxfn/x"])
+    got = ops.max_fn(x.to(dev))
+    want = _t(golden["maxfn/y"])
+    assert torch.equal(got.cpu() == 0, want == 0)
+    _close(got, want)
+
+
+def test_residual_sample_vs_oracle(ops, dev):
+    g = torch.Generator().manual_seed(31)
+    P = torch.softmax(torch.randn(16, 5000, generator=g) * 3, -1)
+    Q = torch.softmax(torch.randn(16, 5000, generator=g) * 3, -1)
+    Q[3] = P[3]  # zero residual mass -> argmax fallback (index 0)
+    e = torch.empty(16, 5000).exponential_(1, generator=g)
+    want = oracle.sample_reject_token(P, Q, e)
+    got = ops.residual_sample(P.to(dev), Q.to(dev), e.to(dev))
+    assert torch.equal(got.cpu(), want)
+    want = oracle.sample_accept_token(P, e)
+    got = ops.sample_rows(P.to(dev), e.to(dev))
+    assert torch.equal(got.cpu(), want)
+
+
+def test_accept_probs_vs_oracle(ops, dev):
+    g = torch.Generator().manual_seed(32)
+    B, gamma, V = 5, 6, 999
+    P = torch.softmax(torch.randn(B, gamma, V, generator=g) * 2, -1)
+    Q = torch.softmax(torch.randn(B, gamma, V, generator=g) * 2, -1)
+    toks = torch.randint(0, V, (B, gamma), generator=g)
+    Q[0, 1, toks[0, 1]] = 0.0  # q == 0, p > 0 -> inf -> accept
+    P[1, 0, toks[1, 0]] = 0.0
+    Q[1, 0, toks[1, 0]] = 0.0  # 0/0 -> nan -> reject
+    r = torch.rand(B, gamma, generator=g)
+    want = oracle.accept_rows(Q, P, toks, r)
+    got = ops.accept_probs(Q.to(dev), P.to(dev), toks.to(dev), r.to(dev))
+    assert torch.equal(got["accept_mask"].cpu(), want["accept_mask"])
+    assert torch.equal(got["accepted_len"].cpu(), want["accepted_len"])
+    assert torch.equal(got["selected_draft_p"].cpu(), want["selected_draft_p"])
+    assert torch.equal(got["selected_target_p"].cpu(), want["selected_target_p"])
+
+
+# ------------------------------------------------------------------ transfer_top_k compression
+def test_topk_rebuild_golden(golden, ops, dev):
+    pr = _t(golden["rebuild/probs"])
+    for k in (1, 7, 64, 999):
+        got = ops.topk_rebuild(pr.to(dev), k, 0)
+        _close(got, _t(golden[f"rebuild/k{k}"]))
+    prn = _t(golden["rebuild_sparse/probs"])
+    _close(ops.topk_rebuild(prn.to(dev), 512, 0), _t(golden["rebuild_sparse/k512"]))
+    v1 = _t(golden["comm/probs1d"])
+    for k in (1, 32):
+        got = ops.topk_rebuild(v1.to(dev)[None], k, 1)[0]
+        assert torch.equal(got.cpu(), _t(golden[f"comm/topk{k}"]))
+    comp = _t(golden["comm/topk32"])
+    _close(ops.topk_rebuild(comp.to(dev)[None], 0, 3)[0], _t(golden["comm/rebuild_full32"]))
+    p3 = _t(golden["comm/probs3d"])
+    _close(ops.topk_rebuild(p3.to(dev), 16, 2), _t(golden["comm/compress_rebuild16"]))
+
+
+@pytest.mark.parametrize("team", [1, 2, 8])
+def test_topk_rebuild_ties_lowest_index_first(ops, dev, team):
+    g = torch.Generator().manual_seed(33)
+    # bf16-grid probabilities: many exact ties at the k-th value
+    p = torch.softmax((torch.randn(5, 32000, generator=g) * 3).bfloat16().float(), -1)
+    ops.set_team_size(team)
+    try:
+        for k in (100, 1024):
+            want = oracle.rebuild_topk_probs(p, k)
+            got = ops.topk_rebuild(p.to(dev), k, 0)
+            assert torch.equal((got.cpu() - want).abs() > 1e-6, torch.zeros_like(want, dtype=torch.bool))
+            _close(got, want)
+            want1 = torch.stack([oracle.apply_top_k_compression(row, k) for row in p])
+            got1 = ops.topk_rebuild(p.to(dev), k, 1)
+            assert torch.equal(got1.cpu(), want1)
+    finally:
+        ops.set_team_size(0)
+
+
+def test_kv_truncate(ops, dev):
+    lens = torch.tensor([10, 3, 7, 0], dtype=torch.int32, device=dev)
+    ops.kv_truncate(lens, 5)
+    assert lens.tolist() == [5, 3, 5, 0]
+    ops.kv_truncate(lens, torch.tensor([9, 1, 2, 4]))
+    assert lens.tolist() == [5, 1, 2, 0]
+
+
+def test_cpu_tensors_are_rejected(ops):
+    with pytest.raises(RuntimeError):
+        ops.norm_logits(torch.randn(2, 10), 1.0)
