@@ -9,6 +9,7 @@
 #include "../../include/duodec.h"
 #include "prob_kernels.cuh"
 #include "row_kernels.cuh"
+#include "stream_kernel.cuh"
 #include "verify_kernels.cuh"
 
 using namespace duodec;
@@ -17,6 +18,7 @@ namespace {
 
 constexpr size_t kMaxDynSmem = 232448;  // 227 KB opt-in limit per block on sm_100
 std::atomic<int> g_team_override{0};
+std::atomic<int> g_stream_path{1};
 
 size_t team_smem_bytes(int V, int rows_resident, int C) {
   const int per = C == 1 ? V : ((((V + C - 1) / C) + 7) & ~7);
@@ -51,6 +53,20 @@ cudaError_t ensure_smem(const void* kernel) {
   if (e != cudaSuccess) return e;
   done.emplace_back(kernel, dev);
   return cudaSuccess;
+}
+
+int sm_count() {
+  static std::mutex mu;
+  static int cached[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 0;
+  std::lock_guard<std::mutex> lk(mu);
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
+    cached[dev] = n;
+  }
+  return cached[dev];
 }
 
 template <class K, class P>
@@ -94,6 +110,8 @@ int duodec_team_size(int V, int rows_resident) {
 
 void duodec_set_team_size(int team) { g_team_override.store(team); }
 
+void duodec_set_stream_path(int enabled) { g_stream_path.store(enabled); }
+
 int duodec_norm_logits(const void* logits, int in_dtype, int64_t in_row_stride, void* out, int out_dtype,
                        int64_t out_row_stride, int rows, int V, float temperature, int top_k, float top_p,
                        void* stream) {
@@ -135,8 +153,10 @@ int duodec_norm_logits(const void* logits, int in_dtype, int64_t in_row_stride, 
 
 size_t duodec_verify_workspace_bytes(int B, int gamma) {
   if (B <= 0 || gamma < 0) return 0;
-  // [B] int counters (padded to 8 bytes each) + [B, gamma+1] int64 position tokens
-  return size_t(B) * 8 + size_t(B) * size_t(gamma + 1) * 8;
+  // [B] int counters (8 bytes each) + [B, gamma+1] int64 position tokens
+  // + [B, gamma] int position counters (8 bytes each) + [B, 2*gamma+1] row records
+  return size_t(B) * 8 + size_t(B) * size_t(gamma + 1) * 8 + size_t(B) * size_t(gamma) * 8 +
+         size_t(B) * size_t(2 * gamma + 1) * sizeof(RowRecord);
 }
 
 int duodec_verify_fused(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss, int64_t t_sb,
@@ -154,6 +174,70 @@ int duodec_verify_fused(const void* draft, const void* target, int dtype, int64_
   if (!(temperature >= 0.0f) || !(draft_temperature >= 0.0f)) return DUODEC_EINVAL;
   if ((temperature == 0.0f) != (draft_temperature == 0.0f)) return DUODEC_EINVAL;  // greedy on both or neither
   if (workspace_bytes < duodec_verify_workspace_bytes(B, gamma)) return DUODEC_EWORKSPACE;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  {
+    // fast path: persistent row-stream kernel (rows of <= 32768 entries that TMA can move:
+    // 16-byte aligned rows and noise, equal vocabularies, no top-k, sampled temperatures)
+    const size_t elt = dtype == DUODEC_F32 ? 4 : 2;
+    auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+    const bool ok = g_stream_path.load() != 0 && Vd == Vt && Vt <= kChunk * kMaxChunks && temperature > 0.0f &&
+                    draft_temperature > 0.0f && top_k <= 0 && draft_top_k <= 0 && (size_t(Vt) * elt) % 16 == 0 &&
+                    al16(target) && (gamma == 0 || al16(draft)) && (size_t(t_sb) * elt) % 16 == 0 &&
+                    (size_t(t_ss) * elt) % 16 == 0 && (size_t(d_sb) * elt) % 16 == 0 &&
+                    (size_t(d_ss) * elt) % 16 == 0 && al16(noise) && (noise_sb % 4) == 0;
+    if (ok) {
+      StreamParams S;
+      S.draft = draft;
+      S.target = target;
+      S.d_sb = d_sb;
+      S.d_ss = d_ss;
+      S.t_sb = t_sb;
+      S.t_ss = t_ss;
+      S.B = B;
+      S.gamma = gamma;
+      S.V = Vt;
+      S.tokens = reinterpret_cast<const long long*>(tokens);
+      S.tok_sb = tok_sb;
+      S.r = r;
+      S.r_sb = r_sb;
+      S.noise = noise;
+      S.noise_sb = noise_sb;
+      S.t_temp = temperature;
+      S.t_top_p = top_p;
+      S.d_temp = draft_temperature;
+      S.d_top_p = draft_top_p;
+      S.accept_mask = accept_mask;
+      S.sel_p = sel_target_p;
+      S.sel_q = sel_draft_p;
+      S.accepted_len = reinterpret_cast<long long*>(accepted_len);
+      S.token = reinterpret_cast<long long*>(token);
+      S.all_accepted = all_accepted;
+      char* w = reinterpret_cast<char*>(workspace);
+      S.counters = reinterpret_cast<int*>(w);
+      w += size_t(B) * 8;
+      S.pair_token = reinterpret_cast<long long*>(w);
+      w += size_t(B) * size_t(gamma + 1) * 8;
+      S.pair_counters = reinterpret_cast<int*>(w);
+      w += size_t(B) * size_t(gamma) * 8;
+      S.records = reinterpret_cast<RowRecord*>(w);
+      const size_t smem = size_t(kSlots) * kSlotBytes + kHistBytes + sizeof(StreamScratch) + 128;
+      const int njobs = B * (2 * gamma + 1);
+      int sms = sm_count();
+      if (sms <= 0) sms = 148;
+      const int grid = njobs < sms ? njobs : sms;
+      cudaError_t e;
+      if (dtype == DUODEC_F32) {
+        e = ensure_smem(reinterpret_cast<const void*>(verify_stream_kernel<float>));
+        if (e != cudaSuccess) return int(e);
+        verify_stream_kernel<float><<<grid, kST, smem, st>>>(S);
+      } else {
+        e = ensure_smem(reinterpret_cast<const void*>(verify_stream_kernel<__nv_bfloat16>));
+        if (e != cudaSuccess) return int(e);
+        verify_stream_kernel<__nv_bfloat16><<<grid, kST, smem, st>>>(S);
+      }
+      return int(cudaGetLastError());
+    }
+  }
   const int Vmax = Vd > Vt ? Vd : Vt;
   const int C = pick_team(Vmax, 2);
   if (C == 0) return DUODEC_ETOOBIG;
@@ -191,7 +275,6 @@ int duodec_verify_fused(const void* draft, const void* target, int dtype, int64_
   P.per = C == 1 ? Vmax : ((((Vmax + C - 1) / C) + 7) & ~7);
   P.slice_floats = ((P.per + 7) & ~7) + 8;
   const size_t smem = team_smem_bytes(Vmax, 2, C);
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int teams = B * (gamma + 1);
   cudaError_t e = cudaSuccess;
   DISPATCH_TEAM(C, {

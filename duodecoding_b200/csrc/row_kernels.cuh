@@ -116,8 +116,10 @@ __device__ __forceinline__ int team_tie_cut(const float* xs, Slice s, float tau,
     };
     const unsigned me = Team<C>::rank();
     I4 lo{{0, 0, 0, 0}}, hi{{0, 0, 0, 0}};
-    if (me < 4) lo.v[me] = block_total;
-    else hi.v[me - 4] = block_total;
+    if (threadIdx.x == 0) {  // one contribution per block: the block reduce sums over threads
+      if (me < 4) lo.v[me] = block_total;
+      else hi.v[me - 4] = block_total;
+    }
     lo = team_allreduce<C>(lo, OpSumI4(), xc);
     if constexpr (C > 4) hi = team_allreduce<C>(hi, OpSumI4(), xc);
     all = 0;

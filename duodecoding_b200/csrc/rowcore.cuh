@@ -8,26 +8,34 @@
 // normaliser Z of the kept entries, so that  p_i = keep(e_i) / Z.
 //
 // Top-p (nucleus) without sorting the row:
-//   1. integer histogram of the e_i over 8192 log-spaced bins taken straight
-//      from the float bit pattern (256 bins per binade, exact float edges);
-//   2. per-bin mass bounds  count*lo_edge < mass <= count*hi_edge  give, by one
-//      block scan, the band of bins [b_lo, b_hi] that can contain the nucleus
-//      boundary; bins above it are kept, bins below it are dropped;
-//   3. the few band entries are ordered exactly like the reference's sort
+//   1. integer histogram of the e_i over 4096 log-spaced bins taken straight
+//      from the float bit pattern d = bits(1.0f) - bits(e): bin = d >> 16 (128
+//      bins per binade), and next to the count of each bin the integer sum of
+//      the low 16 bits of d.  Inside a bin e is linear in d, so
+//          mass(bin) = count * e_top(bin) - ulp(bin) * sum_low(bin)
+//      is EXACT: two native shared-memory integer atomics per entry give the
+//      exact mass of every bin, independent of summation order, team size
+//      and launch.
+//   2. one block scan over the 4096 bin masses (double) finds the bin b* that
+//      holds the nucleus boundary and the exact mass above it; bins above b*
+//      are kept, bins below are dropped;
+//   3. the few entries of b* are ordered exactly like the reference's sort
 //      (scaled logit descending, lowest index first on ties), their masses are
-//      prefix-summed after the exact mass above the band, and the first entry
-//      whose inclusive mass exceeds top_p * Z1 is the last one kept
+//      prefix-summed after the mass above, and the first entry whose inclusive
+//      mass exceeds top_p * Z1 is the last one kept
 //      (src/utils.py:669-681: drop sorted position j when cum[j-1] > top_p).
-//   A band that reaches the histogram tail or holds more than kCandCap entries
-//   (near-uniform rows) takes a slow bisection on (e, index) keys instead.
+//   A boundary below 2^-32 of the row maximum, or a boundary bin with more
+//   than kCandCap entries (near-uniform rows), takes a slow bisection on
+//   (e, index) keys instead.
 #pragma once
 
 #include "scan.cuh"
 
 namespace duodec {
 
-constexpr int kHistBins = 8192;            // 32 binades x 256 bins
-constexpr int kHistBytes = kHistBins * 4;  // 32 KB, reused for the band work
+constexpr int kHistBins = 4096;                // 32 binades x 128 bins
+constexpr int kBinShift = 16;                  // low 16 bits of d stay inside a bin
+constexpr int kHistBytes = 2 * kHistBins * 4;  // counts + low sums = 32 KB, reused for the band work
 constexpr int kCandCap = 1024;
 constexpr unsigned kOneBits = 0x3F800000u;
 
@@ -45,7 +53,8 @@ struct RowScratch {
   unsigned long long bar;   // mbarriers for TMA bulk staging
   unsigned long long bar2;
   int res[4];
-  int b_lo, b_hi, ncand, jstar;
+  int bstar, ncand, jstar, overflow;
+  double m_above;
 };
 
 struct RowStat {
@@ -58,12 +67,15 @@ __device__ __forceinline__ float keep_e(float e, unsigned keep_bits) {
   return __float_as_uint(e) > keep_bits ? e : 0.0f;
 }
 
-__device__ __forceinline__ int e_bin(float e) {
-  const unsigned d = (kOneBits - __float_as_uint(e)) >> 15;
-  return d < unsigned(kHistBins - 1) ? int(d) : kHistBins - 1;
+// bin b holds the float bit patterns kOneBits - d with d in [b<<16, (b<<16) + 0xffff]
+__device__ __forceinline__ unsigned bin_top_bits(int b) { return kOneBits - (unsigned(b) << kBinShift); }
+// exact mass of a bin from its count and the sum of the low bits of d
+__device__ __forceinline__ double bin_mass(int b, unsigned cnt, unsigned low) {
+  const unsigned top = bin_top_bits(b);
+  const double e_top = double(__uint_as_float(top));
+  const double ulp = e_top - double(__uint_as_float(top - 1u));
+  return double(cnt) * e_top - ulp * double(low);
 }
-// bin b holds float bit patterns in (kOneBits - ((b+1)<<15), kOneBits - (b<<15)]
-__device__ __forceinline__ unsigned bin_hi_bits(int b) { return kOneBits - (unsigned(b) << 15); }
 
 // ---------------------------------------------------------------------------
 // argmax of a staged row (temperature == 0 path, src/utils.py:700-704)
@@ -122,8 +134,8 @@ __device__ __noinline__ RowStat nucleus_bisect(float* xs, Slice s, int n4, float
 // ---------------------------------------------------------------------------
 // xs     : this block's slice, fp32 scaled logits padded with -inf to n4*4
 // per    : slice pitch of the team (entry g lives in block g / per)
-// row    : the original global row (band entries are re-read from it so that
-//          their order is the order of the scaled logits, not of the exps)
+// row    : the original global row (boundary-bin entries are re-read from it so
+//          that their order is the order of the scaled logits, not of the exps)
 // work   : kHistBytes of shared memory
 template <int C, class TIn>
 __device__ __forceinline__ RowStat row_core(float* xs, Slice s, int per, int V, const TIn* __restrict__ row,
@@ -132,7 +144,8 @@ __device__ __forceinline__ RowStat row_core(float* xs, Slice s, int per, int V, 
   Xchg* xc = &sc->xc;
   const int n4 = (s.n + 3) >> 2;
   float4* x4 = reinterpret_cast<float4*>(xs);
-  int* hist = reinterpret_cast<int*>(work);
+  unsigned* cnt = reinterpret_cast<unsigned*>(work);
+  unsigned* low = cnt + kHistBins;
 
   // pass 1: max
   float mx = -INFINITY;
@@ -144,18 +157,18 @@ __device__ __forceinline__ RowStat row_core(float* xs, Slice s, int per, int V, 
 
   // top-k: keep every entry >= the k-th largest (ties survive, src/utils.py:665-666)
   float tau_k = -INFINITY;
-  if (top_k > 0 && top_k < V) tau_k = team_kth_largest<C>(xs, n4, top_k, hist, sc->res, xc).value;
+  if (top_k > 0 && top_k < V)
+    tau_k = team_kth_largest<C>(xs, n4, top_k, reinterpret_cast<int*>(work), sc->res, xc).value;
 
   const bool nucleus = top_p > 0.0f;
   if (nucleus) {
     __syncthreads();
-    for (int i = threadIdx.x; i < kHistBins; i += kThreads) hist[i] = 0;
+    for (int i = threadIdx.x; i < 2 * kHistBins; i += kThreads) cnt[i] = 0u;
     __syncthreads();
   }
 
-  // pass 2: e_i = exp(x_i - m) in place, Z1, histogram of e
+  // pass 2: e_i = exp(x_i - m) in place; Z1 (plain rows) or the exact-mass histogram (nucleus rows)
   float z = 0.0f;
-  int tail = 0;
   for (int i = threadIdx.x; i < n4; i += kThreads) {
     float4 v = x4[i];
     float e[4] = {v.x, v.y, v.z, v.w};
@@ -164,94 +177,87 @@ __device__ __forceinline__ RowStat row_core(float* xs, Slice s, int per, int V, 
       const float x = e[c];
       const float ex = (x >= tau_k) ? expf(__fsub_rn(x, m)) : 0.0f;
       e[c] = ex;
-      z += ex;
       if (nucleus) {
-        const int b = e_bin(ex);
-        if (b < kHistBins - 1) atomicAdd(&hist[b], 1);
-        else ++tail;
+        const unsigned d = kOneBits - __float_as_uint(ex);
+        const unsigned b = d >> kBinShift;
+        if (b < unsigned(kHistBins)) {
+          atomicAdd(&cnt[b], 1u);
+          atomicAdd(&low[b], d & 0xffffu);
+        } else {
+          z += ex;  // below 2^-32 of the maximum: summed in float, far under the rounding of Z1
+        }
+      } else {
+        z += ex;
       }
     }
     x4[i] = make_float4(e[0], e[1], e[2], e[3]);
   }
-  const float Z1 = team_allreduce<C>(z, OpSumF(), xc);
-  if (!nucleus) return RowStat{m, Z1, 0u};
+  const float zsum = team_allreduce<C>(z, OpSumF(), xc);
+  if (!nucleus) return RowStat{m, zsum, 0u};
 
-  const int tail_all = team_allreduce<C>(tail, OpSumI(), xc);
-  team_hist_allreduce<C>(hist, kHistBins);
+  team_hist_allreduce<C>(reinterpret_cast<int*>(cnt), 2 * kHistBins);
   if (threadIdx.x == 0) {
-    hist[kHistBins - 1] = tail_all;
-    sc->b_lo = kHistBins;
-    sc->b_hi = -1;
+    sc->bstar = kHistBins;
     sc->ncand = 0;
     sc->jstar = 0x7fffffff;
+    sc->overflow = 0;
   }
-  __syncthreads();
 
-  // mass bounds per bin and the band that can hold the nucleus boundary
-  const double target = double(top_p) * double(Z1);
-  constexpr int kPer = kHistBins / kThreads;  // 16 bins per thread, ascending bin = descending e
+  // exact bin masses -> boundary bin
+  constexpr int kPer = kHistBins / kThreads;  // 8 bins per thread, ascending bin = descending e
   const int b0 = int(threadIdx.x) * kPer;
-  D2 loc{0.0, 0.0};
+  double loc = 0.0;
+  bool big = false;
   for (int i = 0; i < kPer; ++i) {
-    const int b = b0 + i;
-    const double c = double(hist[b]);
-    const double hi = double(__uint_as_float(bin_hi_bits(b)));
-    const double lo = (b == kHistBins - 1) ? 0.0 : double(__uint_as_float(bin_hi_bits(b + 1)));
-    loc.a += c * hi;
-    loc.b += c * lo;
+    const unsigned c = cnt[b0 + i];
+    big |= (c > 65535u);  // the 32-bit low sum may have wrapped
+    loc += bin_mass(b0 + i, c, low[b0 + i]);
   }
-  D2 run = block_exscan(loc, OpSumD2(), D2{0.0, 0.0}, xc);
+  double total = 0.0;
+  const double run0 = block_exscan(loc, OpSumD(), 0.0, xc, &total);
+  const double Z1 = total + double(zsum);
+  const double target = double(top_p) * Z1;
+  if (big) sc->overflow = 1;
   {
-    int my_lo = kHistBins, my_hi = -1;
+    int mine = kHistBins;
+    double run = run0;
     for (int i = 0; i < kPer; ++i) {
-      const int b = b0 + i;
-      const double c = double(hist[b]);
-      const double hi = double(__uint_as_float(bin_hi_bits(b)));
-      const double lo = (b == kHistBins - 1) ? 0.0 : double(__uint_as_float(bin_hi_bits(b + 1)));
-      // an entry of bin b is preceded by at least L(b-1) = run.b and the first
-      // entry with inclusive mass > target lies in b only if U(b) > target
-      if (run.b * (1.0 - 1e-5) <= target) my_hi = b;
-      run.a += c * hi;
-      run.b += c * lo;
-      if (c > 0.0 && run.a * (1.0 + 1e-5) > target && my_lo == kHistBins) my_lo = b;
+      run += bin_mass(b0 + i, cnt[b0 + i], low[b0 + i]);
+      if (run > target && mine == kHistBins) mine = b0 + i;
     }
-    if (my_lo < kHistBins) atomicMin(&sc->b_lo, my_lo);
-    if (my_hi >= 0) atomicMax(&sc->b_hi, my_hi);
+    if (mine < kHistBins) atomicMin(&sc->bstar, mine);
   }
   __syncthreads();
-  const int b_lo = sc->b_lo;
-  const int b_hi = sc->b_hi;
-  if (b_lo >= kHistBins) return RowStat{m, Z1, 0u};  // top_p covers the whole row
-
-  int nband = 0;
-  for (int i = 0; i < kPer; ++i) {
-    const int b = b0 + i;
-    if (b >= b_lo && b <= b_hi) nband += hist[b];
+  const int bstar = sc->bstar;
+  if (bstar >= kHistBins || sc->overflow || cnt[bstar] > unsigned(kCandCap))
+    return nucleus_bisect<C>(xs, s, n4, m, target, xc);
+  {
+    // the owner of b* publishes the exact mass above it
+    if (bstar >= b0 && bstar < b0 + kPer) {
+      double run = run0;
+      for (int i = 0; b0 + i < bstar; ++i) run += bin_mass(b0 + i, cnt[b0 + i], low[b0 + i]);
+      sc->m_above = run;
+    }
   }
-  nband = block_allreduce(nband, OpSumI(), xc);
-  if (b_hi >= kHistBins - 1 || nband > kCandCap) return nucleus_bisect<C>(xs, s, n4, m, target, xc);
+  __syncthreads();
+  const double m_above = sc->m_above;
 
-  // pass 3: exact mass above the band, collect the band entries
+  // pass 3: collect the entries of the boundary bin
   BandWork* bw = reinterpret_cast<BandWork*>(work);
-  const unsigned hi_bits = bin_hi_bits(b_lo);      // bits >  hi_bits  <=> bin <  b_lo
-  const unsigned lo_bits = bin_hi_bits(b_hi + 1);  // bits >  lo_bits  <=> bin <= b_hi
-  __syncthreads();                                 // histogram reads done before the region is reused
-  float above = 0.0f;
+  __syncthreads();  // histogram reads done before the region is reused
   for (int i = threadIdx.x; i < n4; i += kThreads) {
     const float4 v = x4[i];
     const float e[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
-      const unsigned bits = __float_as_uint(e[c]);
-      if (bits > hi_bits) above += e[c];
-      else if (bits > lo_bits) {
+      if (int((kOneBits - __float_as_uint(e[c])) >> kBinShift) == bstar) {
         const int pos = atomicAdd(&sc->ncand, 1);
         if (pos < kCandCap) bw->cand_local[pos] = i * 4 + c;
       }
     }
   }
-  const double m_above = team_allreduce<C>(double(above), OpSumD(), xc);
-  // exact ordering keys of this block's band entries (re-read the scaled logit)
+  __syncthreads();
+  // exact ordering keys of this block's entries (re-read the scaled logit)
   const int nloc = sc->ncand;
   for (int j = threadIdx.x; j < nloc; j += kThreads) {
     const int li = bw->cand_local[j];
@@ -262,7 +268,7 @@ __device__ __forceinline__ RowStat row_core(float* xs, Slice s, int per, int V, 
   }
   Team<C>::sync();
 
-  // team rank 0 orders the band and finds the boundary
+  // team rank 0 orders the boundary bin and finds the boundary
   float Zf = 0.0f;
   if (Team<C>::rank() == 0) {
     int n = nloc;
@@ -322,7 +328,7 @@ __device__ __forceinline__ RowStat row_core(float* xs, Slice s, int per, int V, 
     const int nkeep = jstar == 0x7fffffff ? n : jstar + 1;
     const double Z2 = nkeep > 0 ? bw->cum[nkeep - 1] : m_above;
     Zf = float(Z2);
-    // zero the band entries after the boundary in their owners' slices
+    // zero the entries after the boundary in their owners' slices
     for (int j = nkeep + threadIdx.x; j < n; j += kThreads) {
       const int g = int(unsigned(bw->key[j] & 0xffffffffull));
       const unsigned owner = (C == 1) ? 0u : unsigned(g / per);
@@ -331,7 +337,7 @@ __device__ __forceinline__ RowStat row_core(float* xs, Slice s, int per, int V, 
     }
   }
   Zf = team_bcast0<C>(Zf, xc);
-  return RowStat{m, Zf, lo_bits};
+  return RowStat{m, Zf, kOneBits - (unsigned(bstar + 1) << kBinShift)};
 }
 
 }  // namespace duodec

@@ -55,6 +55,11 @@ def set_team_size(team: int) -> None:
     lib.duodec_set_team_size(int(team))
 
 
+def set_stream_path(enabled: bool) -> None:
+    """Test hook: False forces the general team kernel for verify_fused."""
+    lib.duodec_set_stream_path(1 if enabled else 0)
+
+
 def team_size(V: int, rows_resident: int = 1) -> int:
     return int(lib.duodec_team_size(int(V), int(rows_resident)))
 

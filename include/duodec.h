@@ -46,6 +46,11 @@ int duodec_team_size(int V, int rows_resident);
 /* Override the team-size heuristic (0 = automatic).  Tuning / test hook. */
 void duodec_set_team_size(int team);
 
+/* duodec_verify_fused has two device paths: the persistent row-stream kernel
+ * (rows <= 32768 entries, 16-byte aligned, no top-k, T > 0) and the general
+ * team kernel.  0 forces the general kernel (test hook); default 1. */
+void duodec_set_stream_path(int enabled);
+
 /* ---- logits -> probabilities --------------------------------------------
  * Replaces utils.norm_logits + utils.top_k_top_p_filter
  * (/root/reference/src/utils.py:650-709).

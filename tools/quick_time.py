@@ -26,9 +26,14 @@ for warp in [(1.0, 0, 0.0), (1.0, 0, 0.9), (1.0, 50, 0.0), (0.0, 0, 0.0)]:
             torch.cuda.synchronize()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             n = 40
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr):
+                for i in range(NSETS):
+                    ops.verify_fused(*sets[i % NSETS], *warp, out=out)
+            gr.replay(); torch.cuda.synchronize()
             e0.record()
-            for i in range(n):
-                ops.verify_fused(*sets[i % NSETS], *warp, out=out)
+            for i in range(n // NSETS):
+                gr.replay()
             e1.record()
             torch.cuda.synchronize()
             us = e0.elapsed_time(e1) * 1e3 / n
