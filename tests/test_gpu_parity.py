@@ -387,7 +387,9 @@ def test_topk_rebuild_golden(golden, ops, dev):
     pr = _t(golden["rebuild/probs"])
     for k in (1, 7, 64, 999):
         got = ops.topk_rebuild(pr.to(dev), k, 0)
-        _close(got, _t(golden[f"rebuild/k{k}"]))
+        # the uniform fill is (1 - sum(top-k)) / n_zero: for k close to V that is a cancellation
+        # of two numbers near 1, defined only up to the fp32 summation order (a few 2^-24)
+        _close(got, _t(golden[f"rebuild/k{k}"]), atol=ATOL if k < 999 else 2.4e-7)
     prn = _t(golden["rebuild_sparse/probs"])
     _close(ops.topk_rebuild(prn.to(dev), 512, 0), _t(golden["rebuild_sparse/k512"]))
     v1 = _t(golden["comm/probs1d"])
