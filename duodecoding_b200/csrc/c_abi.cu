@@ -19,6 +19,7 @@ namespace {
 constexpr size_t kMaxDynSmem = 232448;  // 227 KB opt-in limit per block on sm_100
 std::atomic<int> g_team_override{0};
 std::atomic<int> g_stream_path{1};
+std::atomic<int*> g_stats{nullptr};
 
 size_t team_smem_bytes(int V, int rows_resident, int C) {
   const int per = C == 1 ? V : ((((V + C - 1) / C) + 7) & ~7);
@@ -111,6 +112,8 @@ int duodec_team_size(int V, int rows_resident) {
 void duodec_set_team_size(int team) { g_team_override.store(team); }
 
 void duodec_set_stream_path(int enabled) { g_stream_path.store(enabled); }
+
+void duodec_set_stats_buffer(int* device_counters) { g_stats.store(device_counters); }
 
 int duodec_norm_logits(const void* logits, int in_dtype, int64_t in_row_stride, void* out, int out_dtype,
                        int64_t out_row_stride, int rows, int V, float temperature, int top_k, float top_p,
@@ -220,7 +223,8 @@ int duodec_verify_fused(const void* draft, const void* target, int dtype, int64_
       S.pair_counters = reinterpret_cast<int*>(w);
       w += size_t(B) * size_t(gamma) * 8;
       S.records = reinterpret_cast<RowRecord*>(w);
-      const size_t smem = size_t(kSlots) * kSlotBytes + kHistBytes + sizeof(StreamScratch) + 128;
+      S.stats = g_stats.load();
+      const size_t smem = size_t(kSlots) * kSlotBytes + sizeof(V1Scratch) + 128;
       const int njobs = B * (2 * gamma + 1);
       int sms = sm_count();
       if (sms <= 0) sms = 148;

@@ -10,7 +10,7 @@ constexpr int kST = 1024;          // threads of a persistent block (one block p
 constexpr int kSW = kST / 32;      // warps
 constexpr int kChunk = 4096;       // row elements per ring slot: one float4 per thread
 constexpr int kMaxChunks = 8;      // rows up to 32768 entries live in 32 registers per thread
-constexpr int kSlots = 11;         // ring depth (11 x 16 KB)
+constexpr int kSlots = 13;         // ring depth (13 x 16 KB)
 constexpr int kSlotBytes = kChunk * 4;
 
 struct __align__(16) StreamScratch {

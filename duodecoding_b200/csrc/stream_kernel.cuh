@@ -1,33 +1,55 @@
 // Persistent row-stream verification kernel (the fast path of duodec_verify_fused).
 //
 // One 1024-thread block per SM walks a list of ROW jobs (draft row j, target
-// row j, ..., bonus target row of every sequence).  Rows arrive through an
-// 11-slot ring of 16 KB shared-memory chunks filled by TMA bulk copies that one
-// elected thread keeps issuing ahead of the consumers (up to 176 KB in flight
-// per SM), and are pulled into registers - one float4 per thread per chunk, a
-// whole <=32768-entry row in 32 registers per thread - so the logit warp and
-// the softmax statistics never touch shared memory again except for the
-// integer histogram of the nucleus search (rowcore.cuh).  A row job ends with
-// its statistics and the probability of the drafted token in global memory; the
-// second row of a (sequence, position) pair to finish evaluates the accept
-// test and, on a rejection, draws the replacement token from the residual with
-// its own row still in registers and the partner row re-read through L2; the
-// last position of a sequence to finish scans the accept bits.
-// HBM traffic: every logit once, plus one noise row per rejected / bonus position.
+// row j, ..., bonus target row of every sequence).  Rows arrive through a ring
+// of 16 KB shared-memory chunks filled by TMA bulk copies that one elected
+// thread keeps issuing ahead of the consumers, and are pulled into registers -
+// one float4 per thread per chunk, a whole <=32768-entry row in 32 registers
+// per thread.  Everything after that is register arithmetic plus a handful of
+// block reductions:
+//
+//   max -> e_i = 2^(x_i*log2e - max*log2e) -> Z                (softmax statistics)
+//   nucleus (top-p): a threshold search on the register-resident e_i - each
+//     pass sums the mass at or above three candidate thresholds (2 instructions
+//     per entry and threshold, no shared-memory atomics), brackets the boundary
+//     by interpolation, and stops when the bracket provably holds <= 128
+//     entries; those few are ordered exactly like the reference's sort (scaled
+//     logit descending, lowest index first) by an all-pairs rank in shared
+//     memory, which yields the last kept entry and the kept mass Z'.
+//
+// A row job ends with a 32-byte record (max, Z', keep rule, probability of the
+// drafted token) in global memory.  The second row of a (sequence, position)
+// pair to finish evaluates the accept test; the last row of a sequence to finish
+// scans the accept bits and its block draws the ONE token the sequence needs
+// (residual resample at the first rejection, or the bonus sample) by re-reading
+// the two rows through L2 and the sequence's noise row from HBM.
+// HBM traffic: every logit once, plus one noise row per sequence.
+//
+// Reference semantics restated (file:line under /root/reference):
+//   logits / T -> top-p filter -> softmax                src/utils.py:650-709
+//   accept test r <= p/q, leading run                   src/decoding_ops.py:127-147
+//   residual resample sample(max_fn(p - q))             src/decoding_ops.py:190-206, src/utils.py:787-810
+//   bonus sample sample(p_next)                         src/decoding_ops.py:209-220, src/utils.py:727-748
 #pragma once
 
 #include "stream_common.cuh"
 
 namespace duodec {
 
-struct RowRecord {  // 32 bytes per row job, written once, read by the partner
-  float m, Z;
-  unsigned hi_bits;  // e bits >  hi_bits -> kept
-  unsigned lo_bits;  // e bits <= lo_bits -> dropped; in between: the boundary rule
-  float xstar;       // boundary entry (scaled logit, index): kept iff before-or-at it in
-  int istar;         //   (logit descending, index ascending) order; mode 1: index rule only
-  int mode;          // 0: order by scaled logit, 1: all in-between entries share one e (bisection path)
-  float sel;         // probability of the drafted token of this position
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr int kCandMax = 256;        // entries the all-pairs finish can order
+constexpr float kCandGoal = 128.0f;  // the search stops once the bracket holds at most this many
+constexpr int kSearchPasses = 12;
+
+struct RowRecord {  // 32 bytes per row job, written once, read by the partner / the sampler
+  float mL;     // max scaled logit * log2(e)
+  float Z;      // mass of the kept entries
+  float lo;     // e <  lo -> dropped
+  float hi;     // e >= hi -> kept;  in between: the boundary rule
+  float xstar;  // boundary entry (scaled logit, index): kept iff at or before it in
+  int istar;    //   (logit descending, index ascending) order; mode 1: index rule only
+  int mode;     // 0: order by scaled logit then index, 1: all in-between entries share one e (bisection path)
+  float sel;    // probability of the drafted token of this position
 };
 
 struct StreamParams {
@@ -49,9 +71,10 @@ struct StreamParams {
   long long* token;
   unsigned char* all_accepted;
   int* counters;          // [B]           zeroed, self-cleaning
-  long long* pair_token;  // [B, gamma+1]
+  long long* pair_token;  // [B, gamma+1]  accept bit of every position
   int* pair_counters;     // [B, gamma]    zeroed, self-cleaning
   RowRecord* records;     // [B, 2*gamma+1]
+  int* stats;             // optional [32] counters (tuning hook), may be null
 };
 
 struct RowJob {
@@ -73,13 +96,36 @@ __device__ __forceinline__ const TIn* job_row(const StreamParams& P, RowJob jb) 
              : reinterpret_cast<const TIn*>(P.draft) + (long long)jb.b * P.d_sb + (long long)jb.j * P.d_ss;
 }
 
+__device__ __forceinline__ float ex2_approx(float t) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(t));
+  return y;
+}
+// e = exp(x - max) as 2^(x*log2e - max*log2e): one FFMA + one MUFU.  The rounding of max*log2e is a
+// common factor of the whole row and cancels in e / Z.
+__device__ __forceinline__ float row_exp(float x, float mL) { return ex2_approx(fmaf(x, kLog2e, -mL)); }
+
 // keep-rule of a finished row applied to a recomputed entry
 __device__ __forceinline__ float apply_record(const RowRecord& rc, float x, float e, int idx) {
-  const unsigned bits = __float_as_uint(e);
-  if (bits > rc.hi_bits) return e;
-  if (bits <= rc.lo_bits) return 0.0f;
+  if (e >= rc.hi) return e;
+  if (!(e >= rc.lo)) return 0.0f;
   if (rc.mode == 0) return (x > rc.xstar || (x == rc.xstar && idx <= rc.istar)) ? e : 0.0f;
   return idx <= rc.istar ? e : 0.0f;
+}
+
+__device__ __forceinline__ RowRecord load_record(const RowRecord* p) {
+  const uint4* src = reinterpret_cast<const uint4*>(p);
+  const uint4 a = __ldcg(src), b4 = __ldcg(src + 1);
+  RowRecord r;
+  r.mL = __uint_as_float(a.x);
+  r.Z = __uint_as_float(a.y);
+  r.lo = __uint_as_float(a.z);
+  r.hi = __uint_as_float(a.w);
+  r.xstar = __uint_as_float(b4.x);
+  r.istar = int(b4.y);
+  r.mode = int(b4.z);
+  r.sel = __uint_as_float(b4.w);
+  return r;
 }
 
 struct MassBest {
@@ -97,22 +143,40 @@ struct OpMassBest {
     return o;
   }
 };
+struct F4 {
+  float a, b, c, d;
+};
+struct OpSumF4 {
+  __device__ __forceinline__ F4 operator()(F4 x, F4 y) const { return F4{x.a + y.a, x.b + y.b, x.c + y.c, x.d + y.d}; }
+};
 
-// ---------------------------------------------------------------------------
-// register-resident row helpers
-// ---------------------------------------------------------------------------
+// scratch of the persistent block (after the ring)
+struct __align__(16) V1Scratch {
+  StreamScratch s;  // ring barriers + reduction slots
+  float cand_e[kCandMax];
+  float cand_x[kCandMax];
+  int cand_i[kCandMax];
+  float res_x;
+  int res_i;
+  float res_Z;
+  int res_ok;
+  int seq_n;        // >= 0: this block draws the token of its sequence at position seq_n
+  float warm[2];    // log2(boundary e / Z) of the last draft / target row of this block
+  int warm_ok[2];
+};
+
 __device__ __forceinline__ float& f4c(float4& v, int c) {
   return c == 0 ? v.x : (c == 1 ? v.y : (c == 2 ? v.z : v.w));
 }
 
 // slow path of the nucleus boundary on a register-resident row: bisection on
-// K = (bits(e) << 32) | ~index restricted to [klo, khi); `above` is the exact
-// mass of the entries with K >= khi.  Returns K of the last kept entry (0 when
-// nothing is cut) and the kept mass through *Zout.
+// K = (bits(e) << 32) | ~index restricted to [klo, khi); `above` is the mass of
+// the entries with K >= khi.  Returns K of the last kept entry (0 when nothing
+// is cut) and the kept mass through *Zout.
 __device__ __forceinline__ unsigned long long stream_bisect(float4 (&r)[kMaxChunks], int nchunk,
-                                                         unsigned long long klo, unsigned long long khi,
-                                                         double above, double target, StreamScratch* ss,
-                                                         int& phase, double* Zout) {
+                                                        unsigned long long klo, unsigned long long khi,
+                                                        double above, double target, StreamScratch* ss,
+                                                        int& phase, double* Zout) {
   auto F = [&](unsigned long long t) {  // mass of entries with t <= K < khi
     double acc = 0.0;
 #pragma unroll
@@ -146,7 +210,6 @@ __device__ __forceinline__ unsigned long long stream_bisect(float4 (&r)[kMaxChun
   return lo;
 }
 
-
 template <class TIn>
 __device__ __forceinline__ float4 load4_scaled(const TIn* __restrict__ p, float temperature) {
   float4 v;
@@ -159,21 +222,262 @@ __device__ __forceinline__ float4 load4_scaled(const TIn* __restrict__ p, float 
     v.z = __uint_as_float(u.y << 16);
     v.w = __uint_as_float(u.y & 0xffff0000u);
   }
-  v.x = scale_logit(v.x, temperature);
-  v.y = scale_logit(v.y, temperature);
-  v.z = scale_logit(v.z, temperature);
-  v.w = scale_logit(v.w, temperature);
+  if (temperature != 1.0f) {
+    v.x = __fdiv_rn(v.x, temperature);
+    v.y = __fdiv_rn(v.y, temperature);
+    v.z = __fdiv_rn(v.z, temperature);
+    v.w = __fdiv_rn(v.w, temperature);
+  }
   return v;
+}
+
+// mass of the register-resident row at or above three thresholds (t1 <= t2 <= t3)
+__device__ __forceinline__ F4 mass_above3(const float4 (&r)[kMaxChunks], int nchunk, float t1, float t2, float t3) {
+  float a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;
+#pragma unroll
+  for (int c = 0; c < kMaxChunks; ++c) {
+    if (c < nchunk) {
+      const float e[4] = {r[c].x, r[c].y, r[c].z, r[c].w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        if (e[k] >= t1) a1 += e[k];
+        if (e[k] >= t2) a2 += e[k];
+        if (e[k] >= t3) a3 += e[k];
+      }
+    }
+  }
+  return F4{a1, a2, a3, 0.0f};
+}
+
+// ---------------------------------------------------------------------------
+// nucleus boundary of a register-resident row (e values), see the file header.
+// On return rec.{Z, lo, hi, xstar, istar, mode} describe the keep rule.
+// ---------------------------------------------------------------------------
+template <class TIn>
+__device__ __forceinline__ void nucleus_search(float4 (&r)[kMaxChunks], int nchunk, const TIn* row, float temp,
+                                               float top_p, float Zall, int kind, V1Scratch* vs, int& phase,
+                                               RowRecord& rec, int* stats) {
+  StreamScratch* ss = &vs->s;
+  const int tid = threadIdx.x;
+  const double target = double(top_p) * double(Zall);
+  if (!(target < double(Zall))) return;  // top_p >= 1: nothing is cut (rec keeps lo = hi = 0)
+
+  // bracket in e-space: G(e >= lo) > target >= G(e >= hi); u = log2 of the thresholds
+  float lo = 0.0f, hi = 2.0f, Glo = Zall, Ghi = 0.0f;
+  float ulo = -160.0f, uhi = 1.0f;
+  bool have_lo = false, have_hi = false;
+  const float lgZ = __log2f(Zall);
+  const bool warm = vs->warm_ok[kind] != 0;
+  const float uwarm = vs->warm[kind] + lgZ;
+  if (tid == 0) vs->s.ncand = 0;
+  int npass = 0;
+
+#pragma unroll 1
+  for (int pass = 0; pass < kSearchPasses; ++pass) {
+    if (have_lo && (Glo - Ghi) <= kCandGoal * lo) break;
+    npass = pass + 1;
+    float u1, u2, u3;
+    if (pass == 0) {
+      if (warm) {
+        u1 = uwarm - 0.25f, u2 = uwarm, u3 = uwarm + 0.25f;
+      } else {
+        u1 = -12.0f, u2 = -8.0f, u3 = -4.0f;
+      }
+    } else if (!have_lo) {  // everything tried so far was too high: walk down
+      const float top = have_hi ? uhi : 0.0f;
+      u1 = top - 14.0f, u2 = top - 6.0f, u3 = top - 2.0f;
+    } else if (!have_hi) {  // everything tried so far was too low: walk up towards e = 1
+      u1 = 0.75f * ulo, u2 = 0.5f * ulo, u3 = 0.25f * ulo;
+    } else {
+      const float w = uhi - ulo;
+      const float c = ulo + w * __fdividef(Glo - float(target), Glo - Ghi);
+      const float d = 0.125f * w;
+      const float a = ulo + 0.02f * w, b = uhi - 0.02f * w;
+      u1 = fminf(fmaxf(c - d, a), b);
+      u2 = fminf(fmaxf(c, a), b);
+      u3 = fminf(fmaxf(c + d, a), b);
+    }
+    u1 = fminf(fmaxf(u1, -150.0f), 0.5f);
+    u2 = fminf(fmaxf(u2, -150.0f), 0.5f);
+    u3 = fminf(fmaxf(u3, -150.0f), 0.5f);
+    const float t1 = ex2_approx(u1), t2 = ex2_approx(u2), t3 = ex2_approx(u3);
+    const F4 g = sblock_allreduce(mass_above3(r, nchunk, t1, t2, t3), OpSumF4(), ss, phase);
+    const float old_lo = lo, old_hi = hi;
+    // ascending thresholds: the largest one still above the target raises lo, the smallest one not above lowers hi
+    const float tt[3] = {t1, t2, t3}, uu[3] = {u1, u2, u3}, gg[3] = {g.a, g.b, g.c};
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      if (double(gg[k]) > target) {
+        if (tt[k] > lo) lo = tt[k], ulo = uu[k], Glo = gg[k], have_lo = true;
+      } else {
+        if (tt[k] < hi) hi = tt[k], uhi = uu[k], Ghi = gg[k], have_hi = true;
+      }
+    }
+    if (pass > 0 && lo == old_lo && hi == old_hi) break;  // float resolution reached: no progress possible
+  }
+
+  bool solved = false;
+  if (have_lo && (Glo - Ghi) <= kCandGoal * lo) {
+    // ---- collect the bracket [lo, hi) and order it exactly like the reference's sort
+#pragma unroll
+    for (int c = 0; c < kMaxChunks; ++c) {
+      if (c < nchunk) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const float e = f4c(r[c], k);
+          if (e >= lo && e < hi) {
+            const int idx = c * kChunk + 4 * tid + k;
+            const int pos = atomicAdd(&vs->s.ncand, 1);
+            if (pos < kCandMax) {
+              vs->cand_e[pos] = e;
+              vs->cand_i[pos] = idx;
+              vs->cand_x[pos] = scale_logit(to_f32(row[idx]), temp);
+            }
+          }
+        }
+      }
+    }
+    if (tid == 0) vs->res_ok = 0;
+    __syncthreads();
+    const int n = vs->s.ncand;
+    if (n <= kCandMax) {
+      int Pn = 32;
+      while (Pn < n) Pn <<= 1;
+      const int parts = kST / Pn;  // 4..32 threads share one candidate (same warp)
+      const int t = tid / parts, part = tid - t * parts;
+      double cum = 0.0;
+      float ex = 0.0f, xx = 0.0f;
+      int ii = 0;
+      if (t < n) {
+        ex = vs->cand_e[t], xx = vs->cand_x[t], ii = vs->cand_i[t];
+        for (int j = part; j < n; j += parts) {
+          const float xj = vs->cand_x[j];
+          const int ij = vs->cand_i[j];
+          if (xj > xx || (xj == xx && ij <= ii)) cum += double(vs->cand_e[j]);
+        }
+      }
+      for (int o = parts >> 1; o > 0; o >>= 1) cum += __shfl_xor_sync(0xffffffffu, cum, o);
+      const double incl = double(Ghi) + cum;
+      if (t < n && part == 0 && incl > target && !(incl - double(ex) > target)) {
+        vs->res_x = xx;
+        vs->res_i = ii;
+        vs->res_Z = float(incl);
+        vs->res_ok = 1;
+      }
+      __syncthreads();
+      if (vs->res_ok) {
+        solved = true;
+        rec.Z = vs->res_Z;
+        rec.lo = lo;
+        rec.hi = hi;
+        rec.xstar = vs->res_x;
+        rec.istar = vs->res_i;
+        rec.mode = 0;
+      }
+    }
+  }
+  if (!solved) {
+    // slow path: exact bisection on (e, index) keys inside the bracket found so far
+    unsigned long long klo = have_lo ? (unsigned long long)__float_as_uint(lo) << 32 : 0ull;
+    unsigned long long khi = (unsigned long long)__float_as_uint(hi) << 32;
+    double Zk = 0.0;
+    unsigned long long kstar = 0ull;
+#pragma unroll 1
+    for (int attempt = 0; attempt < 2 && kstar == 0ull; ++attempt) {
+      // second attempt: the bracket was inconsistent (rounding), redo on the full range
+      const unsigned long long a = attempt == 0 ? klo : 0ull;
+      const unsigned long long b = attempt == 0 ? khi : (unsigned long long)__float_as_uint(2.0f) << 32;
+      kstar = stream_bisect(r, nchunk, a, b, attempt == 0 ? double(Ghi) : 0.0, target, ss, phase, &Zk);
+    }
+    rec.Z = float(Zk);
+    if (kstar != 0ull) {
+      const float estar = __uint_as_float(unsigned(kstar >> 32));
+      rec.mode = 1;
+      rec.lo = estar;
+      rec.hi = __uint_as_float(unsigned(kstar >> 32) + 1u);
+      rec.istar = int(0xffffffffu - unsigned(kstar & 0xffffffffull));
+      lo = estar;
+    }
+  }
+  if (stats && tid == 0) {
+    atomicAdd(&stats[npass < 15 ? npass : 15], 1);          // [0..15] search passes per row
+    atomicAdd(&stats[solved ? 16 : 17], 1);                  // fast finish / bisection path
+    if (solved) atomicAdd(&stats[18], vs->s.ncand);          // candidates ordered
+  }
+  if (tid == 0 && lo > 0.0f) {
+    vs->warm[kind] = __log2f(lo) - lgZ;
+    vs->warm_ok[kind] = 1;
+  }
+  __syncthreads();  // candidate area and result slots are free for the next row
+}
+
+// ---------------------------------------------------------------------------
+// the one token a sequence needs: residual resample at position n (< gamma) or
+// the bonus sample (n == gamma).  Rows are re-read through L2, noise from HBM.
+// ---------------------------------------------------------------------------
+template <class TIn>
+__device__ __forceinline__ long long sample_sequence(const StreamParams& P, int b, int n, V1Scratch* vs, int& phase) {
+  StreamScratch* ss = &vs->s;
+  const int tid = threadIdx.x;
+  const int gamma = P.gamma, V = P.V;
+  const int nchunk = (V + kChunk - 1) / kChunk;
+  const bool bonus = (n == gamma);
+  const int base = b * (2 * gamma + 1);
+  const RowRecord rp = load_record(&P.records[base + (bonus ? 2 * gamma : 2 * n + 1)]);
+  const RowRecord rq = bonus ? rp : load_record(&P.records[base + 2 * n]);
+  const TIn* prow = job_row<TIn>(P, RowJob{b, n, 1});
+  const TIn* qrow = bonus ? prow : job_row<TIn>(P, RowJob{b, n, 0});
+  const float* nz = P.noise + (long long)b * P.noise_sb;
+  const float invZp = __frcp_rn(rp.Z), invZq = __frcp_rn(rq.Z);
+  MassBest mb{0.0f, -1.0f, 0x7fffffff};
+  ValIdx bd{-INFINITY, 0x7fffffff};
+#pragma unroll 2
+  for (int c = 0; c < nchunk; ++c) {
+    const int i0 = c * kChunk + 4 * tid;
+    if (i0 < V) {
+      float4 xp = load4_scaled<TIn>(prow + i0, P.t_temp);
+      float4 xq = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (!bonus) xq = load4_scaled<TIn>(qrow + i0, P.d_temp);
+      const float4 nv = __ldg(reinterpret_cast<const float4*>(nz + i0));
+      const float nn[4] = {nv.x, nv.y, nv.z, nv.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float x = f4c(xp, k);
+        float d = apply_record(rp, x, row_exp(x, rp.mL), i0 + k) * invZp;
+        if (!bonus) {
+          const float y = f4c(xq, k);
+          d -= apply_record(rq, y, row_exp(y, rq.mL), i0 + k) * invZq;
+        }
+        if (d > 0.0f) {
+          mb.mass += d;
+          const float key = __fdividef(d, nn[k]);
+          if (key > mb.key || (key == mb.key && i0 + k < mb.idx)) {
+            mb.key = key;
+            mb.idx = i0 + k;
+          }
+        }
+        const float dz = (d == d && fabsf(d) != INFINITY) ? d : 0.0f;
+        if (dz > bd.v || (dz == bd.v && i0 + k < bd.i)) bd = ValIdx{dz, i0 + k};
+      }
+    }
+  }
+  mb = sblock_allreduce(mb, OpMassBest(), ss, phase);
+  long long cand;
+  if (mb.mass > 0.0f) {
+    cand = mb.idx == 0x7fffffff ? 0 : mb.idx;
+  } else {
+    bd = sblock_allreduce(bd, OpArgMax(), ss, phase);  // zero mass: first argmax of p - q (src/utils.py:799-806)
+    cand = bd.i == 0x7fffffff ? 0 : bd.i;
+  }
+  return cand;
 }
 
 template <class TIn>
 __global__ void __launch_bounds__(kST, 1) verify_stream_kernel(const __grid_constant__ StreamParams P) {
   extern __shared__ __align__(128) unsigned char smem[];
   unsigned char* ring = smem;
-  unsigned* cnt = reinterpret_cast<unsigned*>(smem + kSlots * kSlotBytes);
-  unsigned* low = cnt + kHistBins;
-  BandWork* bw = reinterpret_cast<BandWork*>(cnt);
-  StreamScratch* ss = reinterpret_cast<StreamScratch*>(smem + kSlots * kSlotBytes + kHistBytes);
+  V1Scratch* vs = reinterpret_cast<V1Scratch*>(smem + kSlots * kSlotBytes);
+  StreamScratch* ss = &vs->s;
 
   const int tid = threadIdx.x;
   const int gamma = P.gamma;
@@ -185,6 +489,7 @@ __global__ void __launch_bounds__(kST, 1) verify_stream_kernel(const __grid_cons
   if (tid == 0) {
     for (int s = 0; s < kSlots; ++s) mbar_init(&ss->full[s], 1);
     mbar_fence_init();
+    vs->warm_ok[0] = vs->warm_ok[1] = 0;
   }
   __syncthreads();
   int phase = 0;
@@ -215,17 +520,6 @@ __global__ void __launch_bounds__(kST, 1) verify_stream_kernel(const __grid_cons
     const TIn* row = job_row<TIn>(P, jb);
     const float temp = jb.is_target ? P.t_temp : P.d_temp;
     const float top_p = jb.is_target ? P.t_top_p : P.d_top_p;
-    const bool nucleus = top_p > 0.0f;
-
-    // the histogram is cleared while the row is still landing
-    if (nucleus)
-      for (int i = tid; i < 2 * kHistBins; i += kST) cnt[i] = 0u;
-    if (tid == 0) {
-      ss->bstar = kHistBins;
-      ss->ncand = 0;
-      ss->jstar = 0x7fffffff;
-      ss->overflow = 0;
-    }
 
     // ---- pull the row out of the ring into registers (scaled logits)
     float4 r[kMaxChunks];
@@ -248,10 +542,12 @@ __global__ void __launch_bounds__(kST, 1) verify_stream_kernel(const __grid_cons
             v.z = __uint_as_float(u.y << 16);
             v.w = __uint_as_float(u.y & 0xffff0000u);
           }
-          v.x = scale_logit(v.x, temp);
-          v.y = scale_logit(v.y, temp);
-          v.z = scale_logit(v.z, temp);
-          v.w = scale_logit(v.w, temp);
+          if (temp != 1.0f) {
+            v.x = __fdiv_rn(v.x, temp);
+            v.y = __fdiv_rn(v.y, temp);
+            v.z = __fdiv_rn(v.z, temp);
+            v.w = __fdiv_rn(v.w, temp);
+          }
         }
         mx = fmaxf(mx, fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w)));
       }
@@ -261,206 +557,36 @@ __global__ void __launch_bounds__(kST, 1) verify_stream_kernel(const __grid_cons
     const float m = sblock_allreduce(mx, OpMaxF(), ss, phase);  // its barrier also frees the ring slots
     if (tid == 0) produce();
 
-    // ---- pass 2: e = exp(x - m) in registers; Z or the exact-mass histogram
+    // ---- e = exp(x - m) in registers, Z
+    const float mL = m * kLog2e;
     float z = 0.0f;
 #pragma unroll
     for (int c = 0; c < kMaxChunks; ++c) {
       if (c < nchunk) {
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          float& x = f4c(r[c], k);
-          const float ex = expf(__fsub_rn(x, m));
-          x = ex;
-          if (nucleus) {
-            const unsigned d = kOneBits - __float_as_uint(ex);
-            const unsigned b = d >> kBinShift;
-            if (b < unsigned(kHistBins)) {
-              atomicAdd(&cnt[b], 1u);
-              atomicAdd(&low[b], d & 0xffffu);
-            } else {
-              z += ex;
-            }
-          } else {
-            z += ex;
-          }
-        }
+        r[c].x = row_exp(r[c].x, mL);
+        r[c].y = row_exp(r[c].y, mL);
+        r[c].z = row_exp(r[c].z, mL);
+        r[c].w = row_exp(r[c].w, mL);
+        z += (r[c].x + r[c].y) + (r[c].z + r[c].w);
       }
     }
-    const float zsum = sblock_allreduce(z, OpSumF(), ss, phase);  // barrier: histogram complete
+    const float Zall = sblock_allreduce(z, OpSumF(), ss, phase);
 
     RowRecord rec;
-    rec.m = m;
-    rec.Z = zsum;
-    rec.hi_bits = 0u;
-    rec.lo_bits = 0u;
+    rec.mL = mL;
+    rec.Z = Zall;
+    rec.lo = 0.0f;
+    rec.hi = 0.0f;
     rec.xstar = -INFINITY;
     rec.istar = 0x7fffffff;
     rec.mode = 0;
     rec.sel = 0.0f;
+    if (top_p > 0.0f) nucleus_search<TIn>(r, nchunk, row, temp, top_p, Zall, jb.is_target, vs, phase, rec, P.stats);
 
-    if (nucleus) {
-      // exact bin masses -> boundary bin (4 bins per thread, ascending bin = descending e)
-      constexpr int kPer = kHistBins / kST;
-      const int b0 = tid * kPer;
-      double loc = 0.0;
-      bool big = false;
-#pragma unroll
-      for (int i = 0; i < kPer; ++i) {
-        const unsigned c = cnt[b0 + i];
-        big |= (c > 65535u);
-        loc += bin_mass(b0 + i, c, low[b0 + i]);
-      }
-      double total = 0.0;
-      const double run0 = sblock_exscan(loc, OpSumD(), 0.0, ss, phase, &total);
-      const double Z1 = total + double(zsum);
-      const double target = double(top_p) * Z1;
-      if (big) ss->overflow = 1;
-      {
-        int mine = kHistBins;
-        double run = run0;
-#pragma unroll
-        for (int i = 0; i < kPer; ++i) {
-          run += bin_mass(b0 + i, cnt[b0 + i], low[b0 + i]);
-          if (run > target && mine == kHistBins) mine = b0 + i;
-        }
-        if (mine < kHistBins) atomicMin(&ss->bstar, mine);
-      }
-      __syncthreads();
-      const int bstar = ss->bstar;
-      const bool have_bin = bstar < kHistBins && !ss->overflow;
-      const unsigned nb = have_bin ? cnt[bstar] : 0u;
-      if (have_bin && bstar >= b0 && bstar < b0 + kPer) {
-        double run = run0;
-        for (int i = 0; b0 + i < bstar; ++i) run += bin_mass(b0 + i, cnt[b0 + i], low[b0 + i]);
-        ss->m_above = run;
-      }
-      __syncthreads();  // m_above visible; histogram reads done before the region is reused
-      if (have_bin && nb <= unsigned(kCandCap)) {
-        const double m_above = ss->m_above;
-        // collect the entries of the boundary bin with their exact ordering keys
-#pragma unroll
-        for (int c = 0; c < kMaxChunks; ++c) {
-          if (c < nchunk) {
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              const float e = f4c(r[c], k);
-              if (int((kOneBits - __float_as_uint(e)) >> kBinShift) == bstar) {
-                const int idx = c * kChunk + 4 * tid + k;
-                const int pos = atomicAdd(&ss->ncand, 1);
-                const float x = scale_logit(to_f32(row[idx]), temp);
-                bw->key[pos] = ((unsigned long long)(~okey(x)) << 32) | (unsigned long long)unsigned(idx);
-                bw->mass[pos] = e;
-              }
-            }
-          }
-        }
-        __syncthreads();
-        const int n = ss->ncand;
-        int Pn = 32;
-        while (Pn < n) Pn <<= 1;
-        if (tid >= n && tid < Pn) {
-          bw->key[tid] = ~0ull;
-          bw->mass[tid] = 0.0f;
-        }
-        __syncthreads();
-        for (int k2 = 2; k2 <= Pn; k2 <<= 1) {
-          for (int j2 = k2 >> 1; j2 > 0; j2 >>= 1) {
-            const int t = tid, u = tid ^ j2;
-            if (t < Pn && u > t) {
-              const unsigned long long a = bw->key[t], b = bw->key[u];
-              const bool up = ((t & k2) == 0);
-              if ((a > b) == up) {
-                bw->key[t] = b;
-                bw->key[u] = a;
-                const float ma = bw->mass[t];
-                bw->mass[t] = bw->mass[u];
-                bw->mass[u] = ma;
-              }
-            }
-            __syncthreads();
-          }
-        }
-        const double mine_mass = tid < Pn ? double(bw->mass[tid]) : 0.0;
-        const double ex = sblock_exscan(mine_mass, OpSumD(), 0.0, ss, phase, static_cast<double*>(nullptr));
-        const double cum = m_above + ex + mine_mass;
-        if (tid < n && cum > target) atomicMin(&ss->jstar, tid);
-        __syncthreads();
-        const int jstar = ss->jstar;
-        const int nkeep = jstar == 0x7fffffff ? n : jstar + 1;
-        if (tid == nkeep - 1) {
-          ss->m_above = cum;
-          ss->keystar = bw->key[tid];
-        }
-        __syncthreads();
-        const unsigned long long keystar = ss->keystar;
-        rec.Z = float(ss->m_above);
-        rec.hi_bits = bin_top_bits(bstar);
-        rec.lo_bits = bin_top_bits(bstar + 1);
-        rec.xstar = okey_inv(~unsigned(keystar >> 32));
-        rec.istar = int(unsigned(keystar & 0xffffffffull));
-        // drop this thread's boundary-bin entries that come after the boundary
-#pragma unroll
-        for (int c = 0; c < kMaxChunks; ++c) {
-          if (c < nchunk) {
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              float& e = f4c(r[c], k);
-              const unsigned bits = __float_as_uint(e);
-              if (bits <= rec.lo_bits) {
-                e = 0.0f;
-              } else if (bits <= rec.hi_bits) {
-                const int idx = c * kChunk + 4 * tid + k;
-                const float x = scale_logit(to_f32(row[idx]), temp);
-                if (!(x > rec.xstar || (x == rec.xstar && idx <= rec.istar))) e = 0.0f;
-              }
-            }
-          }
-        }
-      } else {
-        // slow path: boundary below the histogram range, or a crowded boundary bin
-        unsigned long long klo = 0ull, khi = (unsigned long long)(kOneBits + 1u) << 32;
-        double above = 0.0;
-        if (have_bin) {
-          khi = (unsigned long long)(bin_top_bits(bstar) + 1u) << 32;
-          klo = (unsigned long long)(bin_top_bits(bstar + 1) + 1u) << 32;
-          above = ss->m_above;
-        }
-        double Zk = 0.0;
-        unsigned long long kstar = stream_bisect(r, nchunk, klo, khi, above, target, ss, phase, &Zk);
-        if (kstar == 0ull && have_bin) {
-          // nothing inside the bin crosses the target: the cut is below it (cannot
-          // happen when the bin was located exactly); redo on the full range
-          kstar = stream_bisect(r, nchunk, 0ull, (unsigned long long)(kOneBits + 1u) << 32, 0.0, target, ss,
-                                phase, &Zk);
-        }
-        rec.Z = float(Zk);
-        if (kstar != 0ull) {
-          rec.mode = 1;
-          rec.hi_bits = unsigned(kstar >> 32);
-          rec.lo_bits = rec.hi_bits - 1u;
-          rec.istar = int(0xffffffffu - unsigned(kstar & 0xffffffffull));
-#pragma unroll
-          for (int c = 0; c < kMaxChunks; ++c) {
-            if (c < nchunk) {
-#pragma unroll
-              for (int k = 0; k < 4; ++k) {
-                float& e = f4c(r[c], k);
-                const unsigned idx = unsigned(c * kChunk + 4 * tid + k);
-                const unsigned long long K = ((unsigned long long)__float_as_uint(e) << 32) | (0xffffffffu - idx);
-                if (K < kstar) e = 0.0f;
-              }
-            }
-          }
-        }
-      }
-    }
-    __syncthreads();  // the work region and the scratch flags are free for the next use
-
-    // ---- publish the row, resolve the position / the sequence
+    // ---- publish the row; resolve the position / the sequence
     const long long tok = jb.j < gamma ? P.tokens[(long long)jb.b * P.tok_sb + jb.j] : -1;
     const bool tok_ok = tok >= 0 && tok < V;
     const int owner = tok_ok ? int((tok & (kChunk - 1)) >> 2) : 0;
-    const float* nz = P.noise + (long long)jb.b * P.noise_sb;
     if (tid == owner) {
       if (tok_ok) {
         const int tc = int(tok >> 12), tk = int(tok & 3);
@@ -468,132 +594,55 @@ __global__ void __launch_bounds__(kST, 1) verify_stream_kernel(const __grid_cons
 #pragma unroll
         for (int c = 0; c < kMaxChunks; ++c)
           if (c == tc) e = f4c(r[c], tk);
+        if (e < rec.hi && e >= rec.lo)  // inside the boundary bracket: the exact order decides
+          e = apply_record(rec, scale_logit(to_f32(row[tok]), temp), e, int(tok));
+        else if (!(e >= rec.hi))
+          e = 0.0f;
         rec.sel = __fdiv_rn(e, rec.Z);
       }
-      int old = 0;
+      P.records[job] = rec;
+      __threadfence();
+      int seq_n = -1;
+      bool arrive = true;
       if (jb.j < gamma) {
-        P.records[job] = rec;
-        __threadfence();
-        old = atomicAdd(&P.pair_counters[jb.b * gamma + jb.j], 1);
-        __threadfence();
+        const long long o = (long long)jb.b * gamma + jb.j;
+        const int old = atomicAdd(&P.pair_counters[o], 1);
+        arrive = (old == 1);
+        if (arrive) {  // second row of the pair: accept test  r <= p / q
+          __threadfence();
+          const RowRecord pr = load_record(&P.records[jb.is_target ? job - 1 : job + 1]);
+          const float selp = jb.is_target ? rec.sel : pr.sel;
+          const float selq = jb.is_target ? pr.sel : rec.sel;
+          const int accept = P.r[(long long)jb.b * P.r_sb + jb.j] <= __fdiv_rn(selp, selq);
+          P.accept_mask[o] = (unsigned char)accept;
+          P.sel_p[o] = selp;
+          P.sel_q[o] = selq;
+          P.pair_counters[o] = 0;
+          P.pair_token[(long long)jb.b * (gamma + 1) + jb.j] = accept;
+        }
       }
-      ss->flag = old;
+      if (arrive) {
+        __threadfence();
+        const int done = atomicAdd(&P.counters[jb.b], 1);
+        if (done == gamma) {  // last position of the sequence: leading run of accepts
+          __threadfence();
+          const volatile long long* pt = P.pair_token + (long long)jb.b * (gamma + 1);
+          int a = 0;
+          while (a < gamma && pt[a] != 0) ++a;
+          seq_n = a;
+          P.counters[jb.b] = 0;
+        }
+      }
+      vs->seq_n = seq_n;
     }
     __syncthreads();
-    const bool second = (jb.j < gamma) && (ss->flag == 1);
-    const bool bonus = (jb.j == gamma);
-    if (second || bonus) {
-      long long cand = -1;
-      int accept = 0;
-      float sel_mine = 0.0f, sel_other = 0.0f;
-      if (bonus) {
-        // bonus token: argmax_i p_i / noise_i
-        ValIdx best{-1.0f, 0x7fffffff};
-#pragma unroll
-        for (int c = 0; c < kMaxChunks; ++c) {
-          if (c < nchunk && c * kChunk + 4 * tid < V) {
-            const float4 nv = __ldg(reinterpret_cast<const float4*>(nz + c * kChunk + 4 * tid));
-            const float nn[4] = {nv.x, nv.y, nv.z, nv.w};
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              const float p = __fdiv_rn(f4c(r[c], k), rec.Z);
-              if (p > 0.0f) {
-                const int idx = c * kChunk + 4 * tid + k;
-                const float key = __fdiv_rn(p, nn[k]);
-                if (key > best.v || (key == best.v && idx < best.i)) best = ValIdx{key, idx};
-              }
-            }
-          }
-        }
-        best = sblock_allreduce(best, OpArgMax(), ss, phase);
-        cand = best.i == 0x7fffffff ? 0 : best.i;
-      } else {
-        const int pjob = jb.is_target ? job - 1 : job + 1;
-        RowRecord pr;
-        {
-          const uint4* src = reinterpret_cast<const uint4*>(&P.records[pjob]);
-          const uint4 a = __ldcg(src), b4 = __ldcg(src + 1);
-          pr.m = __uint_as_float(a.x);
-          pr.Z = __uint_as_float(a.y);
-          pr.hi_bits = a.z;
-          pr.lo_bits = a.w;
-          pr.xstar = __uint_as_float(b4.x);
-          pr.istar = int(b4.y);
-          pr.mode = int(b4.z);
-          pr.sel = __uint_as_float(b4.w);
-        }
-        // every thread needs sel of this row: broadcast it from the owner through the record
-        const float my_sel = __uint_as_float(__ldcg(reinterpret_cast<const unsigned*>(&P.records[job].sel)));
-        sel_mine = my_sel;
-        sel_other = pr.sel;
-        const float selp = jb.is_target ? sel_mine : sel_other;
-        const float selq = jb.is_target ? sel_other : sel_mine;
-        accept = P.r[(long long)jb.b * P.r_sb + jb.j] <= __fdiv_rn(selp, selq);
-        if (!accept) {
-          // residual resample: sample(max_fn(p - q)); this row from registers, the partner through L2
-          const RowJob oj = decode_job(pjob, gamma);
-          const TIn* orow = job_row<TIn>(P, oj);
-          const float otemp = oj.is_target ? P.t_temp : P.d_temp;
-          MassBest mb{0.0f, -1.0f, 0x7fffffff};
-          ValIdx bd{-INFINITY, 0x7fffffff};
-#pragma unroll
-          for (int c = 0; c < kMaxChunks; ++c) {
-            if (c < nchunk && c * kChunk + 4 * tid < V) {
-              const int i0 = c * kChunk + 4 * tid;
-              float4 ov = load4_scaled<TIn>(orow + i0, otemp);
-              const float4 nv = __ldg(reinterpret_cast<const float4*>(nz + i0));
-              const float nn[4] = {nv.x, nv.y, nv.z, nv.w};
-#pragma unroll
-              for (int k = 0; k < 4; ++k) {
-                const float xo = f4c(ov, k);
-                const float eo = apply_record(pr, xo, expf(__fsub_rn(xo, pr.m)), i0 + k);
-                const float po = __fdiv_rn(eo, pr.Z);
-                const float pm = __fdiv_rn(f4c(r[c], k), rec.Z);
-                const float d = jb.is_target ? __fsub_rn(pm, po) : __fsub_rn(po, pm);
-                if (d > 0.0f) {
-                  mb.mass += d;
-                  const float key = __fdiv_rn(d, nn[k]);
-                  if (key > mb.key || (key == mb.key && i0 + k < mb.idx)) {
-                    mb.key = key;
-                    mb.idx = i0 + k;
-                  }
-                }
-                const float dz = (d == d && d != INFINITY && d != -INFINITY) ? d : 0.0f;
-                if (dz > bd.v || (dz == bd.v && i0 + k < bd.i)) bd = ValIdx{dz, i0 + k};
-              }
-            }
-          }
-          mb = sblock_allreduce(mb, OpMassBest(), ss, phase);
-          if (mb.mass > 0.0f) {
-            cand = mb.idx == 0x7fffffff ? 0 : mb.idx;
-          } else {
-            bd = sblock_allreduce(bd, OpArgMax(), ss, phase);  // zero mass: first argmax of p - q
-            cand = bd.i == 0x7fffffff ? 0 : bd.i;
-          }
-        }
-      }
+    const int seq_n = vs->seq_n;
+    if (seq_n >= 0) {
+      const long long cand = sample_sequence<TIn>(P, jb.b, seq_n, vs, phase);
       if (tid == 0) {
-        const int b = jb.b;
-        volatile long long* pt = P.pair_token + (long long)b * (gamma + 1);
-        if (!bonus) {
-          const long long o = (long long)b * gamma + jb.j;
-          P.accept_mask[o] = (unsigned char)accept;
-          P.sel_p[o] = jb.is_target ? sel_mine : sel_other;
-          P.sel_q[o] = jb.is_target ? sel_other : sel_mine;
-          P.pair_counters[o] = 0;
-        }
-        pt[jb.j] = (bonus || !accept) ? cand : -1;
-        __threadfence();
-        const int done = atomicAdd(&P.counters[b], 1);
-        if (done == gamma) {
-          __threadfence();
-          int a = 0;
-          while (a < gamma && pt[a] < 0) ++a;
-          P.accepted_len[b] = a;
-          P.token[b] = pt[a];
-          P.all_accepted[b] = (unsigned char)(a == gamma);
-          P.counters[b] = 0;
-        }
+        P.accepted_len[jb.b] = seq_n;
+        P.token[jb.b] = cand;
+        P.all_accepted[jb.b] = (unsigned char)(seq_n == gamma);
       }
     }
   }

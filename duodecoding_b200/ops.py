@@ -60,6 +60,13 @@ def set_stream_path(enabled: bool) -> None:
     lib.duodec_set_stream_path(1 if enabled else 0)
 
 
+def set_stats_buffer(buf: Optional[torch.Tensor]) -> None:
+    """Tuning hook: int32[32] CUDA tensor the row-stream kernel counts into (None disables)."""
+    if buf is not None and (not buf.is_cuda or buf.dtype != torch.int32 or buf.numel() < 32):
+        raise TypeError("stats buffer must be a CUDA int32 tensor with >= 32 entries")
+    lib.duodec_set_stats_buffer(buf.data_ptr() if buf is not None else None)
+
+
 def team_size(V: int, rows_resident: int = 1) -> int:
     return int(lib.duodec_team_size(int(V), int(rows_resident)))
 

@@ -51,6 +51,11 @@ void duodec_set_team_size(int team);
  * team kernel.  0 forces the general kernel (test hook); default 1. */
 void duodec_set_stream_path(int enabled);
 
+/* Tuning hook: device int[32] that the row-stream kernel increments (0..15: rows by number of
+ * nucleus search passes, 16: rows finished by the candidate ordering, 17: rows finished by the
+ * bisection path, 18: candidates ordered).  NULL (default) disables it. */
+void duodec_set_stats_buffer(int* device_counters);
+
 /* ---- logits -> probabilities --------------------------------------------
  * Replaces utils.norm_logits + utils.top_k_top_p_filter
  * (/root/reference/src/utils.py:650-709).
