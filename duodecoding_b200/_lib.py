@@ -10,7 +10,7 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libduodec.so")
+LIB_PATH = os.environ.get("DUODEC_LIB") or os.path.join(_HERE, "libduodec.so")  # env: tuning builds only
 
 F32 = 0
 BF16 = 1

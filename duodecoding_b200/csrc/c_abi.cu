@@ -9,7 +9,7 @@
 #include "../../include/duodec.h"
 #include "prob_kernels.cuh"
 #include "row_kernels.cuh"
-#include "stream_kernel.cuh"
+#include "stream_launch.h"
 #include "verify_kernels.cuh"
 
 using namespace duodec;
@@ -41,7 +41,7 @@ int pick_team(int V, int rows_resident) {
 }
 
 // cudaFuncSetAttribute is per (kernel, device): remember the pairs already set up.
-cudaError_t ensure_smem(const void* kernel) {
+cudaError_t ensure_smem(const void* kernel, size_t bytes = kMaxDynSmem) {
   static std::mutex mu;
   static std::vector<std::pair<const void*, int>> done;
   int dev = 0;
@@ -50,7 +50,7 @@ cudaError_t ensure_smem(const void* kernel) {
   std::lock_guard<std::mutex> lk(mu);
   for (const auto& d : done)
     if (d.first == kernel && d.second == dev) return cudaSuccess;
-  e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kMaxDynSmem));
+  e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(bytes));
   if (e != cudaSuccess) return e;
   done.emplace_back(kernel, dev);
   return cudaSuccess;
@@ -156,10 +156,9 @@ int duodec_norm_logits(const void* logits, int in_dtype, int64_t in_row_stride, 
 
 size_t duodec_verify_workspace_bytes(int B, int gamma) {
   if (B <= 0 || gamma < 0) return 0;
-  // [B] int counters (8 bytes each) + [B, gamma+1] int64 position tokens
-  // + [B, gamma] int position counters (8 bytes each) + [B, 2*gamma+1] row records
-  return size_t(B) * 8 + size_t(B) * size_t(gamma + 1) * 8 + size_t(B) * size_t(gamma) * 8 +
-         size_t(B) * size_t(2 * gamma + 1) * sizeof(RowRecord);
+  // [B] int counters (8 bytes each) + [B, gamma+1] int64 position tokens + 2 row-kind hints
+  // + [B, 2*gamma+1] row records
+  return size_t(B) * 8 + size_t(B) * size_t(gamma + 1) * 8 + stream_workspace_bytes(B, gamma);
 }
 
 int duodec_verify_fused(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss, int64_t t_sb,
@@ -178,69 +177,20 @@ int duodec_verify_fused(const void* draft, const void* target, int dtype, int64_
   if ((temperature == 0.0f) != (draft_temperature == 0.0f)) return DUODEC_EINVAL;  // greedy on both or neither
   if (workspace_bytes < duodec_verify_workspace_bytes(B, gamma)) return DUODEC_EWORKSPACE;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  {
-    // fast path: persistent row-stream kernel (rows of <= 32768 entries that TMA can move:
-    // 16-byte aligned rows and noise, equal vocabularies, no top-k, sampled temperatures)
-    const size_t elt = dtype == DUODEC_F32 ? 4 : 2;
-    auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
-    const bool ok = g_stream_path.load() != 0 && Vd == Vt && Vt <= kChunk * kMaxChunks && temperature > 0.0f &&
-                    draft_temperature > 0.0f && top_k <= 0 && draft_top_k <= 0 && (size_t(Vt) * elt) % 16 == 0 &&
-                    al16(target) && (gamma == 0 || al16(draft)) && (size_t(t_sb) * elt) % 16 == 0 &&
-                    (size_t(t_ss) * elt) % 16 == 0 && (size_t(d_sb) * elt) % 16 == 0 &&
-                    (size_t(d_ss) * elt) % 16 == 0 && al16(noise) && (noise_sb % 4) == 0;
-    if (ok) {
-      StreamParams S;
-      S.draft = draft;
-      S.target = target;
-      S.d_sb = d_sb;
-      S.d_ss = d_ss;
-      S.t_sb = t_sb;
-      S.t_ss = t_ss;
-      S.B = B;
-      S.gamma = gamma;
-      S.V = Vt;
-      S.tokens = reinterpret_cast<const long long*>(tokens);
-      S.tok_sb = tok_sb;
-      S.r = r;
-      S.r_sb = r_sb;
-      S.noise = noise;
-      S.noise_sb = noise_sb;
-      S.t_temp = temperature;
-      S.t_top_p = top_p;
-      S.d_temp = draft_temperature;
-      S.d_top_p = draft_top_p;
-      S.accept_mask = accept_mask;
-      S.sel_p = sel_target_p;
-      S.sel_q = sel_draft_p;
-      S.accepted_len = reinterpret_cast<long long*>(accepted_len);
-      S.token = reinterpret_cast<long long*>(token);
-      S.all_accepted = all_accepted;
-      char* w = reinterpret_cast<char*>(workspace);
-      S.counters = reinterpret_cast<int*>(w);
-      w += size_t(B) * 8;
-      S.pair_token = reinterpret_cast<long long*>(w);
-      w += size_t(B) * size_t(gamma + 1) * 8;
-      S.pair_counters = reinterpret_cast<int*>(w);
-      w += size_t(B) * size_t(gamma) * 8;
-      S.records = reinterpret_cast<RowRecord*>(w);
-      S.stats = g_stats.load();
-      const size_t smem = size_t(kSlots) * kSlotBytes + sizeof(V1Scratch) + 128;
-      const int njobs = B * (2 * gamma + 1);
-      int sms = sm_count();
-      if (sms <= 0) sms = 148;
-      const int grid = njobs < sms ? njobs : sms;
-      cudaError_t e;
-      if (dtype == DUODEC_F32) {
-        e = ensure_smem(reinterpret_cast<const void*>(verify_stream_kernel<float>));
-        if (e != cudaSuccess) return int(e);
-        verify_stream_kernel<float><<<grid, kST, smem, st>>>(S);
-      } else {
-        e = ensure_smem(reinterpret_cast<const void*>(verify_stream_kernel<__nv_bfloat16>));
-        if (e != cudaSuccess) return int(e);
-        verify_stream_kernel<__nv_bfloat16><<<grid, kST, smem, st>>>(S);
-      }
-      return int(cudaGetLastError());
-    }
+  if (g_stream_path.load() != 0) {
+    // fast path: persistent row-stream kernel (stream_launch.cu); falls through when the call does not qualify
+    StreamCall c;
+    c.draft = draft, c.target = target, c.dtype = dtype;
+    c.d_sb = d_sb, c.d_ss = d_ss, c.t_sb = t_sb, c.t_ss = t_ss;
+    c.B = B, c.gamma = gamma, c.Vd = Vd, c.Vt = Vt;
+    c.tokens = tokens, c.tok_sb = tok_sb, c.r = r, c.r_sb = r_sb, c.noise = noise, c.noise_sb = noise_sb;
+    c.temperature = temperature, c.top_k = top_k, c.top_p = top_p;
+    c.draft_temperature = draft_temperature, c.draft_top_k = draft_top_k, c.draft_top_p = draft_top_p;
+    c.accept_mask = accept_mask, c.sel_target_p = sel_target_p, c.sel_draft_p = sel_draft_p;
+    c.accepted_len = accepted_len, c.token = token, c.all_accepted = all_accepted;
+    c.workspace = workspace, c.stats = g_stats.load(), c.stream = st;
+    int rc = 0;
+    if (stream_try_launch(c, &rc)) return rc;
   }
   const int Vmax = Vd > Vt ? Vd : Vt;
   const int C = pick_team(Vmax, 2);

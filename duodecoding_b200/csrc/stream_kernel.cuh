@@ -1,28 +1,32 @@
 // Persistent row-stream verification kernel (the fast path of duodec_verify_fused).
 //
-// One 1024-thread block per SM walks a list of ROW jobs (draft row j, target
-// row j, ..., bonus target row of every sequence).  Rows arrive through a ring
-// of 16 KB shared-memory chunks filled by TMA bulk copies that one elected
-// thread keeps issuing ahead of the consumers, and are pulled into registers -
-// one float4 per thread per chunk, a whole <=32768-entry row in 32 registers
-// per thread.  Everything after that is register arithmetic plus a handful of
-// block reductions:
+// Two 544-thread blocks per SM walk a list of ROW jobs (draft row j, target row
+// j, ..., bonus target row of every sequence).  In each block one producer warp
+// keeps a ring of 8 KB shared-memory chunks full with TMA bulk copies
+// (full/empty mbarriers); 512 consumer threads read every chunk exactly once -
+// one float4 per thread - and keep NOTHING V-sized: a single pass yields
 //
-//   max -> e_i = 2^(x_i*log2e - max*log2e) -> Z                (softmax statistics)
-//   nucleus (top-p): a threshold search on the register-resident e_i - each
-//     pass sums the mass at or above three candidate thresholds (2 instructions
-//     per entry and threshold, no shared-memory atomics), brackets the boundary
-//     by interpolation, and stops when the bracket provably holds <= 128
-//     entries; those few are ordered exactly like the reference's sort (scaled
-//     logit descending, lowest index first) by an all-pairs rank in shared
-//     memory, which yields the last kept entry and the kept mass Z'.
+//   max, Z = sum 2^(x*log2e - M0)          (M0: max*log2e predicted from the last row of the
+//                                           same model; any value within 2^32 of the true max
+//                                           is exact enough, else the row is redone)
+//   for the nucleus (top-p): the mass at or above a predicted window [th_lo, th_hi) of scaled
+//   logits and the window's entries themselves, appended to per-thread shared-memory columns
+//   (no atomics; a small atomic overflow list catches threads that see more than 12).
 //
-// A row job ends with a 32-byte record (max, Z', keep rule, probability of the
-// drafted token) in global memory.  The second row of a (sequence, position)
-// pair to finish evaluates the accept test; the last row of a sequence to finish
-// scans the accept bits and its block draws the ONE token the sequence needs
+// If the nucleus boundary falls inside the window (the common case once the
+// prediction is warm), it is narrowed on the few window entries held in
+// registers (three thresholds per pass, interpolated) until <= 160 remain;
+// those are ordered exactly like the reference's sort (scaled logit descending,
+// lowest index first) by an all-pairs rank, giving the last kept entry
+// (xstar, istar) and the kept mass Z'.  Otherwise the window is moved and the row
+// is re-read through L2 (cold start, or a row unlike its predecessors).
+//
+// A row job ends with a 32-byte record (M0, Z', boundary, probability of the
+// drafted token) in global memory and ONE atomic on its sequence's counter; the
+// block that finishes the last row of a sequence evaluates the gamma accept
+// tests from the records, scans them, and draws the one token the sequence needs
 // (residual resample at the first rejection, or the bonus sample) by re-reading
-// the two rows through L2 and the sequence's noise row from HBM.
+// two rows through L2 and the sequence's noise row from HBM.
 // HBM traffic: every logit once, plus one noise row per sequence.
 //
 // Reference semantics restated (file:line under /root/reference):
@@ -36,20 +40,20 @@
 
 namespace duodec {
 
-constexpr float kLog2e = 1.4426950408889634f;
-constexpr int kCandMax = 256;        // entries the all-pairs finish can order
-constexpr float kCandGoal = 128.0f;  // the search stops once the bracket holds at most this many
-constexpr int kSearchPasses = 12;
-
-struct RowRecord {  // 32 bytes per row job, written once, read by the partner / the sampler
-  float mL;     // max scaled logit * log2(e)
-  float Z;      // mass of the kept entries
-  float lo;     // e <  lo -> dropped
-  float hi;     // e >= hi -> kept;  in between: the boundary rule
-  float xstar;  // boundary entry (scaled logit, index): kept iff at or before it in
-  int istar;    //   (logit descending, index ascending) order; mode 1: index rule only
-  int mode;     // 0: order by scaled logit then index, 1: all in-between entries share one e (bisection path)
+struct RowRecord {  // 32 bytes per row job, written once, read by the block that closes the sequence
+  float m0;     // exponent offset: e_i = 2^(x_i*log2e - m0)
+  float Z;      // mass of the kept entries (same scale)
+  float xstar;  // last kept entry in (scaled logit descending, index ascending) order;
+  int istar;    //   (-inf, INT_MAX) keeps everything
   float sel;    // probability of the drafted token of this position
+  int pad[3];
+};
+
+struct StreamHint {  // per row kind, lives in the workspace, survives across launches
+  float m0;
+  float theta;  // scaled logit of the last nucleus boundary
+  float dens;   // entries per unit of scaled logit around it
+  int valid;
 };
 
 struct StreamParams {
@@ -70,11 +74,10 @@ struct StreamParams {
   long long* accepted_len;
   long long* token;
   unsigned char* all_accepted;
-  int* counters;          // [B]           zeroed, self-cleaning
-  long long* pair_token;  // [B, gamma+1]  accept bit of every position
-  int* pair_counters;     // [B, gamma]    zeroed, self-cleaning
-  RowRecord* records;     // [B, 2*gamma+1]
-  int* stats;             // optional [32] counters (tuning hook), may be null
+  int* counters;       // [B]  zeroed, self-cleaning
+  StreamHint* hints;   // [2]  zeroed once (valid = 0)
+  RowRecord* records;  // [B, 2*gamma+1]
+  int* stats;          // optional [32] counters (tuning hook), may be null
 };
 
 struct RowJob {
@@ -101,31 +104,30 @@ __device__ __forceinline__ float ex2_approx(float t) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(t));
   return y;
 }
-// e = exp(x - max) as 2^(x*log2e - max*log2e): one FFMA + one MUFU.  The rounding of max*log2e is a
+// e = 2^(x*log2e - m0): one FFMA + one MUFU.  m0 is a per-row constant, so its rounding is a
 // common factor of the whole row and cancels in e / Z.
-__device__ __forceinline__ float row_exp(float x, float mL) { return ex2_approx(fmaf(x, kLog2e, -mL)); }
+__device__ __forceinline__ float row_exp(float x, float m0) { return ex2_approx(fmaf(x, kLog2e, -m0)); }
 
-// keep-rule of a finished row applied to a recomputed entry
-__device__ __forceinline__ float apply_record(const RowRecord& rc, float x, float e, int idx) {
-  if (e >= rc.hi) return e;
-  if (!(e >= rc.lo)) return 0.0f;
-  if (rc.mode == 0) return (x > rc.xstar || (x == rc.xstar && idx <= rc.istar)) ? e : 0.0f;
-  return idx <= rc.istar ? e : 0.0f;
+// keep-rule of a finished row: at or before (xstar, istar) in the reference's sort order
+__device__ __forceinline__ bool kept(const RowRecord& rc, float x, int idx) {
+  return x > rc.xstar || (x == rc.xstar && idx <= rc.istar);
 }
 
 __device__ __forceinline__ RowRecord load_record(const RowRecord* p) {
   const uint4* src = reinterpret_cast<const uint4*>(p);
   const uint4 a = __ldcg(src), b4 = __ldcg(src + 1);
   RowRecord r;
-  r.mL = __uint_as_float(a.x);
+  r.m0 = __uint_as_float(a.x);
   r.Z = __uint_as_float(a.y);
-  r.lo = __uint_as_float(a.z);
-  r.hi = __uint_as_float(a.w);
-  r.xstar = __uint_as_float(b4.x);
-  r.istar = int(b4.y);
-  r.mode = int(b4.z);
-  r.sel = __uint_as_float(b4.w);
+  r.xstar = __uint_as_float(a.z);
+  r.istar = int(a.w);
+  r.sel = __uint_as_float(b4.x);
   return r;
+}
+__device__ __forceinline__ void store_record(RowRecord* p, const RowRecord& r) {
+  uint4* dst = reinterpret_cast<uint4*>(p);
+  dst[0] = make_uint4(__float_as_uint(r.m0), __float_as_uint(r.Z), __float_as_uint(r.xstar), unsigned(r.istar));
+  dst[1] = make_uint4(__float_as_uint(r.sel), 0u, 0u, 0u);
 }
 
 struct MassBest {
@@ -143,71 +145,24 @@ struct OpMassBest {
     return o;
   }
 };
-struct F4 {
-  float a, b, c, d;
-};
-struct OpSumF4 {
-  __device__ __forceinline__ F4 operator()(F4 x, F4 y) const { return F4{x.a + y.a, x.b + y.b, x.c + y.c, x.d + y.d}; }
-};
-
-// scratch of the persistent block (after the ring)
-struct __align__(16) V1Scratch {
-  StreamScratch s;  // ring barriers + reduction slots
-  float cand_e[kCandMax];
-  float cand_x[kCandMax];
-  int cand_i[kCandMax];
-  float res_x;
-  int res_i;
-  float res_Z;
-  int res_ok;
-  int seq_n;        // >= 0: this block draws the token of its sequence at position seq_n
-  float warm[2];    // log2(boundary e / Z) of the last draft / target row of this block
-  int warm_ok[2];
-};
 
 __device__ __forceinline__ float& f4c(float4& v, int c) {
   return c == 0 ? v.x : (c == 1 ? v.y : (c == 2 ? v.z : v.w));
 }
 
-// slow path of the nucleus boundary on a register-resident row: bisection on
-// K = (bits(e) << 32) | ~index restricted to [klo, khi); `above` is the mass of
-// the entries with K >= khi.  Returns K of the last kept entry (0 when nothing
-// is cut) and the kept mass through *Zout.
-__device__ __forceinline__ unsigned long long stream_bisect(float4 (&r)[kMaxChunks], int nchunk,
-                                                        unsigned long long klo, unsigned long long khi,
-                                                        double above, double target, StreamScratch* ss,
-                                                        int& phase, double* Zout) {
-  auto F = [&](unsigned long long t) {  // mass of entries with t <= K < khi
-    double acc = 0.0;
-#pragma unroll
-    for (int c = 0; c < kMaxChunks; ++c) {
-      if (c < nchunk) {
-        float4 v = r[c];
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const float e = f4c(v, k);
-          const unsigned idx = unsigned(c * kChunk + 4 * int(threadIdx.x) + k);
-          const unsigned long long K = ((unsigned long long)__float_as_uint(e) << 32) | (0xffffffffu - idx);
-          if (K >= t && K < khi && e > 0.0f) acc += double(e);
-        }
-      }
-    }
-    return sblock_allreduce(acc, OpSumD(), ss, phase);
-  };
-  const double all = above + F(klo);
-  if (!(all > target)) {
-    *Zout = all;
-    return 0ull;
+template <class TIn>
+__device__ __forceinline__ float4 unpack4(const void* p16) {
+  float4 v;
+  if constexpr (sizeof(TIn) == 4) {
+    v = *reinterpret_cast<const float4*>(p16);
+  } else {
+    const uint2 u = *reinterpret_cast<const uint2*>(p16);
+    v.x = __uint_as_float(u.x << 16);
+    v.y = __uint_as_float(u.x & 0xffff0000u);
+    v.z = __uint_as_float(u.y << 16);
+    v.w = __uint_as_float(u.y & 0xffff0000u);
   }
-  unsigned long long lo = klo, hi = khi;
-#pragma unroll 1
-  while (hi - lo > 1ull) {
-    const unsigned long long mid = lo + ((hi - lo) >> 1);
-    if (above + F(mid) > target) lo = mid;
-    else hi = mid;
-  }
-  *Zout = above + F(lo);
-  return lo;
+  return v;
 }
 
 template <class TIn>
@@ -231,184 +186,332 @@ __device__ __forceinline__ float4 load4_scaled(const TIn* __restrict__ p, float 
   return v;
 }
 
-// mass of the register-resident row at or above three thresholds (t1 <= t2 <= t3)
-__device__ __forceinline__ F4 mass_above3(const float4 (&r)[kMaxChunks], int nchunk, float t1, float t2, float t3) {
-  float a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;
-#pragma unroll
-  for (int c = 0; c < kMaxChunks; ++c) {
-    if (c < nchunk) {
-      const float e[4] = {r[c].x, r[c].y, r[c].z, r[c].w};
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        if (e[k] >= t1) a1 += e[k];
-        if (e[k] >= t2) a2 += e[k];
-        if (e[k] >= t3) a3 += e[k];
+// ---------------------------------------------------------------------------
+// one pass over a row: statistics + the window's entries
+// ---------------------------------------------------------------------------
+struct ScanAcc {
+  float mx, z, ghi, gwin;
+  int cnt;  // window entries this thread saw (the first kColCap sit in its column, the rest in the overflow list)
+};
+
+__device__ __forceinline__ void scan_elem(float x, int idx, float m0, float lo, float hi, ScanAcc& a, float* col_x,
+                                          int* col_i, int* novf, StreamScratch* ss) {
+  const float e = row_exp(x, m0);
+  a.z += e;
+#ifdef DUODEC_BRANCHY
+  if (x >= hi) {
+    a.ghi += e;
+  } else if (x >= lo) {
+#else
+  const bool above = x >= hi;
+  if (above) a.ghi += e;
+  if (x >= lo && !above) {  // rare: a window entry
+#endif
+    a.gwin += e;
+    if (a.cnt < kColCap) {
+      col_x[a.cnt * kCT + threadIdx.x] = x;
+      col_i[a.cnt * kCT + threadIdx.x] = idx;
+    } else {
+      const int pos = atomicAdd(novf, 1);
+      if (pos < kOvfCap) {
+        ss->ovf_x[pos] = x;
+        ss->ovf_i[pos] = idx;
       }
     }
+    ++a.cnt;
   }
-  return F4{a1, a2, a3, 0.0f};
 }
 
+__device__ __forceinline__ void scan4(float4 v, int i0, float m0, float lo, float hi, ScanAcc& a, float* col_x,
+                                      int* col_i, int* novf, StreamScratch* ss) {
+  a.mx = fmaxf(a.mx, fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w)));
+  scan_elem(v.x, i0, m0, lo, hi, a, col_x, col_i, novf, ss);
+  scan_elem(v.y, i0 + 1, m0, lo, hi, a, col_x, col_i, novf, ss);
+  scan_elem(v.z, i0 + 2, m0, lo, hi, a, col_x, col_i, novf, ss);
+  scan_elem(v.w, i0 + 3, m0, lo, hi, a, col_x, col_i, novf, ss);
+}
+
+// the same pass with the row re-read through L2 (window moved, or M0 far off)
+template <class TIn>
+__device__ __noinline__ void scan_global(const TIn* row, int V, float temp, float m0, float lo, float hi,
+                                            ScanAcc& a, float* col_x, int* col_i, int* novf, StreamScratch* ss) {
+  // 2048 entries per step (one float4 per thread), four steps in flight
+  const int nstep = (V + 2047) / 2048;
+  for (int c0 = 0; c0 < nstep; c0 += 4) {
+    float4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i0 = (c0 + u) * 2048 + 4 * int(threadIdx.x);
+      if (i0 < V) v[u] = load4_scaled<TIn>(row + i0, temp);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i0 = (c0 + u) * 2048 + 4 * int(threadIdx.x);
+      if (i0 < V) scan4(v[u], i0, m0, lo, hi, a, col_x, col_i, novf, ss);
+    }
+  }
+}
+
+struct PassResult {
+  float mx, z, ghi, gwin;
+  int nwin;  // entries in the window (all threads)
+  int novf;  // of which in the overflow list (> kOvfCap: the list is incomplete)
+};
+
+// pass `pp` counts its overflow pushes in ss->novf[pp & 1]; the other counter is cleared here, before
+// the barrier, for the pass after this one (nobody touches it between the two barriers)
+__device__ __forceinline__ PassResult reduce_pass(const ScanAcc& a, int pp, StreamScratch* ss, int& phase) {
+  if (threadIdx.x == 0) {
+    ss->novf[(pp + 1) & 1] = 0;
+    ss->ncand = 0;
+  }
+  R8 r;
+  r.v[0] = a.mx;
+  r.v[1] = a.z;
+  r.v[2] = a.ghi;
+  r.v[3] = a.gwin;
+  r.v[4] = float(a.cnt);
+  r.v[5] = float(a.cnt > kColCap ? a.cnt - kColCap : 0);
+  r.v[6] = r.v[7] = 0.0f;
+  r = creduce(r, ss, phase);
+  PassResult p;
+  p.mx = r.v[0];
+  p.z = r.v[1];
+  p.ghi = r.v[2];
+  p.gwin = r.v[3];
+  p.nwin = int(r.v[4]);
+  p.novf = int(r.v[5]);
+  return p;
+}
+
+struct F4 {
+  float a, b, c, d;
+};
+struct OpSumF4 {
+  __device__ __forceinline__ F4 operator()(F4 x, F4 y) const { return F4{x.a + y.a, x.b + y.b, x.c + y.c, x.d + y.d}; }
+};
+
 // ---------------------------------------------------------------------------
-// nucleus boundary of a register-resident row (e values), see the file header.
-// On return rec.{Z, lo, hi, xstar, istar, mode} describe the keep rule.
+// nucleus boundary of one row.  `pr` is the reduced result of the pass that just
+// ran over the window [lo, hi) with this thread's counters in `acc`.
+// On return rec.{Z, xstar, istar} hold the keep rule; *theta_out / *dens_out feed the hint.
 // ---------------------------------------------------------------------------
 template <class TIn>
-__device__ __forceinline__ void nucleus_search(float4 (&r)[kMaxChunks], int nchunk, const TIn* row, float temp,
-                                               float top_p, float Zall, int kind, V1Scratch* vs, int& phase,
-                                               RowRecord& rec, int* stats) {
-  StreamScratch* ss = &vs->s;
+__device__ __noinline__ void resolve_nucleus(const TIn* row, int V, float temp, float top_p, float m0,
+                                                PassResult pr, float lo, float hi, float dens, int& pp,
+                                                ScanAcc& acc, float* col_x, int* col_i, StreamScratch* ss, int& phase,
+                                                RowRecord& rec, float* theta_out, float* dens_out, int* stats) {
   const int tid = threadIdx.x;
-  const double target = double(top_p) * double(Zall);
-  if (!(target < double(Zall))) return;  // top_p >= 1: nothing is cut (rec keeps lo = hi = 0)
+  const double target = double(top_p) * double(pr.z);
+  *theta_out = pr.mx;
+  *dens_out = dens;
+  if (!(target < double(pr.z))) return;  // top_p >= 1: nothing is cut
 
-  // bracket in e-space: G(e >= lo) > target >= G(e >= hi); u = log2 of the thresholds
-  float lo = 0.0f, hi = 2.0f, Glo = Zall, Ghi = 0.0f;
-  float ulo = -160.0f, uhi = 1.0f;
-  bool have_lo = false, have_hi = false;
-  const float lgZ = __log2f(Zall);
-  const bool warm = vs->warm_ok[kind] != 0;
-  const float uwarm = vs->warm[kind] + lgZ;
-  if (tid == 0) vs->s.ncand = 0;
+  // boundary entry x* lies in [A, B):  G(x >= A) = GA > target >= GB = G(x >= B)
+  float A = -INFINITY, GA = pr.z, B = nextafterf(pr.mx, INFINITY), GB = 0.0f;
   int npass = 0;
-
+  bool list_ok = false;
 #pragma unroll 1
-  for (int pass = 0; pass < kSearchPasses; ++pass) {
-    if (have_lo && (Glo - Ghi) <= kCandGoal * lo) break;
-    npass = pass + 1;
-    float u1, u2, u3;
-    if (pass == 0) {
-      if (warm) {
-        u1 = uwarm - 0.25f, u2 = uwarm, u3 = uwarm + 0.25f;
-      } else {
-        u1 = -12.0f, u2 = -8.0f, u3 = -4.0f;
-      }
-    } else if (!have_lo) {  // everything tried so far was too high: walk down
-      const float top = have_hi ? uhi : 0.0f;
-      u1 = top - 14.0f, u2 = top - 6.0f, u3 = top - 2.0f;
-    } else if (!have_hi) {  // everything tried so far was too low: walk up towards e = 1
-      u1 = 0.75f * ulo, u2 = 0.5f * ulo, u3 = 0.25f * ulo;
+  for (;;) {
+    if (double(pr.ghi) > target) {
+      A = hi, GA = pr.ghi;
+    } else if (double(pr.ghi + pr.gwin) > target) {
+      if (lo > A) A = lo, GA = pr.ghi + pr.gwin;
+      if (hi < B) B = hi, GB = pr.ghi;
+      list_ok = pr.novf <= kOvfCap;
+    } else if (lo < B) {
+      B = lo, GB = pr.ghi + pr.gwin;
+    }
+    if (pr.nwin > 0 && hi - lo > 0.0f && hi - lo < 1e30f) dens = float(pr.nwin) / (hi - lo);
+    if (list_ok) break;
+    if (nextafterf(A, INFINITY) >= B || npass >= 48) break;  // one float value left: tie mode below
+    // ---- move the window inside [A, B) and re-read the row through L2
+    if (A == -INFINITY) {
+      float step = 4.0f * float(1 << (npass < 6 ? npass : 6));
+      if (dens > 0.0f) step = fminf(step, fmaxf(1200.0f / dens, 1e-3f));
+      lo = B - step, hi = B;
     } else {
-      const float w = uhi - ulo;
-      const float c = ulo + w * __fdividef(Glo - float(target), Glo - Ghi);
-      const float d = 0.125f * w;
-      const float a = ulo + 0.02f * w, b = uhi - 0.02f * w;
-      u1 = fminf(fmaxf(c - d, a), b);
-      u2 = fminf(fmaxf(c, a), b);
-      u3 = fminf(fmaxf(c + d, a), b);
-    }
-    u1 = fminf(fmaxf(u1, -150.0f), 0.5f);
-    u2 = fminf(fmaxf(u2, -150.0f), 0.5f);
-    u3 = fminf(fmaxf(u3, -150.0f), 0.5f);
-    const float t1 = ex2_approx(u1), t2 = ex2_approx(u2), t3 = ex2_approx(u3);
-    const F4 g = sblock_allreduce(mass_above3(r, nchunk, t1, t2, t3), OpSumF4(), ss, phase);
-    const float old_lo = lo, old_hi = hi;
-    // ascending thresholds: the largest one still above the target raises lo, the smallest one not above lowers hi
-    const float tt[3] = {t1, t2, t3}, uu[3] = {u1, u2, u3}, gg[3] = {g.a, g.b, g.c};
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-      if (double(gg[k]) > target) {
-        if (tt[k] > lo) lo = tt[k], ulo = uu[k], Glo = gg[k], have_lo = true;
+      const float W = B - A;
+      const float est = dens > 0.0f ? dens * W : __fdividef(GA - GB, row_exp(A, m0));
+      if (est <= 1200.0f) {
+        lo = A, hi = B;
       } else {
-        if (tt[k] < hi) hi = tt[k], uhi = uu[k], Ghi = gg[k], have_hi = true;
+        const float c = A + W * __fdividef(GA - float(target), GA - GB);
+        const float h = 0.5f * W * __fdividef(1200.0f, est);
+        lo = fmaxf(A, c - h), hi = fminf(B, c + h);
+        if (!(hi > lo)) lo = A, hi = fminf(B, nextafterf(A + 2.0f * h, INFINITY));
+        if (!(hi > lo)) hi = B;
       }
     }
-    if (pass > 0 && lo == old_lo && hi == old_hi) break;  // float resolution reached: no progress possible
+    acc = ScanAcc{-INFINITY, 0.0f, 0.0f, 0.0f, 0};
+    ++pp;
+    scan_global<TIn>(row, V, temp, m0, lo, hi, acc, col_x, col_i, &ss->novf[pp & 1], ss);
+    pr = reduce_pass(acc, pp, ss, phase);
+    ++npass;
   }
+  *dens_out = dens;
 
   bool solved = false;
-  if (have_lo && (Glo - Ghi) <= kCandGoal * lo) {
-    // ---- collect the bracket [lo, hi) and order it exactly like the reference's sort
+  if (list_ok) {
+    // ---- narrow [A, B) on the window entries, now in registers
+    float cx[kColCap + 1], ce[kColCap + 1];
 #pragma unroll
-    for (int c = 0; c < kMaxChunks; ++c) {
-      if (c < nchunk) {
+    for (int j = 0; j < kColCap; ++j) {
+      const bool v = j < acc.cnt;
+      cx[j] = v ? col_x[j * kCT + tid] : -INFINITY;
+      ce[j] = v ? row_exp(cx[j], m0) : 0.0f;
+    }
+    {
+      const bool v = tid < pr.novf;
+      cx[kColCap] = v ? ss->ovf_x[tid] : -INFINITY;
+      ce[kColCap] = v ? row_exp(cx[kColCap], m0) : 0.0f;
+    }
+#pragma unroll 1
+    for (int it = 0; it < 24; ++it) {
+      if ((GA - GB) <= kCandGoal * row_exp(A, m0)) break;
+      const float W = B - A;
+      const float c = A + W * __fdividef(GA - float(target), GA - GB);
+      const float d = 0.125f * W;
+      const float a1 = nextafterf(A, INFINITY), b1 = B;
+      float t1 = fminf(fmaxf(c - d, a1), b1), t2 = fminf(fmaxf(c, a1), b1), t3 = fminf(fmaxf(c + d, a1), b1);
+      if (!(t2 > t1)) t2 = A + 0.5f * W;
+      if (!(t3 > t2)) t3 = A + 0.75f * W;
+      F4 g{0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const float e = f4c(r[c], k);
-          if (e >= lo && e < hi) {
-            const int idx = c * kChunk + 4 * tid + k;
-            const int pos = atomicAdd(&vs->s.ncand, 1);
-            if (pos < kCandMax) {
-              vs->cand_e[pos] = e;
-              vs->cand_i[pos] = idx;
-              vs->cand_x[pos] = scale_logit(to_f32(row[idx]), temp);
-            }
+      for (int j = 0; j <= kColCap; ++j) {
+        if (cx[j] >= t1) g.a += ce[j];
+        if (cx[j] >= t2) g.b += ce[j];
+        if (cx[j] >= t3) g.c += ce[j];
+      }
+      g = creduce_small(g, OpSumF4(), ss, phase);
+      const float oA = A, oB = B;
+      // every list entry is below the window's upper edge, so G(x >= t) = (mass above the window) + list part
+      const float tt[3] = {t1, t2, t3}, gg[3] = {pr.ghi + g.a, pr.ghi + g.b, pr.ghi + g.c};
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        if (tt[k] > oA && tt[k] < oB) {
+          if (double(gg[k]) > target) {
+            if (tt[k] > A) A = tt[k], GA = gg[k];
+          } else {
+            if (tt[k] < B) B = tt[k], GB = gg[k];
           }
         }
       }
+      if (A == oA && B == oB) break;  // float resolution reached
     }
-    if (tid == 0) vs->res_ok = 0;
-    __syncthreads();
-    const int n = vs->s.ncand;
+    // ---- the bracket's entries, ordered exactly like the reference's sort
+#pragma unroll
+    for (int j = 0; j <= kColCap; ++j) {
+      if (cx[j] >= A && cx[j] < B) {
+        const int pos = atomicAdd(&ss->ncand, 1);
+        if (pos < kCandMax) {
+          ss->cand_x[pos] = cx[j];
+          ss->cand_e[pos] = ce[j];
+          ss->cand_i[pos] = j < kColCap ? col_i[j * kCT + tid] : ss->ovf_i[tid];
+        }
+      }
+    }
+    if (tid == 0) ss->res_ok = 0;
+    cbar();
+    const int n = ss->ncand;
     if (n <= kCandMax) {
-      int Pn = 32;
+      int Pn = 16;
       while (Pn < n) Pn <<= 1;
-      const int parts = kST / Pn;  // 4..32 threads share one candidate (same warp)
+      const int parts = kCT / Pn;  // 2..32 threads share one candidate (same warp)
       const int t = tid / parts, part = tid - t * parts;
       double cum = 0.0;
       float ex = 0.0f, xx = 0.0f;
       int ii = 0;
       if (t < n) {
-        ex = vs->cand_e[t], xx = vs->cand_x[t], ii = vs->cand_i[t];
+        ex = ss->cand_e[t], xx = ss->cand_x[t], ii = ss->cand_i[t];
         for (int j = part; j < n; j += parts) {
-          const float xj = vs->cand_x[j];
-          const int ij = vs->cand_i[j];
-          if (xj > xx || (xj == xx && ij <= ii)) cum += double(vs->cand_e[j]);
+          const float xj = ss->cand_x[j];
+          const int ij = ss->cand_i[j];
+          if (xj > xx || (xj == xx && ij <= ii)) cum += double(ss->cand_e[j]);
         }
       }
       for (int o = parts >> 1; o > 0; o >>= 1) cum += __shfl_xor_sync(0xffffffffu, cum, o);
-      const double incl = double(Ghi) + cum;
+      const double incl = double(GB) + cum;
       if (t < n && part == 0 && incl > target && !(incl - double(ex) > target)) {
-        vs->res_x = xx;
-        vs->res_i = ii;
-        vs->res_Z = float(incl);
-        vs->res_ok = 1;
+        ss->res_x = xx;
+        ss->res_i = ii;
+        ss->res_Z = float(incl);
+        ss->res_ok = 1;
       }
-      __syncthreads();
-      if (vs->res_ok) {
+      cbar();
+      if (ss->res_ok) {
         solved = true;
-        rec.Z = vs->res_Z;
-        rec.lo = lo;
-        rec.hi = hi;
-        rec.xstar = vs->res_x;
-        rec.istar = vs->res_i;
-        rec.mode = 0;
+        rec.Z = ss->res_Z;
+        rec.xstar = ss->res_x;
+        rec.istar = ss->res_i;
       }
     }
-  }
-  if (!solved) {
-    // slow path: exact bisection on (e, index) keys inside the bracket found so far
-    unsigned long long klo = have_lo ? (unsigned long long)__float_as_uint(lo) << 32 : 0ull;
-    unsigned long long khi = (unsigned long long)__float_as_uint(hi) << 32;
-    double Zk = 0.0;
-    unsigned long long kstar = 0ull;
+    if (!solved) {
+      // crowded bracket (ties): bisection on K = (okey(x) << 32) | ~index over the list entries
+      auto keyof = [](float x, int idx) {
+        return ((unsigned long long)okey(x) << 32) | (unsigned long long)(0xffffffffu - unsigned(idx));
+      };
+      unsigned long long klo = (unsigned long long)okey(A) << 32, khi = (unsigned long long)okey(B) << 32;
+      unsigned long long kk[kColCap + 1];
+#pragma unroll
+      for (int j = 0; j <= kColCap; ++j) {
+        const int idx = j < kColCap ? (j < acc.cnt ? col_i[j * kCT + tid] : 0) : (tid < pr.novf ? ss->ovf_i[tid] : 0);
+        kk[j] = (cx[j] >= A && cx[j] < B) ? keyof(cx[j], idx) : 0ull;
+      }
+      auto F = [&](unsigned long long K) {
+        double s = 0.0;
+#pragma unroll
+        for (int j = 0; j <= kColCap; ++j)
+          if (kk[j] >= K && kk[j] != 0ull) s += double(ce[j]);
+        return double(GB) + creduce_small(s, OpSumD(), ss, phase);
+      };
 #pragma unroll 1
-    for (int attempt = 0; attempt < 2 && kstar == 0ull; ++attempt) {
-      // second attempt: the bracket was inconsistent (rounding), redo on the full range
-      const unsigned long long a = attempt == 0 ? klo : 0ull;
-      const unsigned long long b = attempt == 0 ? khi : (unsigned long long)__float_as_uint(2.0f) << 32;
-      kstar = stream_bisect(r, nchunk, a, b, attempt == 0 ? double(Ghi) : 0.0, target, ss, phase, &Zk);
+      while (khi - klo > 1ull) {
+        const unsigned long long mid = klo + ((khi - klo) >> 1);
+        if (F(mid) > target) klo = mid;
+        else khi = mid;
+      }
+      rec.Z = float(F(klo));
+      rec.xstar = okey_inv(unsigned(klo >> 32));
+      rec.istar = int(0xffffffffu - unsigned(klo & 0xffffffffull));
+      solved = true;
     }
-    rec.Z = float(Zk);
-    if (kstar != 0ull) {
-      const float estar = __uint_as_float(unsigned(kstar >> 32));
-      rec.mode = 1;
-      rec.lo = estar;
-      rec.hi = __uint_as_float(unsigned(kstar >> 32) + 1u);
-      rec.istar = int(0xffffffffu - unsigned(kstar & 0xffffffffull));
-      lo = estar;
+  } else {
+    // one float value A holds more entries than the list can: count them in index order
+    const float eA = row_exp(A, m0);
+    const int nstep = (V + 2047) / 2048;
+    int ilo = -1, ihi = V - 1;  // smallest I with GB + eA * #{x == A, idx <= I} > target
+    auto C = [&](int I) {
+      float cnt = 0.0f;
+      for (int c = 0; c < nstep; ++c) {
+        const int i0 = c * 2048 + 4 * tid;
+        if (i0 < V) {
+          float4 v = load4_scaled<TIn>(row + i0, temp);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            if (f4c(v, k) >= A && f4c(v, k) < B && i0 + k <= I) cnt += 1.0f;
+        }
+      }
+      return creduce_small(cnt, OpSumF(), ss, phase);
+    };
+#pragma unroll 1
+    while (ihi - ilo > 1) {
+      const int mid = ilo + ((ihi - ilo) >> 1);
+      if (double(GB) + double(eA) * double(C(mid)) > target) ihi = mid;
+      else ilo = mid;
     }
+    rec.Z = float(double(GB) + double(eA) * double(C(ihi)));
+    rec.xstar = A;
+    rec.istar = ihi;
   }
+  *theta_out = rec.xstar;
   if (stats && tid == 0) {
-    atomicAdd(&stats[npass < 15 ? npass : 15], 1);          // [0..15] search passes per row
-    atomicAdd(&stats[solved ? 16 : 17], 1);                  // fast finish / bisection path
-    if (solved) atomicAdd(&stats[18], vs->s.ncand);          // candidates ordered
+    atomicAdd(&stats[npass < 15 ? npass : 15], 1);  // [0..15] rows by number of extra (L2) passes
+    atomicAdd(&stats[16], 1);
+    if (!list_ok) atomicAdd(&stats[17], 1);
+    atomicAdd(&stats[18], ss->ncand);
   }
-  if (tid == 0 && lo > 0.0f) {
-    vs->warm[kind] = __log2f(lo) - lgZ;
-    vs->warm_ok[kind] = 1;
-  }
-  __syncthreads();  // candidate area and result slots are free for the next row
+  cbar();  // candidate area and result slots are free for the next row
 }
 
 // ---------------------------------------------------------------------------
@@ -416,11 +519,11 @@ __device__ __forceinline__ void nucleus_search(float4 (&r)[kMaxChunks], int nchu
 // the bonus sample (n == gamma).  Rows are re-read through L2, noise from HBM.
 // ---------------------------------------------------------------------------
 template <class TIn>
-__device__ __forceinline__ long long sample_sequence(const StreamParams& P, int b, int n, V1Scratch* vs, int& phase) {
-  StreamScratch* ss = &vs->s;
+__device__ __forceinline__ long long sample_sequence(const StreamParams& P, int b, int n, StreamScratch* ss,
+                                                     int& phase) {
   const int tid = threadIdx.x;
   const int gamma = P.gamma, V = P.V;
-  const int nchunk = (V + kChunk - 1) / kChunk;
+  const int nstep = (V + 2047) / 2048;
   const bool bonus = (n == gamma);
   const int base = b * (2 * gamma + 1);
   const RowRecord rp = load_record(&P.records[base + (bonus ? 2 * gamma : 2 * n + 1)]);
@@ -432,25 +535,24 @@ __device__ __forceinline__ long long sample_sequence(const StreamParams& P, int 
   MassBest mb{0.0f, -1.0f, 0x7fffffff};
   ValIdx bd{-INFINITY, 0x7fffffff};
 #pragma unroll 2
-  for (int c = 0; c < nchunk; ++c) {
-    const int i0 = c * kChunk + 4 * tid;
+  for (int c = 0; c < nstep; ++c) {  // 2048 entries per step: one float4 per thread and array
+    const int i0 = c * 2048 + 4 * tid;
     if (i0 < V) {
       float4 xp = load4_scaled<TIn>(prow + i0, P.t_temp);
       float4 xq = make_float4(0.f, 0.f, 0.f, 0.f);
       if (!bonus) xq = load4_scaled<TIn>(qrow + i0, P.d_temp);
-      const float4 nv = __ldg(reinterpret_cast<const float4*>(nz + i0));
-      const float nn[4] = {nv.x, nv.y, nv.z, nv.w};
+      float4 nv = __ldg(reinterpret_cast<const float4*>(nz + i0));
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         const float x = f4c(xp, k);
-        float d = apply_record(rp, x, row_exp(x, rp.mL), i0 + k) * invZp;
+        float d = kept(rp, x, i0 + k) ? row_exp(x, rp.m0) * invZp : 0.0f;
         if (!bonus) {
           const float y = f4c(xq, k);
-          d -= apply_record(rq, y, row_exp(y, rq.mL), i0 + k) * invZq;
+          d -= kept(rq, y, i0 + k) ? row_exp(y, rq.m0) * invZq : 0.0f;
         }
         if (d > 0.0f) {
           mb.mass += d;
-          const float key = __fdividef(d, nn[k]);
+          const float key = __fdividef(d, f4c(nv, k));
           if (key > mb.key || (key == mb.key && i0 + k < mb.idx)) {
             mb.key = key;
             mb.idx = i0 + k;
@@ -461,23 +563,60 @@ __device__ __forceinline__ long long sample_sequence(const StreamParams& P, int 
       }
     }
   }
-  mb = sblock_allreduce(mb, OpMassBest(), ss, phase);
+  mb = creduce_small(mb, OpMassBest(), ss, phase);
   long long cand;
   if (mb.mass > 0.0f) {
     cand = mb.idx == 0x7fffffff ? 0 : mb.idx;
   } else {
-    bd = sblock_allreduce(bd, OpArgMax(), ss, phase);  // zero mass: first argmax of p - q (src/utils.py:799-806)
+    bd = creduce_small(bd, OpArgMax(), ss, phase);  // zero mass: first argmax of p - q (src/utils.py:799-806)
     cand = bd.i == 0x7fffffff ? 0 : bd.i;
   }
   return cand;
 }
 
+// accept tests of every position of sequence b from the published records, leading run, token
 template <class TIn>
-__global__ void __launch_bounds__(kST, 1) verify_stream_kernel(const __grid_constant__ StreamParams P) {
+__device__ __noinline__ void close_sequence(const StreamParams& P, int b, StreamScratch* ss, int& phase) {
+  const int tid = threadIdx.x;
+  const int gamma = P.gamma;
+  if (tid < gamma) {
+    const int base = b * (2 * gamma + 1);
+    const RowRecord rq = load_record(&P.records[base + 2 * tid]);
+    const RowRecord rp = load_record(&P.records[base + 2 * tid + 1]);
+    const long long o = (long long)b * gamma + tid;
+    const int accept = P.r[(long long)b * P.r_sb + tid] <= __fdiv_rn(rp.sel, rq.sel);  // raw IEEE division
+    P.accept_mask[o] = (unsigned char)accept;
+    P.sel_p[o] = rp.sel;
+    P.sel_q[o] = rq.sel;
+    ss->seq_acc[tid] = accept;
+  }
+  cbar();
+  int n = 0;
+  while (n < gamma && ss->seq_acc[n] != 0) ++n;
+  const long long cand = sample_sequence<TIn>(P, b, n, ss, phase);
+  if (tid == 0) {
+    P.accepted_len[b] = n;
+    P.token[b] = cand;
+    P.all_accepted[b] = (unsigned char)(n == gamma);
+  }
+}
+
+// prediction for a row of `kind` (0 draft, 1 target): thread 0 only, published through the scratch
+__device__ __forceinline__ void fetch_hint(const StreamParams& P, int kind, StreamScratch* ss) {
+  const uint4 h = __ldcg(reinterpret_cast<const uint4*>(&P.hints[kind]));
+  ss->hint_m0 = __uint_as_float(h.x);
+  ss->hint_th = __uint_as_float(h.y);
+  ss->hint_dens = __uint_as_float(h.z);
+  ss->hint_ok = int(h.w);
+}
+
+template <class TIn>
+__global__ void __launch_bounds__(kST, 2) verify_stream_kernel(const __grid_constant__ StreamParams P) {
   extern __shared__ __align__(128) unsigned char smem[];
   unsigned char* ring = smem;
-  V1Scratch* vs = reinterpret_cast<V1Scratch*>(smem + kSlots * kSlotBytes);
-  StreamScratch* ss = &vs->s;
+  float* col_x = reinterpret_cast<float*>(smem + kSlots * kSlotBytes);
+  int* col_i = reinterpret_cast<int*>(col_x + kColCap * kCT);
+  StreamScratch* ss = reinterpret_cast<StreamScratch*>(col_i + kColCap * kCT);
 
   const int tid = threadIdx.x;
   const int gamma = P.gamma;
@@ -487,163 +626,157 @@ __global__ void __launch_bounds__(kST, 1) verify_stream_kernel(const __grid_cons
   constexpr int kElt = int(sizeof(TIn));
 
   if (tid == 0) {
-    for (int s = 0; s < kSlots; ++s) mbar_init(&ss->full[s], 1);
+    for (int s = 0; s < kSlots; ++s) {
+      mbar_init(&ss->full[s], 1);
+      mbar_init(&ss->empty[s], kCW);
+    }
     mbar_fence_init();
-    vs->warm_ok[0] = vs->warm_ok[1] = 0;
+    ss->novf[0] = ss->novf[1] = 0;
+    ss->ncand = 0;
+    if (int(blockIdx.x) < njobs) fetch_hint(P, decode_job(blockIdx.x, gamma).is_target, ss);
   }
   __syncthreads();
-  int phase = 0;
 
-  // ---- producer: thread 0 keeps up to kSlots chunks in flight, in job order
-  int issue_job = blockIdx.x, issue_chunk = 0;
-  unsigned issued = 0, consumed = 0;
-  auto produce = [&]() {
-    while (issue_job < njobs && issued - consumed < unsigned(kSlots)) {
-      const TIn* row = job_row<TIn>(P, decode_job(issue_job, gamma));
-      const int e0 = issue_chunk * kChunk;
-      const int ne = (V - e0) < kChunk ? (V - e0) : kChunk;
-      const unsigned slot = issued % unsigned(kSlots);
-      mbar_expect_tx(&ss->full[slot], unsigned(ne * kElt));
-      bulk_g2s(ring + slot * kSlotBytes, row + e0, unsigned(ne * kElt), &ss->full[slot]);
-      ++issued;
-      if (++issue_chunk == nchunk) {
-        issue_chunk = 0;
-        issue_job += gridDim.x;
+  if (tid >= kCT) {
+    // ---- producer warp: one lane streams this block's rows through the ring, in job order
+    if (tid == kCT) {
+      unsigned seq = 0;
+      for (int job = blockIdx.x; job < njobs; job += gridDim.x) {
+        const TIn* row = job_row<TIn>(P, decode_job(job, gamma));
+        for (int c = 0; c < nchunk; ++c, ++seq) {
+          const unsigned slot = seq % unsigned(kSlots);
+          if (seq >= unsigned(kSlots)) mbar_wait(&ss->empty[slot], ((seq / unsigned(kSlots)) - 1u) & 1u);
+          const int e0 = c * kChunk;
+          const int ne = (V - e0) < kChunk ? (V - e0) : kChunk;
+          mbar_expect_tx(&ss->full[slot], unsigned(ne * kElt));
+          bulk_g2s(ring + slot * kSlotBytes, row + e0, unsigned(ne * kElt), &ss->full[slot]);
+        }
       }
     }
-  };
-  if (tid == 0) produce();
+    return;
+  }
 
+  // ---- consumers
+  int phase = 0, pp = 0;
+  unsigned seq = 0;
+  const int lane = tid & 31;
 #pragma unroll 1
   for (int job = blockIdx.x; job < njobs; job += gridDim.x) {
     const RowJob jb = decode_job(job, gamma);
     const TIn* row = job_row<TIn>(P, jb);
     const float temp = jb.is_target ? P.t_temp : P.d_temp;
     const float top_p = jb.is_target ? P.t_top_p : P.d_top_p;
+    const bool nucleus = top_p > 0.0f;
+    long long tk0 = 0;
+    if (P.stats && tid == 0) tk0 = clock64();
+    auto tick = [&](int slot) {  // tuning hook: cycles per phase summed over blocks (units of 16 cycles)
+      if (P.stats && tid == 0) {
+        const long long t = clock64();
+        atomicAdd(&P.stats[slot], int((t - tk0) >> 4));
+        tk0 = t;
+      }
+    };
 
-    // ---- pull the row out of the ring into registers (scaled logits)
-    float4 r[kMaxChunks];
-    float mx = -INFINITY;
-#pragma unroll
-    for (int c = 0; c < kMaxChunks; ++c) {
-      float4 v = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
-      if (c < nchunk) {
-        const unsigned seq = consumed + unsigned(c);
-        const unsigned slot = seq % unsigned(kSlots);
-        mbar_wait(&ss->full[slot], (seq / unsigned(kSlots)) & 1u);
-        if (c * kChunk + 4 * tid < V) {
-          const unsigned char* sp = ring + slot * kSlotBytes;
-          if constexpr (kElt == 4) {
-            v = reinterpret_cast<const float4*>(sp)[tid];
-          } else {
-            const uint2 u = reinterpret_cast<const uint2*>(sp)[tid];
-            v.x = __uint_as_float(u.x << 16);
-            v.y = __uint_as_float(u.x & 0xffff0000u);
-            v.z = __uint_as_float(u.y << 16);
-            v.w = __uint_as_float(u.y & 0xffff0000u);
-          }
-          if (temp != 1.0f) {
-            v.x = __fdiv_rn(v.x, temp);
-            v.y = __fdiv_rn(v.y, temp);
-            v.z = __fdiv_rn(v.z, temp);
-            v.w = __fdiv_rn(v.w, temp);
-          }
+    // the drafted token's logit is needed at the end of the job: fetch it now (thread 0)
+    long long tok = -1;
+    float xtok = 0.0f;
+#ifndef DUODEC_LATE_TOK
+    if (tid == 0 && jb.j < gamma) {
+      tok = P.tokens[(long long)jb.b * P.tok_sb + jb.j];
+      if (tok >= 0 && tok < V) xtok = scale_logit(to_f32(__ldcg(row + tok)), temp);
+    }
+#endif
+
+    // prediction (published before the last barrier): exponent offset and nucleus window
+    const bool warm = ss->hint_ok != 0;
+    float m0 = warm ? ss->hint_m0 : 0.0f;
+    float dens = warm ? ss->hint_dens : 0.0f;
+    float lo = INFINITY, hi = INFINITY;
+    if (nucleus && warm && dens > 0.0f) {
+      #ifndef DUODEC_WIN
+#define DUODEC_WIN 1100.0f
+#endif
+      const float hw = fminf(fmaxf(__fdividef(DUODEC_WIN, dens), 0.02f), 6.0f);
+      lo = ss->hint_th - hw, hi = ss->hint_th + hw;
+    }
+
+    // ---- the one pass over the row, chunk by chunk as the TMA copies land
+    ScanAcc acc{-INFINITY, 0.0f, 0.0f, 0.0f, 0};
+    ++pp;
+#pragma unroll 1
+    for (int c = 0; c < nchunk; ++c, ++seq) {
+      const unsigned slot = seq % unsigned(kSlots);
+      mbar_wait(&ss->full[slot], (seq / unsigned(kSlots)) & 1u);
+      const int i0 = c * kChunk + 4 * tid;
+      if (i0 < V) {
+        float4 v = unpack4<TIn>(ring + slot * kSlotBytes + 4 * tid * kElt);
+        if (temp != 1.0f) {
+          v.x = __fdiv_rn(v.x, temp);
+          v.y = __fdiv_rn(v.y, temp);
+          v.z = __fdiv_rn(v.z, temp);
+          v.w = __fdiv_rn(v.w, temp);
         }
-        mx = fmaxf(mx, fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w)));
+        scan4(v, i0, m0, lo, hi, acc, col_x, col_i, &ss->novf[pp & 1], ss);
       }
-      r[c] = v;
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&ss->empty[slot]);
     }
-    consumed += unsigned(nchunk);
-    const float m = sblock_allreduce(mx, OpMaxF(), ss, phase);  // its barrier also frees the ring slots
-    if (tid == 0) produce();
-
-    // ---- e = exp(x - m) in registers, Z
-    const float mL = m * kLog2e;
-    float z = 0.0f;
-#pragma unroll
-    for (int c = 0; c < kMaxChunks; ++c) {
-      if (c < nchunk) {
-        r[c].x = row_exp(r[c].x, mL);
-        r[c].y = row_exp(r[c].y, mL);
-        r[c].z = row_exp(r[c].z, mL);
-        r[c].w = row_exp(r[c].w, mL);
-        z += (r[c].x + r[c].y) + (r[c].z + r[c].w);
-      }
+    tick(20);
+    PassResult pr = reduce_pass(acc, pp, ss, phase);
+    tick(21);
+    if (!(fabsf(pr.mx * kLog2e - m0) <= 32.0f) || !(pr.z < INFINITY) || !(pr.z > 0.0f)) {
+      // the predicted offset was far from this row's maximum: redo the pass with the exact one
+      m0 = pr.mx * kLog2e;
+      acc = ScanAcc{-INFINITY, 0.0f, 0.0f, 0.0f, 0};
+      ++pp;
+      scan_global<TIn>(row, V, temp, m0, lo, hi, acc, col_x, col_i, &ss->novf[pp & 1], ss);
+      pr = reduce_pass(acc, pp, ss, phase);
     }
-    const float Zall = sblock_allreduce(z, OpSumF(), ss, phase);
 
     RowRecord rec;
-    rec.mL = mL;
-    rec.Z = Zall;
-    rec.lo = 0.0f;
-    rec.hi = 0.0f;
+    rec.m0 = m0;
+    rec.Z = pr.z;
     rec.xstar = -INFINITY;
     rec.istar = 0x7fffffff;
-    rec.mode = 0;
     rec.sel = 0.0f;
-    if (top_p > 0.0f) nucleus_search<TIn>(r, nchunk, row, temp, top_p, Zall, jb.is_target, vs, phase, rec, P.stats);
+    float theta = pr.mx;
+    if (nucleus)
+      resolve_nucleus<TIn>(row, V, temp, top_p, m0, pr, lo, hi, dens, pp, acc, col_x, col_i, ss, phase, rec, &theta,
+                           &dens, P.stats);
 
-    // ---- publish the row; resolve the position / the sequence
-    const long long tok = jb.j < gamma ? P.tokens[(long long)jb.b * P.tok_sb + jb.j] : -1;
-    const bool tok_ok = tok >= 0 && tok < V;
-    const int owner = tok_ok ? int((tok & (kChunk - 1)) >> 2) : 0;
-    if (tid == owner) {
-      if (tok_ok) {
-        const int tc = int(tok >> 12), tk = int(tok & 3);
-        float e = 0.0f;
-#pragma unroll
-        for (int c = 0; c < kMaxChunks; ++c)
-          if (c == tc) e = f4c(r[c], tk);
-        if (e < rec.hi && e >= rec.lo)  // inside the boundary bracket: the exact order decides
-          e = apply_record(rec, scale_logit(to_f32(row[tok]), temp), e, int(tok));
-        else if (!(e >= rec.hi))
-          e = 0.0f;
+    tick(22);
+    // ---- publish the row; the last row of a sequence closes it
+    if (tid == 0) {
+#ifdef DUODEC_LATE_TOK
+      if (jb.j < gamma) {
+        tok = P.tokens[(long long)jb.b * P.tok_sb + jb.j];
+        if (tok >= 0 && tok < V) xtok = scale_logit(to_f32(__ldcg(row + tok)), temp);
+      }
+#endif
+      if (tok >= 0 && tok < V) {
+        const float e = kept(rec, xtok, int(tok)) ? row_exp(xtok, m0) : 0.0f;
         rec.sel = __fdiv_rn(e, rec.Z);
       }
-      P.records[job] = rec;
+      store_record(&P.records[job], rec);
+      // prediction for later rows of the same model (any finished row's values will do)
+      *reinterpret_cast<uint4*>(&P.hints[jb.is_target]) =
+          make_uint4(__float_as_uint(pr.mx * kLog2e), __float_as_uint(theta), __float_as_uint(dens), 1u);
       __threadfence();
-      int seq_n = -1;
-      bool arrive = true;
-      if (jb.j < gamma) {
-        const long long o = (long long)jb.b * gamma + jb.j;
-        const int old = atomicAdd(&P.pair_counters[o], 1);
-        arrive = (old == 1);
-        if (arrive) {  // second row of the pair: accept test  r <= p / q
-          __threadfence();
-          const RowRecord pr = load_record(&P.records[jb.is_target ? job - 1 : job + 1]);
-          const float selp = jb.is_target ? rec.sel : pr.sel;
-          const float selq = jb.is_target ? pr.sel : rec.sel;
-          const int accept = P.r[(long long)jb.b * P.r_sb + jb.j] <= __fdiv_rn(selp, selq);
-          P.accept_mask[o] = (unsigned char)accept;
-          P.sel_p[o] = selp;
-          P.sel_q[o] = selq;
-          P.pair_counters[o] = 0;
-          P.pair_token[(long long)jb.b * (gamma + 1) + jb.j] = accept;
-        }
-      }
-      if (arrive) {
+      const int done = atomicAdd(&P.counters[jb.b], 1);
+      const int last = (done == 2 * gamma);
+      if (last) {
+        P.counters[jb.b] = 0;
         __threadfence();
-        const int done = atomicAdd(&P.counters[jb.b], 1);
-        if (done == gamma) {  // last position of the sequence: leading run of accepts
-          __threadfence();
-          const volatile long long* pt = P.pair_token + (long long)jb.b * (gamma + 1);
-          int a = 0;
-          while (a < gamma && pt[a] != 0) ++a;
-          seq_n = a;
-          P.counters[jb.b] = 0;
-        }
       }
-      vs->seq_n = seq_n;
+      ss->seq_last = last;
+      const int next = job + int(gridDim.x);
+      if (next < njobs) fetch_hint(P, decode_job(next, gamma).is_target, ss);
     }
-    __syncthreads();
-    const int seq_n = vs->seq_n;
-    if (seq_n >= 0) {
-      const long long cand = sample_sequence<TIn>(P, jb.b, seq_n, vs, phase);
-      if (tid == 0) {
-        P.accepted_len[jb.b] = seq_n;
-        P.token[jb.b] = cand;
-        P.all_accepted[jb.b] = (unsigned char)(seq_n == gamma);
-      }
+    cbar();
+    tick(23);
+    if (ss->seq_last) {
+      close_sequence<TIn>(P, jb.b, ss, phase);
+      tick(24);
     }
   }
 }

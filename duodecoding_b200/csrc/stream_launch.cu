@@ -1,0 +1,113 @@
+// Launcher of the persistent row-stream verification kernel (see stream_kernel.cuh).
+#include <mutex>
+#include <utility>
+#include <vector>
+
+#include "../../include/duodec.h"
+#include "stream_kernel.cuh"
+#include "stream_launch.h"
+
+namespace duodec {
+
+namespace {
+
+size_t stream_smem_bytes() {
+  return size_t(kSlots) * kSlotBytes + size_t(kColCap) * kCT * 8 + sizeof(StreamScratch) + 128;
+}
+
+// cudaFuncSetAttribute is per (kernel, device): remember the pairs already set up.
+cudaError_t ensure_stream_smem(const void* kernel, size_t bytes) {
+  static std::mutex mu;
+  static std::vector<std::pair<const void*, int>> done;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  std::lock_guard<std::mutex> lk(mu);
+  for (const auto& d : done)
+    if (d.first == kernel && d.second == dev) return cudaSuccess;
+  e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(bytes));
+  if (e != cudaSuccess) return e;
+  done.emplace_back(kernel, dev);
+  return cudaSuccess;
+}
+
+int stream_sm_count() {
+  static std::mutex mu;
+  static int cached[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  std::lock_guard<std::mutex> lk(mu);
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) return 148;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
+
+}  // namespace
+
+size_t stream_workspace_bytes(int B, int gamma) {
+  return 2 * sizeof(StreamHint) + size_t(B) * size_t(2 * gamma + 1) * sizeof(RowRecord);
+}
+
+bool stream_try_launch(const StreamCall& c, int* rc) {
+  const size_t elt = c.dtype == DUODEC_F32 ? 4 : 2;
+  auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+  const bool ok = c.Vd == c.Vt && c.gamma <= 64 && c.temperature > 0.0f && c.draft_temperature > 0.0f &&
+                  c.top_k <= 0 && c.draft_top_k <= 0 && (size_t(c.Vt) * elt) % 16 == 0 && al16(c.target) &&
+                  (c.gamma == 0 || al16(c.draft)) && (size_t(c.t_sb) * elt) % 16 == 0 &&
+                  (size_t(c.t_ss) * elt) % 16 == 0 && (size_t(c.d_sb) * elt) % 16 == 0 &&
+                  (size_t(c.d_ss) * elt) % 16 == 0 && al16(c.noise) && (c.noise_sb % 4) == 0;
+  if (!ok) return false;
+  StreamParams S;
+  S.draft = c.draft;
+  S.target = c.target;
+  S.d_sb = c.d_sb;
+  S.d_ss = c.d_ss;
+  S.t_sb = c.t_sb;
+  S.t_ss = c.t_ss;
+  S.B = c.B;
+  S.gamma = c.gamma;
+  S.V = c.Vt;
+  S.tokens = reinterpret_cast<const long long*>(c.tokens);
+  S.tok_sb = c.tok_sb;
+  S.r = c.r;
+  S.r_sb = c.r_sb;
+  S.noise = c.noise;
+  S.noise_sb = c.noise_sb;
+  S.t_temp = c.temperature;
+  S.t_top_p = c.top_p;
+  S.d_temp = c.draft_temperature;
+  S.d_top_p = c.draft_top_p;
+  S.accept_mask = c.accept_mask;
+  S.sel_p = c.sel_target_p;
+  S.sel_q = c.sel_draft_p;
+  S.accepted_len = reinterpret_cast<long long*>(c.accepted_len);
+  S.token = reinterpret_cast<long long*>(c.token);
+  S.all_accepted = c.all_accepted;
+  char* w = reinterpret_cast<char*>(c.workspace);
+  S.counters = reinterpret_cast<int*>(w);
+  w += size_t(c.B) * 8;
+  w += size_t(c.B) * size_t(c.gamma + 1) * 8;  // (the general kernel's position tokens)
+  S.hints = reinterpret_cast<StreamHint*>(w);
+  w += 2 * sizeof(StreamHint);
+  S.records = reinterpret_cast<RowRecord*>(w);
+  S.stats = c.stats;
+  const size_t smem = stream_smem_bytes();
+  const int njobs = c.B * (2 * c.gamma + 1);
+  const int sms = stream_sm_count();
+  const int grid = njobs < 2 * sms ? njobs : 2 * sms;
+  cudaError_t e;
+  if (c.dtype == DUODEC_F32) {
+    e = ensure_stream_smem(reinterpret_cast<const void*>(verify_stream_kernel<float>), smem);
+    if (e == cudaSuccess) verify_stream_kernel<float><<<grid, kST, smem, c.stream>>>(S);
+  } else {
+    e = ensure_stream_smem(reinterpret_cast<const void*>(verify_stream_kernel<__nv_bfloat16>), smem);
+    if (e == cudaSuccess) verify_stream_kernel<__nv_bfloat16><<<grid, kST, smem, c.stream>>>(S);
+  }
+  *rc = int(e != cudaSuccess ? e : cudaGetLastError());
+  return true;
+}
+
+}  // namespace duodec

@@ -335,8 +335,9 @@ def test_verify_fused_repeatable_and_workspace_self_cleaning(ops, dev):
         again = ops.verify_fused(*args, 1.0, 0, 0.9)
         ops.set_stream_path(True)
         for k in first:
-            if first[k].is_floating_point() and it % 2 == 1:
-                # the general team kernel uses expf, the row-stream kernel 2^(x*log2e): same values to ~1e-6
+            if first[k].is_floating_point():
+                # the general team kernel uses expf, the row-stream kernel 2^(x*log2e - M0) with an exponent
+                # offset M0 predicted from earlier rows: probabilities repeat to ~1e-6, not bitwise
                 torch.testing.assert_close(first[k], again[k], rtol=RTOL, atol=1e-9)
             else:
                 assert torch.equal(first[k], again[k]), k
