@@ -188,7 +188,7 @@ int duodec_verify_fused(const void* draft, const void* target, int dtype, int64_
     c.draft_temperature = draft_temperature, c.draft_top_k = draft_top_k, c.draft_top_p = draft_top_p;
     c.accept_mask = accept_mask, c.sel_target_p = sel_target_p, c.sel_draft_p = sel_draft_p;
     c.accepted_len = accepted_len, c.token = token, c.all_accepted = all_accepted;
-    c.workspace = workspace, c.stats = g_stats.load(), c.stream = st;
+    c.workspace = workspace, c.stats = g_stats.load(), c.path = g_stream_path.load(), c.stream = st;
     int rc = 0;
     if (stream_try_launch(c, &rc)) return rc;
   }

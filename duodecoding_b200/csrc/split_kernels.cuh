@@ -1,0 +1,723 @@
+// Split verification kernels (the default fast path of duodec_verify_fused).
+//
+//   row_scan_kernel   grid (S slices, rows): every block streams ONE 8192-entry slice of one
+//                     logit row with eight independent 128-bit loads per thread in flight,
+//                     and reduces  max, Z = sum 2^(x*log2e - M0), the mass above a predicted
+//                     nucleus window and the window's entries (appended to the row's list in
+//                     global memory).  The block that finishes a row LAST resolves the row:
+//                     nucleus boundary from the list (narrowing on registers + exact all-pairs
+//                     order of the last <= 160 candidates), kept mass Z', probability of the
+//                     drafted token -> a 32-byte record.  A row whose boundary is not inside the
+//                     predicted window (cold start, unusual row) is re-read through L2 by that
+//                     block with a moved window.
+//   seq_sample_kernel grid (S3 slices, B): accept tests r <= p/q from the records, leading run,
+//                     and the ONE token the sequence needs - residual resample at the first
+//                     rejection or the bonus sample - as a sliced arg-max of d_i / noise_i that
+//                     is combined across slices with packed 64-bit atomicMax.
+//
+// HBM traffic: every logit once (row_scan), plus per sequence two rows through L2 and one noise
+// row (seq_sample).  Reference semantics: see stream_kernel.cuh (same record / keep rule).
+#pragma once
+
+#include "stream_kernel.cuh"
+
+namespace duodec {
+
+constexpr int kT3 = 256;        // threads per block
+constexpr int kW3 = kT3 / 32;
+constexpr int kSlice = 8192;    // row entries per row_scan block: 8 float4 per thread
+constexpr int kListCap = 4096;  // window entries a row's global list can hold
+constexpr int kCol3 = 8;        // window entries a thread stages in its own shared-memory column
+constexpr int kOvf3 = 512;      // staged overflow entries per block
+constexpr int kSlice3 = 4096;   // row entries per seq_sample block: 4 float4 per thread and array
+
+struct RowPartial {
+  float mx, z, ghi, gwin;
+};
+struct ListEntry {
+  float x;
+  int idx;
+};
+
+struct SplitParams {
+  const void* draft;
+  const void* target;
+  long long d_sb, d_ss, t_sb, t_ss;
+  int B, gamma, V, S;
+  const long long* tokens;
+  long long tok_sb;
+  const float* r;
+  long long r_sb;
+  const float* noise;
+  long long noise_sb;
+  float t_temp, t_top_p, d_temp, d_top_p;
+  unsigned char* accept_mask;
+  float* sel_p;
+  float* sel_q;
+  long long* accepted_len;
+  long long* token;
+  unsigned char* all_accepted;
+  // workspace (zero-filled once; every counter below is restored to zero by the kernels)
+  StreamHint* hints;      // [2] prediction read by this launch
+  StreamHint* hints_new;  // [2] prediction written by this launch (copied over by seq_sample)
+  RowRecord* records;     // [rows]
+  RowPartial* partials;   // [rows, S]
+  int* row_count;         // [rows] entries in the row's list
+  int* row_arrive;        // [rows] slices finished
+  ListEntry* lists;       // [rows, kListCap]
+  unsigned long long* seq_key;  // [B] best (d/noise, index)
+  unsigned long long* seq_bd;   // [B] best (p - q, index) for the zero-mass fallback
+  float* seq_mass;              // [B]
+  int* seq_arrive;              // [B]
+  int* stats;
+};
+
+struct __align__(16) Scratch3 {
+  R8 red[2][kW3];
+  float cand_e[kCandMax];
+  float cand_x[kCandMax];
+  int cand_i[kCandMax];
+  int ncand, novf, base, last;
+  float res_x;
+  int res_i;
+  float res_Z;
+  int res_ok;
+  float hint_m0, hint_th, hint_dens;
+  int hint_ok;
+  int seq_acc[64];
+  int wsum[kW3];
+};
+
+// all-reduce of an R8 (v[0] max, v[1..7] sum) over the 256 threads; one __syncthreads, ping-pong scratch
+__device__ __forceinline__ R8 reduce3(R8 a, Scratch3* sc, int& phase) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    a.v[0] = fmaxf(a.v[0], __shfl_xor_sync(0xffffffffu, a.v[0], o));
+#pragma unroll
+    for (int i = 1; i < 8; ++i) a.v[i] += __shfl_xor_sync(0xffffffffu, a.v[i], o);
+  }
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (lane == 0) sc->red[phase][w] = a;
+  __syncthreads();
+  R8 x = sc->red[phase][lane & (kW3 - 1)];
+  phase ^= 1;
+#pragma unroll
+  for (int o = kW3 / 2; o > 0; o >>= 1) {
+    x.v[0] = fmaxf(x.v[0], __shfl_xor_sync(0xffffffffu, x.v[0], o));
+#pragma unroll
+    for (int i = 1; i < 8; ++i) x.v[i] += __shfl_xor_sync(0xffffffffu, x.v[i], o);
+  }
+  return x;
+}
+
+template <class T, class Op>
+__device__ __forceinline__ T reduce3_small(T v, Op op, Scratch3* sc, int& phase) {
+  static_assert(sizeof(T) <= 16 && sizeof(T) % 4 == 0, "");
+  v = warp_allreduce(v, op);
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (lane == 0) *reinterpret_cast<T*>(&sc->red[phase][w]) = v;
+  __syncthreads();
+  T x = *reinterpret_cast<T*>(&sc->red[phase][lane & (kW3 - 1)]);
+  phase ^= 1;
+#pragma unroll
+  for (int o = kW3 / 2; o > 0; o >>= 1) x = op(x, shfl_xor_any(x, o));
+  return x;
+}
+
+struct Pass3 {
+  float mx, z, ghi, gwin;
+  int n;  // entries appended to the row's list (> kListCap: the list is incomplete)
+};
+
+// One more pass over a whole row by a single block, through L2: statistics for the window
+// [lo, hi) and its entries appended to the (emptied) global list.
+template <class TIn>
+__device__ __noinline__ Pass3 rescan_row(const TIn* row, int V, float temp, float m0, float lo, float hi,
+                                         ListEntry* list, int* count, Scratch3* sc, int& phase) {
+  const int tid = threadIdx.x;
+  if (tid == 0) *count = 0;
+  __syncthreads();
+  float mx = -INFINITY, z = 0.0f, ghi = 0.0f, gwin = 0.0f;
+  for (int c0 = 0; c0 < V; c0 += 4 * 4 * kT3) {
+    float4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i0 = c0 + u * 4 * kT3 + 4 * tid;
+      if (i0 < V) v[u] = load4_scaled<TIn>(row + i0, temp);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i0 = c0 + u * 4 * kT3 + 4 * tid;
+      if (i0 < V) {
+        mx = fmaxf(mx, fmaxf(fmaxf(v[u].x, v[u].y), fmaxf(v[u].z, v[u].w)));
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const float x = f4c(v[u], k);
+          const float e = row_exp(x, m0);
+          z += e;
+          if (x >= hi) {
+            ghi += e;
+          } else if (x >= lo) {
+            gwin += e;
+            const int pos = atomicAdd(count, 1);
+            if (pos < kListCap) list[pos] = ListEntry{x, i0 + k};
+          }
+        }
+      }
+    }
+  }
+  R8 r;
+  r.v[0] = mx, r.v[1] = z, r.v[2] = ghi, r.v[3] = gwin;
+  r.v[4] = r.v[5] = r.v[6] = r.v[7] = 0.0f;
+  r = reduce3(r, sc, phase);  // its barrier orders every append before the reads below
+  Pass3 p;
+  p.mx = r.v[0], p.z = r.v[1], p.ghi = r.v[2], p.gwin = r.v[3];
+  p.n = *reinterpret_cast<volatile int*>(count);
+  return p;
+}
+
+// Nucleus boundary of one row by the block that finished it; `pr` describes the pass over
+// the window [lo, hi) whose entries sit in `list`.  Fills rec.{Z, xstar, istar}.
+template <class TIn>
+__device__ __noinline__ void resolve_row3(const TIn* row, int V, float temp, float top_p, float m0, Pass3 pr,
+                                          float lo, float hi, float dens, ListEntry* list, int* count,
+                                          Scratch3* sc, int& phase, RowRecord& rec, float* theta_out,
+                                          float* dens_out, int* stats) {
+  const int tid = threadIdx.x;
+  const double target = double(top_p) * double(pr.z);
+  *theta_out = pr.mx;
+  *dens_out = dens;
+  if (!(target < double(pr.z))) return;  // top_p >= 1: nothing is cut
+
+  // boundary entry x* lies in [A, B):  G(x >= A) = GA > target >= GB = G(x >= B)
+  float A = -INFINITY, GA = pr.z, B = nextafterf(pr.mx, INFINITY), GB = 0.0f;
+  int npass = 0;
+  bool list_ok = false;
+#pragma unroll 1
+  for (;;) {
+    if (double(pr.ghi) > target) {
+      A = hi, GA = pr.ghi;
+    } else if (double(pr.ghi + pr.gwin) > target) {
+      if (lo > A) A = lo, GA = pr.ghi + pr.gwin;
+      if (hi < B) B = hi, GB = pr.ghi;
+      list_ok = pr.n <= kListCap;
+    } else if (lo < B) {
+      B = lo, GB = pr.ghi + pr.gwin;
+    }
+    if (pr.n > 0 && hi - lo > 0.0f && hi - lo < 1e30f) dens = float(pr.n) / (hi - lo);
+    if (list_ok) break;
+    if (nextafterf(A, INFINITY) >= B || npass >= 48) break;  // one float value left: tie mode below
+    if (A == -INFINITY) {
+      float step = 4.0f * float(1 << (npass < 6 ? npass : 6));
+      if (dens > 0.0f) step = fminf(step, fmaxf(2000.0f / dens, 1e-3f));
+      lo = B - step, hi = B;
+    } else {
+      const float W = B - A;
+      const float est = dens > 0.0f ? dens * W : __fdividef(GA - GB, row_exp(A, m0));
+      if (est <= 2000.0f) {
+        lo = A, hi = B;
+      } else {
+        const float c = A + W * __fdividef(GA - float(target), GA - GB);
+        const float h = 0.5f * W * __fdividef(2000.0f, est);
+        lo = fmaxf(A, c - h), hi = fminf(B, c + h);
+        if (!(hi > lo)) lo = A, hi = fminf(B, nextafterf(A + 2.0f * h, INFINITY));
+        if (!(hi > lo)) hi = B;
+      }
+    }
+    pr = rescan_row<TIn>(row, V, temp, m0, lo, hi, list, count, sc, phase);
+    ++npass;
+  }
+  *dens_out = dens;
+  if (stats && tid == 0) {
+    atomicAdd(&stats[npass < 15 ? npass : 15], 1);  // [0..15] rows by number of extra (L2) passes
+    atomicAdd(&stats[16], 1);
+  }
+
+  if (list_ok) {
+    // ---- narrow [A, B) on the list entries, held in registers (16 per thread)
+    constexpr int kPer = kListCap / kT3;
+    const float gtop = pr.ghi;  // every list entry is below the window's upper edge
+    float cx[kPer], ce[kPer];
+#pragma unroll
+    for (int j = 0; j < kPer; ++j) {
+      const int p = j * kT3 + tid;
+      float x = -INFINITY;
+      if (p < pr.n) x = __ldcg(&list[p].x);
+      cx[j] = x;
+      ce[j] = p < pr.n ? row_exp(x, m0) : 0.0f;
+    }
+#pragma unroll 1
+    for (int it = 0; it < 24; ++it) {
+      if ((GA - GB) <= kCandGoal * row_exp(A, m0)) break;
+      const float W = B - A;
+      const float c = A + W * __fdividef(GA - float(target), GA - GB);
+      const float d = 0.125f * W;
+      const float a1 = nextafterf(A, INFINITY), b1 = B;
+      float t1 = fminf(fmaxf(c - d, a1), b1), t2 = fminf(fmaxf(c, a1), b1), t3 = fminf(fmaxf(c + d, a1), b1);
+      if (!(t2 > t1)) t2 = A + 0.5f * W;
+      if (!(t3 > t2)) t3 = A + 0.75f * W;
+      F4 g{0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int j = 0; j < kPer; ++j) {
+        if (cx[j] >= t1) g.a += ce[j];
+        if (cx[j] >= t2) g.b += ce[j];
+        if (cx[j] >= t3) g.c += ce[j];
+      }
+      g = reduce3_small(g, OpSumF4(), sc, phase);
+      const float oA = A, oB = B;
+      const float tt[3] = {t1, t2, t3}, gg[3] = {gtop + g.a, gtop + g.b, gtop + g.c};
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        if (tt[k] > oA && tt[k] < oB) {
+          if (double(gg[k]) > target) {
+            if (tt[k] > A) A = tt[k], GA = gg[k];
+          } else {
+            if (tt[k] < B) B = tt[k], GB = gg[k];
+          }
+        }
+      }
+      if (A == oA && B == oB) break;  // float resolution reached
+    }
+    // ---- the bracket's entries, ordered exactly like the reference's sort
+    if (tid == 0) {
+      sc->ncand = 0;
+      sc->res_ok = 0;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < kPer; ++j) {
+      if (cx[j] >= A && cx[j] < B) {
+        const int pos = atomicAdd(&sc->ncand, 1);
+        if (pos < kCandMax) {
+          sc->cand_x[pos] = cx[j];
+          sc->cand_e[pos] = ce[j];
+          sc->cand_i[pos] = __ldcg(&list[j * kT3 + tid].idx);
+        }
+      }
+    }
+    __syncthreads();
+    const int n = sc->ncand;
+    bool solved = false;
+    if (n <= kCandMax) {
+      int Pn = 16;
+      while (Pn < n) Pn <<= 1;
+      const int parts = kT3 / Pn;  // 1..16 threads share one candidate (same warp)
+      const int t = tid / parts, part = tid - t * parts;
+      double cum = 0.0;
+      float ex = 0.0f, xx = 0.0f;
+      int ii = 0;
+      if (t < n) {
+        ex = sc->cand_e[t], xx = sc->cand_x[t], ii = sc->cand_i[t];
+        for (int j = part; j < n; j += parts) {
+          const float xj = sc->cand_x[j];
+          const int ij = sc->cand_i[j];
+          if (xj > xx || (xj == xx && ij <= ii)) cum += double(sc->cand_e[j]);
+        }
+      }
+      for (int o = parts >> 1; o > 0; o >>= 1) cum += __shfl_xor_sync(0xffffffffu, cum, o);
+      const double incl = double(GB) + cum;
+      if (t < n && part == 0 && incl > target && !(incl - double(ex) > target)) {
+        sc->res_x = xx;
+        sc->res_i = ii;
+        sc->res_Z = float(incl);
+        sc->res_ok = 1;
+      }
+      __syncthreads();
+      if (sc->res_ok) {
+        solved = true;
+        rec.Z = sc->res_Z;
+        rec.xstar = sc->res_x;
+        rec.istar = sc->res_i;
+      }
+    }
+    if (stats && tid == 0) atomicAdd(&stats[18], n);
+    if (!solved) {
+      // crowded bracket (ties): bisection on K = (okey(x) << 32) | ~index over the list entries
+      if (stats && tid == 0) atomicAdd(&stats[17], 1);
+      unsigned long long klo = (unsigned long long)okey(A) << 32, khi = (unsigned long long)okey(B) << 32;
+      auto F = [&](unsigned long long K) {
+        double s = 0.0;
+#pragma unroll
+        for (int j = 0; j < kPer; ++j) {
+          if (cx[j] >= A && cx[j] < B) {
+            const unsigned idx = unsigned(__ldcg(&list[j * kT3 + tid].idx));
+            const unsigned long long kk = ((unsigned long long)okey(cx[j]) << 32) | (0xffffffffu - idx);
+            if (kk >= K) s += double(ce[j]);
+          }
+        }
+        return double(GB) + reduce3_small(s, OpSumD(), sc, phase);
+      };
+#pragma unroll 1
+      while (khi - klo > 1ull) {
+        const unsigned long long mid = klo + ((khi - klo) >> 1);
+        if (F(mid) > target) klo = mid;
+        else khi = mid;
+      }
+      rec.Z = float(F(klo));
+      rec.xstar = okey_inv(unsigned(klo >> 32));
+      rec.istar = int(0xffffffffu - unsigned(klo & 0xffffffffull));
+    }
+  } else {
+    // one float value A holds more entries than the list can: count them in index order
+    if (stats && tid == 0) atomicAdd(&stats[19], 1);
+    const float eA = row_exp(A, m0);
+    int ilo = -1, ihi = V - 1;  // smallest I with GB + eA * #{A <= x < B, idx <= I} > target
+    auto C = [&](int I) {
+      float cnt = 0.0f;
+      for (int i0 = 4 * tid; i0 < V; i0 += 4 * kT3) {
+        float4 v = load4_scaled<TIn>(row + i0, temp);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (f4c(v, k) >= A && f4c(v, k) < B && i0 + k <= I) cnt += 1.0f;
+      }
+      return reduce3_small(cnt, OpSumF(), sc, phase);
+    };
+#pragma unroll 1
+    while (ihi - ilo > 1) {
+      const int mid = ilo + ((ihi - ilo) >> 1);
+      if (double(GB) + double(eA) * double(C(mid)) > target) ihi = mid;
+      else ilo = mid;
+    }
+    rec.Z = float(double(GB) + double(eA) * double(C(ihi)));
+    rec.xstar = A;
+    rec.istar = ihi;
+  }
+  *theta_out = rec.xstar;
+  __syncthreads();
+}
+
+template <class TIn>
+__device__ __forceinline__ const TIn* split_row(const SplitParams& P, RowJob jb) {
+  return jb.is_target
+             ? reinterpret_cast<const TIn*>(P.target) + (long long)jb.b * P.t_sb + (long long)jb.j * P.t_ss
+             : reinterpret_cast<const TIn*>(P.draft) + (long long)jb.b * P.d_sb + (long long)jb.j * P.d_ss;
+}
+
+// ---------------------------------------------------------------------------
+// kernel 1: slice scan + (last block of a row) row resolve
+// ---------------------------------------------------------------------------
+template <class TIn>
+__global__ void __launch_bounds__(kT3, 4) row_scan_kernel(const __grid_constant__ SplitParams P) {
+  __shared__ float col_x[kCol3 * kT3];
+  __shared__ int col_i[kCol3 * kT3];
+  __shared__ float ovf_x[kOvf3];
+  __shared__ int ovf_i[kOvf3];
+  __shared__ Scratch3 sc;
+
+  const int tid = threadIdx.x;
+  const int slice = blockIdx.x, job = blockIdx.y;
+  const int V = P.V, gamma = P.gamma;
+  const RowJob jb = decode_job(job, gamma);
+  const TIn* row = split_row<TIn>(P, jb);
+  const float temp = jb.is_target ? P.t_temp : P.d_temp;
+  const float top_p = jb.is_target ? P.t_top_p : P.d_top_p;
+  const bool nucleus = top_p > 0.0f;
+
+  // prediction of this launch (built by the previous one's seq_sample_kernel): exponent offset, window
+  const uint4 h = __ldg(reinterpret_cast<const uint4*>(&P.hints[jb.is_target]));
+  const bool warm = int(h.w) != 0;
+  float m0 = warm ? __uint_as_float(h.x) : 0.0f;
+  float dens = warm ? __uint_as_float(h.z) : 0.0f;
+  float lo = INFINITY, hi = INFINITY;
+  if (nucleus && warm && dens > 0.0f) {
+    const float hw = __ldg(&P.hints[jb.is_target].hw);
+    lo = __uint_as_float(h.y) - hw, hi = __uint_as_float(h.y) + hw;
+  }
+  if (tid == 0) sc.novf = 0;
+  __syncthreads();
+
+  // ---- this block's slice: eight independent 128-bit loads per thread, then arithmetic
+  const int s0 = slice * kSlice;
+  float4 v[8];
+#pragma unroll
+  for (int u = 0; u < 8; ++u) {
+    const int i0 = s0 + u * 4 * kT3 + 4 * tid;
+    if (i0 < V) v[u] = load4_scaled<TIn>(row + i0, temp);
+  }
+  float mx = -INFINITY, z = 0.0f, ghi = 0.0f, gwin = 0.0f;
+  int cnt = 0;
+#pragma unroll
+  for (int u = 0; u < 8; ++u) {
+    const int i0 = s0 + u * 4 * kT3 + 4 * tid;
+    if (i0 < V) {
+      mx = fmaxf(mx, fmaxf(fmaxf(v[u].x, v[u].y), fmaxf(v[u].z, v[u].w)));
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float x = f4c(v[u], k);
+        const float e = row_exp(x, m0);
+        z += e;
+        const bool above = x >= hi;
+        if (above) ghi += e;
+        if (x >= lo && !above) {  // rare: a window entry, staged in this thread's column
+          gwin += e;
+          if (cnt < kCol3) {
+            col_x[cnt * kT3 + tid] = x;
+            col_i[cnt * kT3 + tid] = i0 + k;
+          } else {
+            const int pos = atomicAdd(&sc.novf, 1);
+            if (pos < kOvf3) {
+              ovf_x[pos] = x;
+              ovf_i[pos] = i0 + k;
+            }
+          }
+          ++cnt;
+        }
+      }
+    }
+  }
+  int phase = 0;
+  R8 r;
+  r.v[0] = mx, r.v[1] = z, r.v[2] = ghi, r.v[3] = gwin, r.v[4] = float(cnt);
+  r.v[5] = r.v[6] = r.v[7] = 0.0f;
+  r = reduce3(r, &sc, phase);
+  const int ncta = int(r.v[4]);
+
+  // ---- append the staged entries to the row's list: one global atomic per block
+  ListEntry* list = P.lists + (long long)job * kListCap;
+  if (ncta > 0) {
+    const int mine = cnt < kCol3 ? cnt : kCol3;
+    int incl = mine;  // exclusive offset of this thread's column entries among the block's
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int o = __shfl_up_sync(0xffffffffu, incl, d);
+      if ((tid & 31) >= d) incl += o;
+    }
+    if ((tid & 31) == 31) sc.wsum[tid >> 5] = incl;
+    if (tid == 0) {
+      // a block whose staging overflowed marks the list incomplete by over-reserving
+      const int reserve = sc.novf > kOvf3 ? kListCap + 1 : ncta;
+      sc.base = atomicAdd(&P.row_count[job], reserve);
+    }
+    __syncthreads();
+    int off = incl - mine;
+    int colsum = 0;
+#pragma unroll
+    for (int w = 0; w < kW3; ++w) {
+      if (w < (tid >> 5)) off += sc.wsum[w];
+      colsum += sc.wsum[w];
+    }
+    const int base = sc.base;
+    for (int j = 0; j < mine; ++j) {
+      const int pos = base + off + j;
+      if (pos < kListCap) list[pos] = ListEntry{col_x[j * kT3 + tid], col_i[j * kT3 + tid]};
+    }
+    const int nov = sc.novf < kOvf3 ? sc.novf : kOvf3;
+    for (int t = tid; t < nov; t += kT3) {
+      const int pos = base + colsum + t;
+      if (pos < kListCap) list[pos] = ListEntry{ovf_x[t], ovf_i[t]};
+    }
+  }
+  if (tid == 0) {
+    P.partials[(long long)job * P.S + slice] = RowPartial{r.v[0], r.v[1], r.v[2], r.v[3]};
+  }
+  __syncthreads();
+  if (tid == 0) {
+    __threadfence();  // cumulative: the barrier ordered every thread's list writes before it
+    sc.last = (atomicAdd(&P.row_arrive[job], 1) == P.S - 1);
+  }
+  __syncthreads();
+  if (!sc.last) return;
+
+  // ---- this block finished the row: combine the slices and resolve it
+  __threadfence();
+  R8 c;
+  c.v[0] = -INFINITY;
+  c.v[1] = c.v[2] = c.v[3] = c.v[4] = c.v[5] = c.v[6] = c.v[7] = 0.0f;
+  for (int s = tid; s < P.S; s += kT3) {
+    const float4 q = __ldcg(reinterpret_cast<const float4*>(&P.partials[(long long)job * P.S + s]));
+    c.v[0] = fmaxf(c.v[0], q.x), c.v[1] += q.y, c.v[2] += q.z, c.v[3] += q.w;
+  }
+  c = reduce3(c, &sc, phase);
+  Pass3 pr;
+  pr.mx = c.v[0], pr.z = c.v[1], pr.ghi = c.v[2], pr.gwin = c.v[3];
+  pr.n = *reinterpret_cast<volatile int*>(&P.row_count[job]);
+  if (!(fabsf(pr.mx * kLog2e - m0) <= 32.0f) || !(pr.z < INFINITY) || !(pr.z > 0.0f)) {
+    // the predicted offset was far from this row's maximum: redo the pass with the exact one
+    m0 = pr.mx * kLog2e;
+    pr = rescan_row<TIn>(row, V, temp, m0, lo, hi, list, &P.row_count[job], &sc, phase);
+  }
+  RowRecord rec;
+  rec.m0 = m0;
+  rec.Z = pr.z;
+  rec.xstar = -INFINITY;
+  rec.istar = 0x7fffffff;
+  rec.sel = 0.0f;
+  rec.mxl = pr.mx * kLog2e;
+  rec.dens = 0.0f;
+  float theta = pr.mx;
+  if (nucleus)
+    resolve_row3<TIn>(row, V, temp, top_p, m0, pr, lo, hi, dens, list, &P.row_count[job], &sc, phase, rec, &theta,
+                      &dens, P.stats);
+  if (tid == 0) {
+    if (jb.j < gamma) {
+      const long long tok = P.tokens[(long long)jb.b * P.tok_sb + jb.j];
+      if (tok >= 0 && tok < V) {
+        const float x = scale_logit(to_f32(__ldcg(row + tok)), temp);
+        const float e = kept(rec, x, int(tok)) ? row_exp(x, m0) : 0.0f;
+        rec.sel = __fdiv_rn(e, rec.Z);
+      }
+    }
+    rec.dens = (nucleus && rec.xstar > -INFINITY) ? dens : 0.0f;
+    store_record(&P.records[job], rec);
+    P.row_count[job] = 0;
+    P.row_arrive[job] = 0;
+  }
+}
+
+// ---------------------------------------------------------------------------
+// kernel 2: accept tests, leading run, sliced token draw
+// ---------------------------------------------------------------------------
+struct SampleAcc {
+  float mass;
+  unsigned long long key;  // (bits(d / noise) << 32) | ~index, d > 0
+  unsigned long long bd;   // (okey(p - q) << 32) | ~index      (zero-mass fallback: first argmax of p - q)
+};
+
+template <class TIn>
+__global__ void __launch_bounds__(kT3, 4) seq_sample_kernel(const __grid_constant__ SplitParams P) {
+  __shared__ Scratch3 sc;
+  __shared__ unsigned long long wkey[kW3], wbd[kW3];
+  __shared__ float wmass[kW3];
+  const int tid = threadIdx.x;
+  const int slice = blockIdx.x, b = blockIdx.y;
+  const int gamma = P.gamma, V = P.V;
+  const int base = b * (2 * gamma + 1);
+
+  if (slice == 0 && b == 0) {
+    // prediction for the next launch, per row kind: mean exponent offset, mean / spread of the
+    // nucleus boundary and mean list density over this launch's rows (fixed order: deterministic)
+    int phase = 0;
+    const int rows = P.B * (2 * gamma + 1);
+    for (int kind = 0; kind < 2; ++kind) {
+      R8 a;
+      a.v[0] = -INFINITY;
+      for (int i = 1; i < 8; ++i) a.v[i] = 0.0f;
+      for (int job = tid; job < rows; job += kT3) {
+        if (decode_job(job, gamma).is_target != kind) continue;
+        const RowRecord rc = load_record(&P.records[job]);
+        a.v[1] += 1.0f;
+        a.v[2] += rc.mxl;
+        if (rc.dens > 0.0f) {
+          a.v[3] += 1.0f;
+          a.v[4] += rc.xstar;
+          a.v[5] += rc.xstar * rc.xstar;
+          a.v[6] += rc.dens;
+        }
+      }
+      a = reduce3(a, &sc, phase);
+      if (tid == 0 && a.v[1] > 0.0f) {
+        StreamHint hn;
+        hn.m0 = a.v[2] / a.v[1];
+        hn.theta = 0.0f, hn.dens = 0.0f, hn.hw = 0.0f;
+        hn.valid = 1;
+        hn.pad[0] = hn.pad[1] = hn.pad[2] = 0;
+        if (a.v[3] > 0.0f) {
+          const float mean = a.v[4] / a.v[3];
+          const float var = fmaxf(a.v[5] / a.v[3] - mean * mean, 0.0f);
+          hn.theta = mean;
+          hn.dens = a.v[6] / a.v[3];
+          // three standard deviations, at least ~200 entries, at most ~1800 entries per side
+          hn.hw = fminf(fminf(fmaxf(3.0f * sqrtf(var), 200.0f / hn.dens), 1800.0f / hn.dens), 8.0f);
+        }
+        P.hints[kind] = hn;
+      }
+    }
+    __syncthreads();
+  }
+  if (tid < gamma) {
+    const RowRecord rq = load_record(&P.records[base + 2 * tid]);
+    const RowRecord rp = load_record(&P.records[base + 2 * tid + 1]);
+    const int accept = P.r[(long long)b * P.r_sb + tid] <= __fdiv_rn(rp.sel, rq.sel);  // raw IEEE division
+    sc.seq_acc[tid] = accept;
+    if (slice == 0) {
+      const long long o = (long long)b * gamma + tid;
+      P.accept_mask[o] = (unsigned char)accept;
+      P.sel_p[o] = rp.sel;
+      P.sel_q[o] = rq.sel;
+    }
+  }
+  __syncthreads();
+  int n = 0;
+  while (n < gamma && sc.seq_acc[n] != 0) ++n;
+  const bool bonus = (n == gamma);
+  const RowRecord rp = load_record(&P.records[base + (bonus ? 2 * gamma : 2 * n + 1)]);
+  const RowRecord rq = bonus ? rp : load_record(&P.records[base + 2 * n]);
+  const TIn* prow = split_row<TIn>(P, RowJob{b, n, 1});
+  const TIn* qrow = bonus ? prow : split_row<TIn>(P, RowJob{b, n, 0});
+  const float* nz = P.noise + (long long)b * P.noise_sb;
+  const float invZp = __frcp_rn(rp.Z), invZq = __frcp_rn(rq.Z);
+
+  float mass = 0.0f, bkey = -1.0f, bdv = -INFINITY;
+  int bidx = 0x7fffffff, bdi = 0x7fffffff;
+  const int s0 = slice * kSlice3;
+#pragma unroll
+  for (int u = 0; u < kSlice3 / (4 * kT3); ++u) {
+    const int i0 = s0 + u * 4 * kT3 + 4 * tid;
+    if (i0 < V) {
+      float4 xp = load4_scaled<TIn>(prow + i0, P.t_temp);
+      float4 xq = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (!bonus) xq = load4_scaled<TIn>(qrow + i0, P.d_temp);
+      float4 nv = __ldg(reinterpret_cast<const float4*>(nz + i0));
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float x = f4c(xp, k);
+        float d = kept(rp, x, i0 + k) ? row_exp(x, rp.m0) * invZp : 0.0f;
+        if (!bonus) {
+          const float y = f4c(xq, k);
+          d -= kept(rq, y, i0 + k) ? row_exp(y, rq.m0) * invZq : 0.0f;
+        }
+        if (d > 0.0f) {
+          mass += d;
+          const float key = __fdividef(d, f4c(nv, k));
+          if (key > bkey || (key == bkey && i0 + k < bidx)) bkey = key, bidx = i0 + k;
+        }
+        const float dz = (d == d && fabsf(d) != INFINITY) ? d : 0.0f;
+        if (dz > bdv || (dz == bdv && i0 + k < bdi)) bdv = dz, bdi = i0 + k;
+      }
+    }
+  }
+  unsigned long long pk = bidx == 0x7fffffff ? 0ull
+                                            : ((unsigned long long)__float_as_uint(bkey) << 32) |
+                                                  (unsigned long long)(0xffffffffu - unsigned(bidx));
+  unsigned long long pb =
+      bdi == 0x7fffffff ? 0ull
+                        : ((unsigned long long)okey(bdv) << 32) | (unsigned long long)(0xffffffffu - unsigned(bdi));
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    mass += __shfl_xor_sync(0xffffffffu, mass, o);
+    const unsigned long long ok = __shfl_xor_sync(0xffffffffu, pk, o);
+    const unsigned long long ob = __shfl_xor_sync(0xffffffffu, pb, o);
+    pk = ok > pk ? ok : pk;
+    pb = ob > pb ? ob : pb;
+  }
+  if ((tid & 31) == 0) wmass[tid >> 5] = mass, wkey[tid >> 5] = pk, wbd[tid >> 5] = pb;
+  __syncthreads();
+  if (tid == 0) {
+    for (int w = 1; w < kW3; ++w) {
+      mass += wmass[w];
+      pk = wkey[w] > pk ? wkey[w] : pk;
+      pb = wbd[w] > pb ? wbd[w] : pb;
+    }
+    if (mass > 0.0f) atomicAdd(&P.seq_mass[b], mass);
+    if (pk != 0ull) atomicMax(&P.seq_key[b], pk);
+    if (pb != 0ull) atomicMax(&P.seq_bd[b], pb);
+    __threadfence();
+    if (atomicAdd(&P.seq_arrive[b], 1) == int(gridDim.x) - 1) {
+      __threadfence();
+      const float m = atomicAdd(&P.seq_mass[b], 0.0f);
+      const unsigned long long k = atomicMax(&P.seq_key[b], 0ull);
+      const unsigned long long d = atomicMax(&P.seq_bd[b], 0ull);
+      const unsigned long long win = (m > 0.0f && k != 0ull) ? k : d;
+      long long tok = win == 0ull ? 0 : (long long)(0xffffffffu - unsigned(win & 0xffffffffull));
+      P.accepted_len[b] = n;
+      P.token[b] = tok;
+      P.all_accepted[b] = (unsigned char)(n == gamma);
+      P.seq_mass[b] = 0.0f;
+      P.seq_key[b] = 0ull;
+      P.seq_bd[b] = 0ull;
+      P.seq_arrive[b] = 0;
+    }
+  }
+}
+
+}  // namespace duodec

@@ -46,7 +46,9 @@ struct RowRecord {  // 32 bytes per row job, written once, read by the block tha
   float xstar;  // last kept entry in (scaled logit descending, index ascending) order;
   int istar;    //   (-inf, INT_MAX) keeps everything
   float sel;    // probability of the drafted token of this position
-  int pad[3];
+  float mxl;    // row maximum * log2(e)            } statistics the next launch's
+  float dens;   // list entries per unit of logit    } prediction is built from
+  int pad;
 };
 
 struct StreamHint {  // per row kind, lives in the workspace, survives across launches
@@ -54,6 +56,8 @@ struct StreamHint {  // per row kind, lives in the workspace, survives across la
   float theta;  // scaled logit of the last nucleus boundary
   float dens;   // entries per unit of scaled logit around it
   int valid;
+  float hw;     // half-width of the predicted window (split kernels; 0: derive from dens)
+  int pad[3];
 };
 
 struct StreamParams {
@@ -122,12 +126,14 @@ __device__ __forceinline__ RowRecord load_record(const RowRecord* p) {
   r.xstar = __uint_as_float(a.z);
   r.istar = int(a.w);
   r.sel = __uint_as_float(b4.x);
+  r.mxl = __uint_as_float(b4.y);
+  r.dens = __uint_as_float(b4.z);
   return r;
 }
 __device__ __forceinline__ void store_record(RowRecord* p, const RowRecord& r) {
   uint4* dst = reinterpret_cast<uint4*>(p);
   dst[0] = make_uint4(__float_as_uint(r.m0), __float_as_uint(r.Z), __float_as_uint(r.xstar), unsigned(r.istar));
-  dst[1] = make_uint4(__float_as_uint(r.sel), 0u, 0u, 0u);
+  dst[1] = make_uint4(__float_as_uint(r.sel), __float_as_uint(r.mxl), __float_as_uint(r.dens), 0u);
 }
 
 struct MassBest {
@@ -739,6 +745,8 @@ __global__ void __launch_bounds__(kST, 2) verify_stream_kernel(const __grid_cons
     rec.xstar = -INFINITY;
     rec.istar = 0x7fffffff;
     rec.sel = 0.0f;
+    rec.mxl = pr.mx * kLog2e;
+    rec.dens = 0.0f;
     float theta = pr.mx;
     if (nucleus)
       resolve_nucleus<TIn>(row, V, temp, top_p, m0, pr, lo, hi, dens, pp, acc, col_x, col_i, ss, phase, rec, &theta,

@@ -4,7 +4,7 @@
 #include <vector>
 
 #include "../../include/duodec.h"
-#include "stream_kernel.cuh"
+#include "split_kernels.cuh"
 #include "stream_launch.h"
 
 namespace duodec {
@@ -47,8 +47,12 @@ int stream_sm_count() {
 
 }  // namespace
 
+constexpr int kMaxSlices = 32;  // row_scan slices the workspace is sized for (V <= 262144)
+
 size_t stream_workspace_bytes(int B, int gamma) {
-  return 2 * sizeof(StreamHint) + size_t(B) * size_t(2 * gamma + 1) * sizeof(RowRecord);
+  const size_t rows = size_t(B) * size_t(2 * gamma + 1);
+  return 4 * sizeof(StreamHint) + rows * sizeof(RowRecord) + rows * kMaxSlices * sizeof(RowPartial) + rows * 8 +
+         size_t(B) * 24 + rows * size_t(kListCap) * sizeof(ListEntry);
 }
 
 bool stream_try_launch(const StreamCall& c, int* rc) {
@@ -60,6 +64,68 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
                   (size_t(c.t_ss) * elt) % 16 == 0 && (size_t(c.d_sb) * elt) % 16 == 0 &&
                   (size_t(c.d_ss) * elt) % 16 == 0 && al16(c.noise) && (c.noise_sb % 4) == 0;
   if (!ok) return false;
+  const size_t rows = size_t(c.B) * size_t(2 * c.gamma + 1);
+  if (c.path == 1 && c.Vt <= kMaxSlices * kSlice && rows <= 65535 && c.B <= 65535) {
+    SplitParams Q;
+    Q.draft = c.draft;
+    Q.target = c.target;
+    Q.d_sb = c.d_sb;
+    Q.d_ss = c.d_ss;
+    Q.t_sb = c.t_sb;
+    Q.t_ss = c.t_ss;
+    Q.B = c.B;
+    Q.gamma = c.gamma;
+    Q.V = c.Vt;
+    Q.S = (c.Vt + kSlice - 1) / kSlice;
+    Q.tokens = reinterpret_cast<const long long*>(c.tokens);
+    Q.tok_sb = c.tok_sb;
+    Q.r = c.r;
+    Q.r_sb = c.r_sb;
+    Q.noise = c.noise;
+    Q.noise_sb = c.noise_sb;
+    Q.t_temp = c.temperature;
+    Q.t_top_p = c.top_p;
+    Q.d_temp = c.draft_temperature;
+    Q.d_top_p = c.draft_top_p;
+    Q.accept_mask = c.accept_mask;
+    Q.sel_p = c.sel_target_p;
+    Q.sel_q = c.sel_draft_p;
+    Q.accepted_len = reinterpret_cast<long long*>(c.accepted_len);
+    Q.token = reinterpret_cast<long long*>(c.token);
+    Q.all_accepted = c.all_accepted;
+    char* w = reinterpret_cast<char*>(c.workspace) + size_t(c.B) * 8 + size_t(c.B) * size_t(c.gamma + 1) * 8;
+    Q.hints = reinterpret_cast<StreamHint*>(w);
+    Q.hints_new = Q.hints + 2;
+    w += 4 * sizeof(StreamHint);
+    Q.records = reinterpret_cast<RowRecord*>(w);
+    w += rows * sizeof(RowRecord);
+    Q.partials = reinterpret_cast<RowPartial*>(w);
+    w += rows * kMaxSlices * sizeof(RowPartial);
+    Q.row_count = reinterpret_cast<int*>(w);
+    w += rows * 4;
+    Q.row_arrive = reinterpret_cast<int*>(w);
+    w += rows * 4;
+    Q.seq_key = reinterpret_cast<unsigned long long*>(w);
+    w += size_t(c.B) * 8;
+    Q.seq_bd = reinterpret_cast<unsigned long long*>(w);
+    w += size_t(c.B) * 8;
+    Q.seq_mass = reinterpret_cast<float*>(w);
+    w += size_t(c.B) * 4;
+    Q.seq_arrive = reinterpret_cast<int*>(w);
+    w += size_t(c.B) * 4;
+    Q.lists = reinterpret_cast<ListEntry*>(w);
+    Q.stats = c.stats;
+    const dim3 g1(unsigned(Q.S), unsigned(rows)), g2(unsigned((c.Vt + kSlice3 - 1) / kSlice3), unsigned(c.B));
+    if (c.dtype == DUODEC_F32) {
+      row_scan_kernel<float><<<g1, kT3, 0, c.stream>>>(Q);
+      seq_sample_kernel<float><<<g2, kT3, 0, c.stream>>>(Q);
+    } else {
+      row_scan_kernel<__nv_bfloat16><<<g1, kT3, 0, c.stream>>>(Q);
+      seq_sample_kernel<__nv_bfloat16><<<g2, kT3, 0, c.stream>>>(Q);
+    }
+    *rc = int(cudaGetLastError());
+    return true;
+  }
   StreamParams S;
   S.draft = c.draft;
   S.target = c.target;
@@ -91,7 +157,7 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
   w += size_t(c.B) * 8;
   w += size_t(c.B) * size_t(c.gamma + 1) * 8;  // (the general kernel's position tokens)
   S.hints = reinterpret_cast<StreamHint*>(w);
-  w += 2 * sizeof(StreamHint);
+  w += 4 * sizeof(StreamHint);  // (this launch's and the next launch's predictions of the split kernels)
   S.records = reinterpret_cast<RowRecord*>(w);
   S.stats = c.stats;
   const size_t smem = stream_smem_bytes();
