@@ -18,7 +18,7 @@ namespace {
 
 constexpr size_t kMaxDynSmem = 232448;  // 227 KB opt-in limit per block on sm_100
 std::atomic<int> g_team_override{0};
-std::atomic<int> g_stream_path{1};
+std::atomic<int> g_stream_path{3};
 std::atomic<int*> g_stats{nullptr};
 
 size_t team_smem_bytes(int V, int rows_resident, int C) {

@@ -137,6 +137,9 @@ struct OpMaxF {
 struct OpSumF {
   __device__ __forceinline__ float operator()(float a, float b) const { return a + b; }
 };
+struct OpSumU64 {
+  __device__ __forceinline__ unsigned long long operator()(unsigned long long a, unsigned long long b) const { return a + b; }
+};
 struct OpSumD {
   __device__ __forceinline__ double operator()(double a, double b) const { return a + b; }
 };

@@ -31,6 +31,9 @@ constexpr int kCol3 = 8;        // window entries a thread stages in its own sha
 constexpr int kOvf3 = 512;      // staged overflow entries per block
 constexpr int kSlice3 = 4096;   // row entries per seq_sample block: 4 float4 per thread and array
 
+// barrier of the 256 worker threads (named, so that a kernel may run a producer warp beside them)
+__device__ __forceinline__ void bar3() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+
 struct RowPartial {
   float mx, z, ghi, gwin;
 };
@@ -38,6 +41,9 @@ struct ListEntry {
   float x;
   int idx;
 };
+
+__device__ __forceinline__ float ld_list_x(const ListEntry* e) { return *reinterpret_cast<const volatile float*>(&e->x); }
+__device__ __forceinline__ int ld_list_i(const ListEntry* e) { return *reinterpret_cast<const volatile int*>(&e->idx); }
 
 struct SplitParams {
   const void* draft;
@@ -86,6 +92,12 @@ struct __align__(16) Scratch3 {
   int hint_ok;
   int seq_acc[64];
   int wsum[kW3];
+  unsigned long long hist[256];      // level histogram: (count << 50) | fixed-point mass
+  unsigned long long cand_f[kCandMax];
+  unsigned long long wscan[kW3];
+  unsigned long long gb_new, lastkey;
+  unsigned kmin, kmax;
+  int bstar, bcount;
 };
 
 // all-reduce of an R8 (v[0] max, v[1..7] sum) over the 256 threads; one __syncthreads, ping-pong scratch
@@ -98,7 +110,7 @@ __device__ __forceinline__ R8 reduce3(R8 a, Scratch3* sc, int& phase) {
   }
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   if (lane == 0) sc->red[phase][w] = a;
-  __syncthreads();
+  bar3();
   R8 x = sc->red[phase][lane & (kW3 - 1)];
   phase ^= 1;
 #pragma unroll
@@ -116,7 +128,7 @@ __device__ __forceinline__ T reduce3_small(T v, Op op, Scratch3* sc, int& phase)
   v = warp_allreduce(v, op);
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   if (lane == 0) *reinterpret_cast<T*>(&sc->red[phase][w]) = v;
-  __syncthreads();
+  bar3();
   T x = *reinterpret_cast<T*>(&sc->red[phase][lane & (kW3 - 1)]);
   phase ^= 1;
 #pragma unroll
@@ -131,12 +143,12 @@ struct Pass3 {
 
 // One more pass over a whole row by a single block, through L2: statistics for the window
 // [lo, hi) and its entries appended to the (emptied) global list.
-template <class TIn>
+template <class TIn, int kCap>
 __device__ __noinline__ Pass3 rescan_row(const TIn* row, int V, float temp, float m0, float lo, float hi,
                                          ListEntry* list, int* count, Scratch3* sc, int& phase) {
   const int tid = threadIdx.x;
   if (tid == 0) *count = 0;
-  __syncthreads();
+  bar3();
   float mx = -INFINITY, z = 0.0f, ghi = 0.0f, gwin = 0.0f;
   for (int c0 = 0; c0 < V; c0 += 4 * 4 * kT3) {
     float4 v[4];
@@ -160,7 +172,7 @@ __device__ __noinline__ Pass3 rescan_row(const TIn* row, int V, float temp, floa
           } else if (x >= lo) {
             gwin += e;
             const int pos = atomicAdd(count, 1);
-            if (pos < kListCap) list[pos] = ListEntry{x, i0 + k};
+            if (pos < kCap) list[pos] = ListEntry{x, i0 + k};
           }
         }
       }
@@ -176,9 +188,218 @@ __device__ __noinline__ Pass3 rescan_row(const TIn* row, int V, float temp, floa
   return p;
 }
 
+// Nucleus boundary among the n (<= kCap) entries of `list`, all of them inside [A, B), given
+// GB = mass of the row's entries >= B and the row's total mass Z:  the LAST entry, in the
+// reference's order (scaled logit descending, lowest index first), that is still kept, i.e. the
+// first whose inclusive cumulative mass exceeds target = top_p * Z.  Fills rec.{Z, xstar, istar}.
+template <int kCap>
+__device__ __noinline__ void list_select(const ListEntry* list, int nlist, float A, float B, float GB, float Zrow,
+                                         double target, float m0, Scratch3* sc, int& phase, RowRecord& rec,
+                                         int* stats) {
+  const int tid = threadIdx.x;
+  struct { float z; int n; } pr{Zrow, nlist};
+  const float lo = A;
+  // ---- boundary search on the list entries (16 per thread, in registers), in exact integer
+  // arithmetic: every entry's mass as a 38-bit fixed-point fraction of 2^ceil(log2 Z), so that
+  // sums do not depend on the order of the shared-memory atomics.  A level spreads the entries
+  // of [A, B) over 256 value buckets (mass and count packed in one 64-bit word), a suffix scan
+  // finds the bucket in which the kept mass crosses top_p * Z; with <= kCandMax entries in it
+  // the all-pairs finish below orders them exactly like the reference's sort.
+  constexpr int kPer = kCap / kT3;
+  constexpr unsigned long long kMassMask = (1ull << 50) - 1ull;
+  const int ez = int(__float_as_uint(pr.z) >> 23) - 126;               // Z = f * 2^ez, f in [0.5, 1)
+  const float S = __uint_as_float(unsigned(127 + 38 - ez) << 23);      // 2^(38 - ez)
+  const unsigned long long tgt = (unsigned long long)(target * double(S));  // floor
+  unsigned long long GBf = (unsigned long long)(double(GB) * double(S));    // floor: GBf <= tgt
+  float cx[kPer];
+  unsigned long long cf[kPer];
+#pragma unroll
+  for (int j = 0; j < kPer; ++j) {
+    const int p = j * kT3 + tid;
+    float x = -INFINITY;
+    if (p < pr.n) x = ld_list_x(&list[p]);
+    cx[j] = x;
+    cf[j] = p < pr.n ? __float2ull_rn(row_exp(x, m0) * S) : 0ull;
+  }
+  if (A < lo) A = lo;  // every list entry is inside the window
+  bool solved = false, tie_mode = false;
+  int ncand_stat = 0;
+#pragma unroll 1
+  for (int level = 0; level < 8 && !solved && !tie_mode; ++level) {
+    sc->hist[tid] = 0ull;
+    if (tid == 0) {
+      sc->bstar = -1;
+      sc->kmin = 0xffffffffu;
+      sc->kmax = 0u;
+      sc->ncand = 0;
+      sc->res_ok = 0;
+      sc->lastkey = 0xffffffffffffffffull;
+    }
+    bar3();
+    const float bsc = 256.0f / (B - A);
+#pragma unroll
+    for (int j = 0; j < kPer; ++j) {
+      if (cx[j] >= A && cx[j] < B) {
+        int bk = int((cx[j] - A) * bsc);
+        bk = bk < 0 ? 0 : (bk > 255 ? 255 : bk);
+        atomicAdd(&sc->hist[bk], cf[j] | (1ull << 50));
+      }
+    }
+    bar3();
+    // suffix scan over buckets 255..0 (thread t owns bucket 255 - t)
+    const unsigned long long hv = sc->hist[255 - tid];
+    unsigned long long inc = hv;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const unsigned long long o = __shfl_up_sync(0xffffffffu, inc, d);
+      if ((tid & 31) >= d) inc += o;
+    }
+    if ((tid & 31) == 31) sc->wscan[tid >> 5] = inc;
+    bar3();
+#pragma unroll
+    for (int w = 0; w < kW3; ++w)
+      if (w < (tid >> 5)) inc += sc->wscan[w];
+    const unsigned long long m_incl = GBf + (inc & kMassMask), m_excl = m_incl - (hv & kMassMask);
+    if ((hv >> 50) != 0ull && m_incl > tgt && m_excl <= tgt) {
+      sc->bstar = 255 - tid;
+      sc->gb_new = m_excl;
+      sc->bcount = int(hv >> 50);
+    }
+    if (tid == kT3 - 1 && m_incl <= tgt) sc->bstar = -2;  // rounding only: the whole bracket is kept
+    bar3();
+    const int bstar = sc->bstar;
+    if (bstar == -2 || bstar == -1) {
+      // keep everything down to the last entry of the bracket in the reference's order
+      unsigned long long kk = 0xffffffffffffffffull;
+#pragma unroll
+      for (int j = 0; j < kPer; ++j) {
+        if (cx[j] >= A && cx[j] < B) {
+          const unsigned idx = unsigned(ld_list_i(&list[j * kT3 + tid]));
+          const unsigned long long k2 = ((unsigned long long)okey(cx[j]) << 32) | (0xffffffffu - idx);
+          kk = k2 < kk ? k2 : kk;
+        }
+      }
+      if (kk != 0xffffffffffffffffull) atomicMin(&sc->lastkey, kk);
+      bar3();
+      const unsigned long long lk = sc->lastkey;
+      if (tid == kT3 - 1) sc->gb_new = m_incl;  // the bracket's total is this thread's inclusive sum
+      bar3();
+      if (lk != 0xffffffffffffffffull) {
+        rec.Z = float(double(sc->gb_new) / double(S));
+        rec.xstar = okey_inv(unsigned(lk >> 32));
+        rec.istar = int(0xffffffffu - unsigned(lk & 0xffffffffull));
+        solved = true;
+      } else {
+        tie_mode = true;  // empty bracket: let the generic bisection decide
+      }
+      break;
+    }
+    const int bcount = sc->bcount;
+    const unsigned long long gb_new = sc->gb_new;
+    if (bcount <= kCandMax) {
+      // ---- the bucket's entries, ordered exactly like the reference's sort
+#pragma unroll
+      for (int j = 0; j < kPer; ++j) {
+        if (cx[j] >= A && cx[j] < B) {
+          int bk = int((cx[j] - A) * bsc);
+          bk = bk < 0 ? 0 : (bk > 255 ? 255 : bk);
+          if (bk == bstar) {
+            const int pos = atomicAdd(&sc->ncand, 1);
+            sc->cand_x[pos] = cx[j];
+            sc->cand_f[pos] = cf[j];
+            sc->cand_i[pos] = ld_list_i(&list[j * kT3 + tid]);
+          }
+        }
+      }
+      bar3();
+      const int n = sc->ncand;
+      ncand_stat = n;
+      int Pn = 16;
+      while (Pn < n) Pn <<= 1;
+      const int parts = kT3 / Pn;  // 1..16 threads share one candidate (same warp)
+      const int t = tid / parts, part = tid - t * parts;
+      unsigned long long cum = 0ull, fx = 0ull;
+      float xx = 0.0f;
+      int ii = 0;
+      if (t < n) {
+        fx = sc->cand_f[t], xx = sc->cand_x[t], ii = sc->cand_i[t];
+        for (int j = part; j < n; j += parts) {
+          const float xj = sc->cand_x[j];
+          const int ij = sc->cand_i[j];
+          if (xj > xx || (xj == xx && ij <= ii)) cum += sc->cand_f[j];
+        }
+      }
+      for (int o = parts >> 1; o > 0; o >>= 1) cum += __shfl_xor_sync(0xffffffffu, cum, o);
+      const unsigned long long incl = gb_new + cum;
+      if (t < n && part == 0 && incl > tgt && incl - fx <= tgt) {
+        sc->res_x = xx;
+        sc->res_i = ii;
+        sc->gb_new = incl;
+        sc->res_ok = 1;
+      }
+      bar3();
+      if (sc->res_ok) {
+        solved = true;
+        rec.Z = float(double(sc->gb_new) / double(S));
+        rec.xstar = sc->res_x;
+        rec.istar = sc->res_i;
+      } else {
+        tie_mode = true;  // cannot happen with exact sums; stay safe
+      }
+      break;
+    }
+    // crowded bucket: shrink the bracket to the bucket's value range and go one level down
+#pragma unroll
+    for (int j = 0; j < kPer; ++j) {
+      if (cx[j] >= A && cx[j] < B) {
+        int bk = int((cx[j] - A) * bsc);
+        bk = bk < 0 ? 0 : (bk > 255 ? 255 : bk);
+        if (bk == bstar) {
+          atomicMin(&sc->kmin, okey(cx[j]));
+          atomicMax(&sc->kmax, okey(cx[j]));
+        }
+      }
+    }
+    bar3();
+    const unsigned kmin = sc->kmin, kmax = sc->kmax;
+    A = okey_inv(kmin);
+    B = nextafterf(okey_inv(kmax), INFINITY);
+    GBf = gb_new;
+    if (kmin == kmax) tie_mode = true;  // more equal values than the finish can order
+    bar3();
+  }
+  if (stats && tid == 0) atomicAdd(&stats[18], ncand_stat);
+  if (!solved) {
+    // ties / crowded bracket: bisection on K = (okey(x) << 32) | ~index over the bracket's entries
+    if (stats && tid == 0) atomicAdd(&stats[17], 1);
+    unsigned long long klo = (unsigned long long)okey(A) << 32, khi = (unsigned long long)okey(B) << 32;
+    auto F = [&](unsigned long long K) {
+      unsigned long long s = 0ull;
+#pragma unroll
+      for (int j = 0; j < kPer; ++j) {
+        if (cx[j] >= A && cx[j] < B) {
+          const unsigned idx = unsigned(ld_list_i(&list[j * kT3 + tid]));
+          const unsigned long long kk = ((unsigned long long)okey(cx[j]) << 32) | (0xffffffffu - idx);
+          if (kk >= K) s += cf[j];
+        }
+      }
+      return GBf + reduce3_small(s, OpSumU64(), sc, phase);
+    };
+#pragma unroll 1
+    while (khi - klo > 1ull) {
+      const unsigned long long mid = klo + ((khi - klo) >> 1);
+      if (F(mid) > tgt) klo = mid;
+      else khi = mid;
+    }
+    rec.Z = float(double(F(klo)) / double(S));
+    rec.xstar = okey_inv(unsigned(klo >> 32));
+    rec.istar = int(0xffffffffu - unsigned(klo & 0xffffffffull));
+  }
+}
+
 // Nucleus boundary of one row by the block that finished it; `pr` describes the pass over
 // the window [lo, hi) whose entries sit in `list`.  Fills rec.{Z, xstar, istar}.
-template <class TIn>
+template <class TIn, int kCap>
 __device__ __noinline__ void resolve_row3(const TIn* row, int V, float temp, float top_p, float m0, Pass3 pr,
                                           float lo, float hi, float dens, ListEntry* list, int* count,
                                           Scratch3* sc, int& phase, RowRecord& rec, float* theta_out,
@@ -200,7 +421,7 @@ __device__ __noinline__ void resolve_row3(const TIn* row, int V, float temp, flo
     } else if (double(pr.ghi + pr.gwin) > target) {
       if (lo > A) A = lo, GA = pr.ghi + pr.gwin;
       if (hi < B) B = hi, GB = pr.ghi;
-      list_ok = pr.n <= kListCap;
+      list_ok = pr.n <= kCap;
     } else if (lo < B) {
       B = lo, GB = pr.ghi + pr.gwin;
     }
@@ -209,154 +430,35 @@ __device__ __noinline__ void resolve_row3(const TIn* row, int V, float temp, flo
     if (nextafterf(A, INFINITY) >= B || npass >= 48) break;  // one float value left: tie mode below
     if (A == -INFINITY) {
       float step = 4.0f * float(1 << (npass < 6 ? npass : 6));
-      if (dens > 0.0f) step = fminf(step, fmaxf(2000.0f / dens, 1e-3f));
+      if (dens > 0.0f) step = fminf(step, fmaxf((0.5f * float(kCap)) / dens, 1e-3f));
       lo = B - step, hi = B;
     } else {
       const float W = B - A;
       const float est = dens > 0.0f ? dens * W : __fdividef(GA - GB, row_exp(A, m0));
-      if (est <= 2000.0f) {
+      if (est <= (0.5f * float(kCap))) {
         lo = A, hi = B;
       } else {
         const float c = A + W * __fdividef(GA - float(target), GA - GB);
-        const float h = 0.5f * W * __fdividef(2000.0f, est);
+        const float h = 0.5f * W * __fdividef((0.5f * float(kCap)), est);
         lo = fmaxf(A, c - h), hi = fminf(B, c + h);
         if (!(hi > lo)) lo = A, hi = fminf(B, nextafterf(A + 2.0f * h, INFINITY));
         if (!(hi > lo)) hi = B;
       }
     }
-    pr = rescan_row<TIn>(row, V, temp, m0, lo, hi, list, count, sc, phase);
+    pr = rescan_row<TIn, kCap>(row, V, temp, m0, lo, hi, list, count, sc, phase);
     ++npass;
   }
   *dens_out = dens;
   if (stats && tid == 0) {
     atomicAdd(&stats[npass < 15 ? npass : 15], 1);  // [0..15] rows by number of extra (L2) passes
     atomicAdd(&stats[16], 1);
+    atomicAdd(&stats[21], pr.n);
+    atomicMax(&stats[22], pr.n);
   }
 
   if (list_ok) {
-    // ---- narrow [A, B) on the list entries, held in registers (16 per thread)
-    constexpr int kPer = kListCap / kT3;
-    const float gtop = pr.ghi;  // every list entry is below the window's upper edge
-    float cx[kPer], ce[kPer];
-#pragma unroll
-    for (int j = 0; j < kPer; ++j) {
-      const int p = j * kT3 + tid;
-      float x = -INFINITY;
-      if (p < pr.n) x = __ldcg(&list[p].x);
-      cx[j] = x;
-      ce[j] = p < pr.n ? row_exp(x, m0) : 0.0f;
-    }
-#pragma unroll 1
-    for (int it = 0; it < 24; ++it) {
-      if ((GA - GB) <= kCandGoal * row_exp(A, m0)) break;
-      const float W = B - A;
-      const float c = A + W * __fdividef(GA - float(target), GA - GB);
-      const float d = 0.125f * W;
-      const float a1 = nextafterf(A, INFINITY), b1 = B;
-      float t1 = fminf(fmaxf(c - d, a1), b1), t2 = fminf(fmaxf(c, a1), b1), t3 = fminf(fmaxf(c + d, a1), b1);
-      if (!(t2 > t1)) t2 = A + 0.5f * W;
-      if (!(t3 > t2)) t3 = A + 0.75f * W;
-      F4 g{0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-      for (int j = 0; j < kPer; ++j) {
-        if (cx[j] >= t1) g.a += ce[j];
-        if (cx[j] >= t2) g.b += ce[j];
-        if (cx[j] >= t3) g.c += ce[j];
-      }
-      g = reduce3_small(g, OpSumF4(), sc, phase);
-      const float oA = A, oB = B;
-      const float tt[3] = {t1, t2, t3}, gg[3] = {gtop + g.a, gtop + g.b, gtop + g.c};
-#pragma unroll
-      for (int k = 0; k < 3; ++k) {
-        if (tt[k] > oA && tt[k] < oB) {
-          if (double(gg[k]) > target) {
-            if (tt[k] > A) A = tt[k], GA = gg[k];
-          } else {
-            if (tt[k] < B) B = tt[k], GB = gg[k];
-          }
-        }
-      }
-      if (A == oA && B == oB) break;  // float resolution reached
-    }
-    // ---- the bracket's entries, ordered exactly like the reference's sort
-    if (tid == 0) {
-      sc->ncand = 0;
-      sc->res_ok = 0;
-    }
-    __syncthreads();
-#pragma unroll
-    for (int j = 0; j < kPer; ++j) {
-      if (cx[j] >= A && cx[j] < B) {
-        const int pos = atomicAdd(&sc->ncand, 1);
-        if (pos < kCandMax) {
-          sc->cand_x[pos] = cx[j];
-          sc->cand_e[pos] = ce[j];
-          sc->cand_i[pos] = __ldcg(&list[j * kT3 + tid].idx);
-        }
-      }
-    }
-    __syncthreads();
-    const int n = sc->ncand;
-    bool solved = false;
-    if (n <= kCandMax) {
-      int Pn = 16;
-      while (Pn < n) Pn <<= 1;
-      const int parts = kT3 / Pn;  // 1..16 threads share one candidate (same warp)
-      const int t = tid / parts, part = tid - t * parts;
-      double cum = 0.0;
-      float ex = 0.0f, xx = 0.0f;
-      int ii = 0;
-      if (t < n) {
-        ex = sc->cand_e[t], xx = sc->cand_x[t], ii = sc->cand_i[t];
-        for (int j = part; j < n; j += parts) {
-          const float xj = sc->cand_x[j];
-          const int ij = sc->cand_i[j];
-          if (xj > xx || (xj == xx && ij <= ii)) cum += double(sc->cand_e[j]);
-        }
-      }
-      for (int o = parts >> 1; o > 0; o >>= 1) cum += __shfl_xor_sync(0xffffffffu, cum, o);
-      const double incl = double(GB) + cum;
-      if (t < n && part == 0 && incl > target && !(incl - double(ex) > target)) {
-        sc->res_x = xx;
-        sc->res_i = ii;
-        sc->res_Z = float(incl);
-        sc->res_ok = 1;
-      }
-      __syncthreads();
-      if (sc->res_ok) {
-        solved = true;
-        rec.Z = sc->res_Z;
-        rec.xstar = sc->res_x;
-        rec.istar = sc->res_i;
-      }
-    }
-    if (stats && tid == 0) atomicAdd(&stats[18], n);
-    if (!solved) {
-      // crowded bracket (ties): bisection on K = (okey(x) << 32) | ~index over the list entries
-      if (stats && tid == 0) atomicAdd(&stats[17], 1);
-      unsigned long long klo = (unsigned long long)okey(A) << 32, khi = (unsigned long long)okey(B) << 32;
-      auto F = [&](unsigned long long K) {
-        double s = 0.0;
-#pragma unroll
-        for (int j = 0; j < kPer; ++j) {
-          if (cx[j] >= A && cx[j] < B) {
-            const unsigned idx = unsigned(__ldcg(&list[j * kT3 + tid].idx));
-            const unsigned long long kk = ((unsigned long long)okey(cx[j]) << 32) | (0xffffffffu - idx);
-            if (kk >= K) s += double(ce[j]);
-          }
-        }
-        return double(GB) + reduce3_small(s, OpSumD(), sc, phase);
-      };
-#pragma unroll 1
-      while (khi - klo > 1ull) {
-        const unsigned long long mid = klo + ((khi - klo) >> 1);
-        if (F(mid) > target) klo = mid;
-        else khi = mid;
-      }
-      rec.Z = float(F(klo));
-      rec.xstar = okey_inv(unsigned(klo >> 32));
-      rec.istar = int(0xffffffffu - unsigned(klo & 0xffffffffull));
-    }
+    if (A < lo) A = lo;  // every list entry is inside the window
+    list_select<kCap>(list, pr.n, A, B, GB, pr.z, target, m0, sc, phase, rec, stats);
   } else {
     // one float value A holds more entries than the list can: count them in index order
     if (stats && tid == 0) atomicAdd(&stats[19], 1);
@@ -383,7 +485,7 @@ __device__ __noinline__ void resolve_row3(const TIn* row, int V, float temp, flo
     rec.istar = ihi;
   }
   *theta_out = rec.xstar;
-  __syncthreads();
+  bar3();
 }
 
 template <class TIn>
@@ -424,7 +526,7 @@ __global__ void __launch_bounds__(kT3, 4) row_scan_kernel(const __grid_constant_
     lo = __uint_as_float(h.y) - hw, hi = __uint_as_float(h.y) + hw;
   }
   if (tid == 0) sc.novf = 0;
-  __syncthreads();
+  bar3();
 
   // ---- this block's slice: eight independent 128-bit loads per thread, then arithmetic
   const int s0 = slice * kSlice;
@@ -488,7 +590,7 @@ __global__ void __launch_bounds__(kT3, 4) row_scan_kernel(const __grid_constant_
       const int reserve = sc.novf > kOvf3 ? kListCap + 1 : ncta;
       sc.base = atomicAdd(&P.row_count[job], reserve);
     }
-    __syncthreads();
+    bar3();
     int off = incl - mine;
     int colsum = 0;
 #pragma unroll
@@ -510,12 +612,12 @@ __global__ void __launch_bounds__(kT3, 4) row_scan_kernel(const __grid_constant_
   if (tid == 0) {
     P.partials[(long long)job * P.S + slice] = RowPartial{r.v[0], r.v[1], r.v[2], r.v[3]};
   }
-  __syncthreads();
+  bar3();
   if (tid == 0) {
     __threadfence();  // cumulative: the barrier ordered every thread's list writes before it
     sc.last = (atomicAdd(&P.row_arrive[job], 1) == P.S - 1);
   }
-  __syncthreads();
+  bar3();
   if (!sc.last) return;
 
   // ---- this block finished the row: combine the slices and resolve it
@@ -534,7 +636,7 @@ __global__ void __launch_bounds__(kT3, 4) row_scan_kernel(const __grid_constant_
   if (!(fabsf(pr.mx * kLog2e - m0) <= 32.0f) || !(pr.z < INFINITY) || !(pr.z > 0.0f)) {
     // the predicted offset was far from this row's maximum: redo the pass with the exact one
     m0 = pr.mx * kLog2e;
-    pr = rescan_row<TIn>(row, V, temp, m0, lo, hi, list, &P.row_count[job], &sc, phase);
+    pr = rescan_row<TIn, kListCap>(row, V, temp, m0, lo, hi, list, &P.row_count[job], &sc, phase);
   }
   RowRecord rec;
   rec.m0 = m0;
@@ -546,7 +648,7 @@ __global__ void __launch_bounds__(kT3, 4) row_scan_kernel(const __grid_constant_
   rec.dens = 0.0f;
   float theta = pr.mx;
   if (nucleus)
-    resolve_row3<TIn>(row, V, temp, top_p, m0, pr, lo, hi, dens, list, &P.row_count[job], &sc, phase, rec, &theta,
+    resolve_row3<TIn, kListCap>(row, V, temp, top_p, m0, pr, lo, hi, dens, list, &P.row_count[job], &sc, phase, rec, &theta,
                       &dens, P.stats);
   if (tid == 0) {
     if (jb.j < gamma) {
@@ -616,13 +718,13 @@ __global__ void __launch_bounds__(kT3, 4) seq_sample_kernel(const __grid_constan
           const float var = fmaxf(a.v[5] / a.v[3] - mean * mean, 0.0f);
           hn.theta = mean;
           hn.dens = a.v[6] / a.v[3];
-          // three standard deviations, at least ~200 entries, at most ~1800 entries per side
-          hn.hw = fminf(fminf(fmaxf(3.0f * sqrtf(var), 200.0f / hn.dens), 1800.0f / hn.dens), 8.0f);
+          // four standard deviations, at least ~200 entries, at most ~1800 entries per side
+          hn.hw = fminf(fminf(fmaxf(4.0f * sqrtf(var), 200.0f / hn.dens), 1800.0f / hn.dens), 8.0f);
         }
         P.hints[kind] = hn;
       }
     }
-    __syncthreads();
+    bar3();
   }
   if (tid < gamma) {
     const RowRecord rq = load_record(&P.records[base + 2 * tid]);
@@ -636,7 +738,7 @@ __global__ void __launch_bounds__(kT3, 4) seq_sample_kernel(const __grid_constan
       P.sel_q[o] = rq.sel;
     }
   }
-  __syncthreads();
+  bar3();
   int n = 0;
   while (n < gamma && sc.seq_acc[n] != 0) ++n;
   const bool bonus = (n == gamma);
@@ -691,7 +793,7 @@ __global__ void __launch_bounds__(kT3, 4) seq_sample_kernel(const __grid_constan
     pb = ob > pb ? ob : pb;
   }
   if ((tid & 31) == 0) wmass[tid >> 5] = mass, wkey[tid >> 5] = pk, wbd[tid >> 5] = pb;
-  __syncthreads();
+  bar3();
   if (tid == 0) {
     for (int w = 1; w < kW3; ++w) {
       mass += wmass[w];

@@ -55,9 +55,15 @@ def set_team_size(team: int) -> None:
     lib.duodec_set_team_size(int(team))
 
 
-def set_stream_path(enabled: bool) -> None:
-    """Test hook: False forces the general team kernel for verify_fused."""
-    lib.duodec_set_stream_path(1 if enabled else 0)
+FAST_PATH = 3  # row-ring scan kernel + sliced sample kernel
+
+
+def set_stream_path(path) -> None:
+    """Test hook: device path of verify_fused.  True: the default fast path (3, row-ring scan kernel);
+    False / 0: the general team kernel; 1: sliced scan kernel; 2: first-generation persistent kernel."""
+    if isinstance(path, bool):
+        path = FAST_PATH if path else 0
+    lib.duodec_set_stream_path(int(path))
 
 
 def set_stats_buffer(buf: Optional[torch.Tensor]) -> None:

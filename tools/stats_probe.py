@@ -12,11 +12,11 @@ dev = torch.device("cuda:0")
 sets = bench.make_sets(dev, 4, 1234)
 stats = torch.zeros(32, dtype=torch.int32, device=dev)
 ops.set_stats_buffer(stats)
-for it in range(3):
+for it in range(8):
     stats.zero_()
     out = ops.verify_fused(*sets[it % 4], bench.TEMP, bench.TOP_K, bench.TOP_P)
     torch.cuda.synchronize()
-    print("  cycles/16 summed: ring pass, reduce, resolve, publish, close:", stats[20:25].tolist())
+    print("  list entries: sum", int(stats[21]), "max", int(stats[22]))
     print("launch", it, "rows by extra L2 passes", stats[:16].tolist(), "rows", int(stats[16]), "cands", int(stats[18]))
 print("passes histogram", stats[:16].tolist(), "fast", int(stats[16]), "bisect", int(stats[17]), "cands", int(stats[18]))
 ops.set_stats_buffer(None)
