@@ -8,7 +8,7 @@
 //                    threads take 8 entries each per stage (two conflict-free 128-bit shared loads).
 //
 //   A row without nucleus filter is one pass:  Z = sum 2^(x*log2e - M0).
-//   A row with top-p is streamed TWICE (the second time it comes out of L2, HBM sees it once):
+//   A row with top-p is read TWICE (the second time out of L2 with plain loads, HBM sees it once):
 //     pass 1  e = 2^(x*log2e - M0) is added to a PER-THREAD histogram of 32 buckets, one per
 //             unit of the exponent t = x*log2e - M0 (rounded to nearest, clamped), in shared
 //             memory (hist[bucket][thread]: bank = thread, no conflicts, no atomics).  The
@@ -36,7 +36,7 @@ constexpr int kStageBytes = kStageElems * 4;      // sized for fp32 rows; bf16 r
 #define DUODEC_RING_STAGES 8
 #endif
 constexpr int kStages = DUODEC_RING_STAGES;
-constexpr int kRingListCap = 2048;                // entries of the boundary bucket the block's list can hold
+constexpr int kRingPer = kListCap / kT3;           // boundary-bucket entries a worker thread can keep (its list column)
 constexpr int kRT = kT3 + 32;                     // 256 workers + the producer warp
 constexpr int kHB = 32;                           // histogram buckets
 constexpr float kHTmin = -27.0f, kHTmax = 4.0f;   // bucket b holds round(t) == b - 27 (ends clamped)
@@ -66,6 +66,29 @@ struct OpMinMax {
 __device__ __forceinline__ int hist_bits(float t) {
   return __float_as_int(fminf(fmaxf(t, kHTmin), kHTmax) + kHMagic);
 }
+
+// one ring stage = 8 entries per worker thread: two 128-bit shared loads (entries 4*tid.. and
+// 4*(256+tid)..); the tail of the last stage of a row is stale shared memory and is skipped.
+#define RING_STAGE_BEGIN(c)                                                                   \
+  const unsigned slot = seq % unsigned(kStages);                                              \
+  mbar_wait(&rs->full[slot], (seq / unsigned(kStages)) & 1u);                                  \
+  const unsigned char* st = ring + size_t(slot) * kStageBytes;                                \
+  float4 va = unpack4<TIn>(st + size_t(tid * 4) * kElt);                                      \
+  float4 vb = unpack4<TIn>(st + size_t((kT3 + tid) * 4) * kElt);                              \
+  const int ia = (c) * kStageElems + tid * 4, ib = ia + kT3 * 4;                               \
+  if (temp != 1.0f) {                                                                         \
+    va.x = __fdiv_rn(va.x, temp), va.y = __fdiv_rn(va.y, temp);                               \
+    va.z = __fdiv_rn(va.z, temp), va.w = __fdiv_rn(va.w, temp);                               \
+    vb.x = __fdiv_rn(vb.x, temp), vb.y = __fdiv_rn(vb.y, temp);                               \
+    vb.z = __fdiv_rn(vb.z, temp), vb.w = __fdiv_rn(vb.w, temp);                               \
+  }
+#define RING_STAGE_END()                                                                      \
+  __syncwarp();                                                                               \
+  if (lane == 0) mbar_arrive(&rs->empty[slot]);                                               \
+  ++seq;
+#define RING_EACH(F)                                                                          \
+  if (ia < V) { F(va.x, ia) F(va.y, ia + 1) F(va.z, ia + 2) F(va.w, ia + 3) }                 \
+  if (ib < V) { F(vb.x, ib) F(vb.y, ib + 1) F(vb.z, ib + 2) F(vb.w, ib + 3) }
 
 template <class TIn>
 __global__ void __launch_bounds__(kRT, 2) row_ring_kernel(const __grid_constant__ SplitParams P) {
@@ -98,8 +121,7 @@ __global__ void __launch_bounds__(kRT, 2) row_ring_kernel(const __grid_constant_
       for (int job = blockIdx.x; job < njobs; job += gridDim.x) {
         const RowJob jb = decode_job(job, gamma);
         const TIn* row = split_row<TIn>(P, jb);
-        const int passes = (jb.is_target ? P.t_top_p : P.d_top_p) > 0.0f ? 2 : 1;
-        for (int ps = 0; ps < passes; ++ps) {
+        {
           for (int c = 0; c < nchunk; ++c, ++seq) {
             const unsigned slot = seq % unsigned(kStages);
             if (seq >= unsigned(kStages)) mbar_wait(&rs->empty[slot], ((seq / unsigned(kStages)) - 1u) & 1u);
@@ -144,37 +166,6 @@ __global__ void __launch_bounds__(kRT, 2) row_ring_kernel(const __grid_constant_
     const uint4 h = __ldg(reinterpret_cast<const uint4*>(&P.hints[jb.is_target]));
     float m0 = int(h.w) != 0 ? __uint_as_float(h.x) : 0.0f;
 
-    // one stage of the ring: 8 entries per thread, handed to f(x, index)
-    auto stage = [&](int c, auto&& f) {
-      const unsigned slot = seq % unsigned(kStages);
-      mbar_wait(&rs->full[slot], (seq / unsigned(kStages)) & 1u);
-      const unsigned char* st = ring + size_t(slot) * kStageBytes;
-      const int e0 = c * kStageElems;
-      float4 v[2];
-#pragma unroll
-      for (int u = 0; u < 2; ++u) {
-        const int o = (u * kT3 + tid) * 4;
-        if (e0 + o < V) v[u] = unpack4<TIn>(st + size_t(o) * kElt);
-      }
-#pragma unroll
-      for (int u = 0; u < 2; ++u) {
-        const int i0 = e0 + (u * kT3 + tid) * 4;
-        if (i0 < V) {
-          if (temp != 1.0f) {
-            v[u].x = __fdiv_rn(v[u].x, temp);
-            v[u].y = __fdiv_rn(v[u].y, temp);
-            v[u].z = __fdiv_rn(v[u].z, temp);
-            v[u].w = __fdiv_rn(v[u].w, temp);
-          }
-#pragma unroll
-          for (int k = 0; k < 4; ++k) f(f4c(v[u], k), i0 + k);
-        }
-      }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&rs->empty[slot]);
-      ++seq;
-    };
-
     RowRecord rec;
     rec.m0 = m0;
     rec.xstar = -INFINITY;
@@ -182,16 +173,26 @@ __global__ void __launch_bounds__(kRT, 2) row_ring_kernel(const __grid_constant_
     rec.sel = 0.0f;
     rec.dens = 0.0f;
     bool slow = false;
+    long long tk0 = 0;
+    if (P.stats && tid == 0) tk0 = clock64();
+    auto tick = [&](int k) {  // tuning hook: cycles per phase summed over blocks (units of 16 cycles)
+      if (P.stats && tid == 0) {
+        const long long t = clock64();
+        atomicAdd(&P.stats[k], int((t - tk0) >> 4));
+        tk0 = t;
+      }
+    };
     float Z = 0.0f, mxl = m0;
 
     if (!nucleus) {
       float z = 0.0f, mx = -INFINITY;
 #pragma unroll 1
-      for (int c = 0; c < nchunk; ++c)
-        stage(c, [&](float x, int) {
-          z += row_exp(x, m0);
-          mx = fmaxf(mx, x);
-        });
+      for (int c = 0; c < nchunk; ++c) {
+        RING_STAGE_BEGIN(c)
+#define F_PLAIN(x, i) z += row_exp(x, m0), mx = fmaxf(mx, x);
+        RING_EACH(F_PLAIN)
+        RING_STAGE_END()
+      }
       R8 r;
       r.v[0] = mx, r.v[1] = z;
       r.v[2] = r.v[3] = r.v[4] = r.v[5] = r.v[6] = r.v[7] = 0.0f;
@@ -202,13 +203,18 @@ __global__ void __launch_bounds__(kRT, 2) row_ring_kernel(const __grid_constant_
     } else {
       // ---- pass 1: per-thread mass histogram over the exponent
 #pragma unroll 1
-      for (int c = 0; c < nchunk; ++c)
-        stage(c, [&](float x, int) {
-          const float t = fmaf(x, kLog2e, -m0);
-          const float e = ex2_approx(t);
-          float* a = hp + (hist_bits(t) - bits0) * kT3;
-          *a += e;
-        });
+      for (int c = 0; c < nchunk; ++c) {
+        RING_STAGE_BEGIN(c)
+#define F_HIST(x, i)                                  \
+  {                                                   \
+    const float t = fmaf(x, kLog2e, -m0);             \
+    float* a = hp + (hist_bits(t) - bits0) * kT3;     \
+    *a += ex2_approx(t);                              \
+  }
+        RING_EACH(F_HIST)
+        RING_STAGE_END()
+      }
+      tick(24);
       bar3();
       // bucket sums: warp w owns buckets 4w .. 4w+3 (fixed order: deterministic)
 #pragma unroll
@@ -225,64 +231,84 @@ __global__ void __launch_bounds__(kRT, 2) row_ring_kernel(const __grid_constant_
         if (lane == 0) rs->hsum[b] = s;
       }
       bar3();
-      int btop = -1;
-#pragma unroll 1
-      for (int b = kHB - 1; b >= 0; --b) {
-        const float hb = rs->hsum[b];
-        Z += hb;
-        if (btop < 0 && hb > 0.0f) btop = b;
+      // every warp scans the 32 bucket sums from the top (lane l holds bucket 31 - l): fixed shuffle
+      // tree, the same values in every warp
+      const float hb = rs->hsum[kHB - 1 - lane];
+      float incl = hb;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const float o = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += o;
       }
-      mxl = m0 + (btop == kHB - 1 ? fmaxf(kHTmax, log2f(rs->hsum[kHB - 1])) : float(btop) + kHTmin);
+      Z = __shfl_sync(0xffffffffu, incl, 31);
+      const unsigned nonempty = __ballot_sync(0xffffffffu, hb > 0.0f);
+      const int btop = nonempty ? kHB - 1 - (__ffs(nonempty) - 1) : -1;
+      mxl = m0 + (btop == kHB - 1 ? fmaxf(kHTmax, log2f(__shfl_sync(0xffffffffu, hb, 0))) : float(btop) + kHTmin);
       slow = !(Z < INFINITY) || !(Z > 0.0f);
       const double target = double(top_p) * double(Z);
       int bstar = -1;
       float GB = 0.0f;
       if (!slow && target < double(Z)) {
-        float S = 0.0f;
-#pragma unroll 1
-        for (int b = kHB - 1; b >= 0; --b) {
-          const float incl = S + rs->hsum[b];
-          if (double(incl) > target) {
-            bstar = b, GB = S;
-            break;
-          }
-          S = incl;
+        const unsigned crossed = __ballot_sync(0xffffffffu, double(incl) > target);
+        if (crossed) {
+          const int l = __ffs(crossed) - 1;  // first bucket from the top whose inclusive mass exceeds the target
+          bstar = kHB - 1 - l;
+          GB = __shfl_sync(0xffffffffu, incl - hb, l);
         }
         if (bstar <= 0) slow = true;  // the lower end bucket is unbounded below
       }
+      tick(25);
       // ---- pass 2: the boundary bucket's entries (always consumed: the producer streams them)
       const int want = bstar > 0 && !slow ? bits0 + bstar : 0x7fffffff;
-      float hmx = -INFINITY, hngmn = -INFINITY;
+      int mycnt = 0;
+      ListEntry* col = list + tid;  // this thread's column: entry j at list[j * 256 + tid]
+#define F_PICK(x, i)                                                  \
+  if (hist_bits(fmaf(x, kLog2e, -m0)) == want) {                      \
+    if (mycnt < kRingPer) col[mycnt * kT3] = ListEntry{x, i};         \
+    ++mycnt;                                                          \
+  }
+      if (want != 0x7fffffff) {
+        // the row again, out of L2, with plain 128-bit loads: eight per thread in flight
 #pragma unroll 1
-      for (int c = 0; c < nchunk; ++c)
-        stage(c, [&](float x, int idx) {
-          if (hist_bits(fmaf(x, kLog2e, -m0)) == want) {
-            const int pos = atomicAdd(&rs->nlist, 1);
-            if (pos < kRingListCap) list[pos] = ListEntry{x, idx};
-            hmx = fmaxf(hmx, x);
-            hngmn = fmaxf(hngmn, -x);
+        for (int c0 = 0; c0 < V; c0 += 8 * 4 * kT3) {
+          float4 v[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int i0 = c0 + (u * kT3 + tid) * 4;
+            if (i0 < V) v[u] = load4_scaled<TIn>(row + i0, temp);
           }
-        });
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int i0 = c0 + (u * kT3 + tid) * 4;
+            if (i0 < V) {
+              F_PICK(v[u].x, i0) F_PICK(v[u].y, i0 + 1) F_PICK(v[u].z, i0 + 2) F_PICK(v[u].w, i0 + 3)
+            }
+          }
+        }
+      }
+      tick(26);
       if (bstar > 0 && !slow) {
-        const MinMax mm = reduce3_small(MinMax{hmx, hngmn}, OpMinMax(), sc, phase);  // (barrier: list complete)
-        const int n = *reinterpret_cast<volatile int*>(&rs->nlist);
-        if (n > kRingListCap || n <= 0) {
+        const int cmax = reduce3_small(mycnt, OpMaxI(), sc, phase);
+        if (cmax > kRingPer) {
           slow = true;
         } else {
-          if (P.stats && tid == 0) {
-            atomicAdd(&P.stats[0], 1);
-            atomicAdd(&P.stats[16], 1);
-            atomicAdd(&P.stats[21], n);
-            atomicMax(&P.stats[22], n);
+          if (P.stats) {
+            const int n = reduce3_small(mycnt, OpSumI(), sc, phase);
+            if (tid == 0) {
+              atomicAdd(&P.stats[0], 1);
+              atomicAdd(&P.stats[16], 1);
+              atomicAdd(&P.stats[21], n);
+              atomicMax(&P.stats[22], n);
+            }
           }
-          list_select<kRingListCap>(list, n, -mm.ngmn, nextafterf(mm.mx, INFINITY), GB, Z, target, m0, sc, phase,
-                                    rec, P.stats);
+          list_select<kListCap>(list, 0, mycnt, 0.0f, 0.0f, GB, Z, target, m0, sc, phase, rec, P.stats);
         }
       } else {
         rec.Z = Z;  // top_p >= 1 keeps everything (or slow)
       }
     }
     if (!nucleus) rec.Z = Z;
+    tick(27);
     rec.mxl = mxl;
     if (slow) {
       // general search: exact row maximum first, then the windowed search through L2

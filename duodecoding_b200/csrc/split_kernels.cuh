@@ -193,7 +193,8 @@ __device__ __noinline__ Pass3 rescan_row(const TIn* row, int V, float temp, floa
 // reference's order (scaled logit descending, lowest index first), that is still kept, i.e. the
 // first whose inclusive cumulative mass exceeds target = top_p * Z.  Fills rec.{Z, xstar, istar}.
 template <int kCap>
-__device__ __noinline__ void list_select(const ListEntry* list, int nlist, float A, float B, float GB, float Zrow,
+__device__ __noinline__ void list_select(const ListEntry* list, int nlist, int mycnt, float A, float B, float GB,
+                                         float Zrow,
                                          double target, float m0, Scratch3* sc, int& phase, RowRecord& rec,
                                          int* stats) {
   const int tid = threadIdx.x;
@@ -211,15 +212,25 @@ __device__ __noinline__ void list_select(const ListEntry* list, int nlist, float
   const float S = __uint_as_float(unsigned(127 + 38 - ez) << 23);      // 2^(38 - ez)
   const unsigned long long tgt = (unsigned long long)(target * double(S));  // floor
   unsigned long long GBf = (unsigned long long)(double(GB) * double(S));    // floor: GBf <= tgt
+  // entry j of this thread sits at list[j * 256 + tid]; it exists if j < mycnt (per-thread columns,
+  // mycnt >= 0) or j * 256 + tid < nlist (one shared list, mycnt < 0)
   float cx[kPer];
-  unsigned long long cf[kPer];
+  auto fx = [&](float x) { return __float2ull_rn(row_exp(x, m0) * S); };  // fixed-point mass of an entry
+  float emx = -INFINITY, engmn = -INFINITY;
 #pragma unroll
   for (int j = 0; j < kPer; ++j) {
     const int p = j * kT3 + tid;
+    const bool have = mycnt >= 0 ? j < mycnt : p < pr.n;
     float x = -INFINITY;
-    if (p < pr.n) x = ld_list_x(&list[p]);
+    if (have) {
+      x = ld_list_x(&list[p]);
+      emx = fmaxf(emx, x), engmn = fmaxf(engmn, -x);
+    }
     cx[j] = x;
-    cf[j] = p < pr.n ? __float2ull_rn(row_exp(x, m0) * S) : 0ull;
+  }
+  if (mycnt >= 0) {  // the bracket is the value range of the entries
+    const F4 mm = reduce3_small(F4{emx, engmn, 0.0f, 0.0f}, OpMaxF4(), sc, phase);
+    A = -mm.b, B = nextafterf(mm.a, INFINITY);
   }
   if (A < lo) A = lo;  // every list entry is inside the window
   bool solved = false, tie_mode = false;
@@ -242,7 +253,7 @@ __device__ __noinline__ void list_select(const ListEntry* list, int nlist, float
       if (cx[j] >= A && cx[j] < B) {
         int bk = int((cx[j] - A) * bsc);
         bk = bk < 0 ? 0 : (bk > 255 ? 255 : bk);
-        atomicAdd(&sc->hist[bk], cf[j] | (1ull << 50));
+        atomicAdd(&sc->hist[bk], fx(cx[j]) | (1ull << 50));
       }
     }
     bar3();
@@ -306,7 +317,7 @@ __device__ __noinline__ void list_select(const ListEntry* list, int nlist, float
           if (bk == bstar) {
             const int pos = atomicAdd(&sc->ncand, 1);
             sc->cand_x[pos] = cx[j];
-            sc->cand_f[pos] = cf[j];
+            sc->cand_f[pos] = fx(cx[j]);
             sc->cand_i[pos] = ld_list_i(&list[j * kT3 + tid]);
           }
         }
@@ -380,7 +391,7 @@ __device__ __noinline__ void list_select(const ListEntry* list, int nlist, float
         if (cx[j] >= A && cx[j] < B) {
           const unsigned idx = unsigned(ld_list_i(&list[j * kT3 + tid]));
           const unsigned long long kk = ((unsigned long long)okey(cx[j]) << 32) | (0xffffffffu - idx);
-          if (kk >= K) s += cf[j];
+          if (kk >= K) s += fx(cx[j]);
         }
       }
       return GBf + reduce3_small(s, OpSumU64(), sc, phase);
@@ -458,7 +469,7 @@ __device__ __noinline__ void resolve_row3(const TIn* row, int V, float temp, flo
 
   if (list_ok) {
     if (A < lo) A = lo;  // every list entry is inside the window
-    list_select<kCap>(list, pr.n, A, B, GB, pr.z, target, m0, sc, phase, rec, stats);
+    list_select<kCap>(list, pr.n, -1, A, B, GB, pr.z, target, m0, sc, phase, rec, stats);
   } else {
     // one float value A holds more entries than the list can: count them in index order
     if (stats && tid == 0) atomicAdd(&stats[19], 1);

@@ -293,6 +293,11 @@ __device__ __forceinline__ PassResult reduce_pass(const ScanAcc& a, int pp, Stre
 struct F4 {
   float a, b, c, d;
 };
+struct OpMaxF4 {
+  __device__ __forceinline__ F4 operator()(F4 x, F4 y) const {
+    return F4{fmaxf(x.a, y.a), fmaxf(x.b, y.b), fmaxf(x.c, y.c), fmaxf(x.d, y.d)};
+  }
+};
 struct OpSumF4 {
   __device__ __forceinline__ F4 operator()(F4 x, F4 y) const { return F4{x.a + y.a, x.b + y.b, x.c + y.c, x.d + y.d}; }
 };
