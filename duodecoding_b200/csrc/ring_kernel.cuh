@@ -8,7 +8,7 @@
 //                    threads take 8 entries each per stage (two conflict-free 128-bit shared loads).
 //
 //   A row without nucleus filter is one pass:  Z = sum 2^(x*log2e - M0).
-//   A row with top-p is read TWICE (the second time out of L2 with plain loads, HBM sees it once):
+//   A row with top-p is streamed TWICE (the second time it comes out of L2, HBM sees it once):
 //     pass 1  e = 2^(x*log2e - M0) is added to a PER-THREAD histogram of 32 buckets, one per
 //             unit of the exponent t = x*log2e - M0 (rounded to nearest, clamped), in shared
 //             memory (hist[bucket][thread]: bank = thread, no conflicts, no atomics).  The
@@ -121,7 +121,8 @@ __global__ void __launch_bounds__(kRT, 2) row_ring_kernel(const __grid_constant_
       for (int job = blockIdx.x; job < njobs; job += gridDim.x) {
         const RowJob jb = decode_job(job, gamma);
         const TIn* row = split_row<TIn>(P, jb);
-        {
+        const int passes = (jb.is_target ? P.t_top_p : P.d_top_p) > 0.0f ? 2 : 1;
+        for (int ps = 0; ps < passes; ++ps) {
           for (int c = 0; c < nchunk; ++c, ++seq) {
             const unsigned slot = seq % unsigned(kStages);
             if (seq >= unsigned(kStages)) mbar_wait(&rs->empty[slot], ((seq / unsigned(kStages)) - 1u) & 1u);
@@ -173,15 +174,18 @@ __global__ void __launch_bounds__(kRT, 2) row_ring_kernel(const __grid_constant_
     rec.sel = 0.0f;
     rec.dens = 0.0f;
     bool slow = false;
+#ifdef DUODEC_TICKS
     long long tk0 = 0;
     if (P.stats && tid == 0) tk0 = clock64();
-    auto tick = [&](int k) {  // tuning hook: cycles per phase summed over blocks (units of 16 cycles)
-      if (P.stats && tid == 0) {
-        const long long t = clock64();
-        atomicAdd(&P.stats[k], int((t - tk0) >> 4));
-        tk0 = t;
-      }
-    };
+#define tick(k)                                            \
+  if (P.stats && tid == 0) {                               \
+    const long long t_ = clock64();                        \
+    atomicAdd(&P.stats[k], int((t_ - tk0) >> 4));          \
+    tk0 = t_;                                              \
+  }
+#else
+#define tick(k)
+#endif
     float Z = 0.0f, mxl = m0;
 
     if (!nucleus) {
@@ -267,24 +271,11 @@ __global__ void __launch_bounds__(kRT, 2) row_ring_kernel(const __grid_constant_
     if (mycnt < kRingPer) col[mycnt * kT3] = ListEntry{x, i};         \
     ++mycnt;                                                          \
   }
-      if (want != 0x7fffffff) {
-        // the row again, out of L2, with plain 128-bit loads: eight per thread in flight
 #pragma unroll 1
-        for (int c0 = 0; c0 < V; c0 += 8 * 4 * kT3) {
-          float4 v[8];
-#pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            const int i0 = c0 + (u * kT3 + tid) * 4;
-            if (i0 < V) v[u] = load4_scaled<TIn>(row + i0, temp);
-          }
-#pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            const int i0 = c0 + (u * kT3 + tid) * 4;
-            if (i0 < V) {
-              F_PICK(v[u].x, i0) F_PICK(v[u].y, i0 + 1) F_PICK(v[u].z, i0 + 2) F_PICK(v[u].w, i0 + 3)
-            }
-          }
-        }
+      for (int c = 0; c < nchunk; ++c) {  // always consumed: the producer streams the row twice
+        RING_STAGE_BEGIN(c)
+        RING_EACH(F_PICK)
+        RING_STAGE_END()
       }
       tick(26);
       if (bstar > 0 && !slow) {
@@ -301,7 +292,7 @@ __global__ void __launch_bounds__(kRT, 2) row_ring_kernel(const __grid_constant_
               atomicMax(&P.stats[22], n);
             }
           }
-          list_select<kListCap>(list, 0, mycnt, 0.0f, 0.0f, GB, Z, target, m0, sc, phase, rec, P.stats);
+          list_select_body<kListCap>(list, 0, mycnt, 0.0f, 0.0f, GB, Z, target, m0, sc, phase, rec, P.stats);
         }
       } else {
         rec.Z = Z;  // top_p >= 1 keeps everything (or slow)

@@ -193,10 +193,9 @@ __device__ __noinline__ Pass3 rescan_row(const TIn* row, int V, float temp, floa
 // reference's order (scaled logit descending, lowest index first), that is still kept, i.e. the
 // first whose inclusive cumulative mass exceeds target = top_p * Z.  Fills rec.{Z, xstar, istar}.
 template <int kCap>
-__device__ __noinline__ void list_select(const ListEntry* list, int nlist, int mycnt, float A, float B, float GB,
-                                         float Zrow,
-                                         double target, float m0, Scratch3* sc, int& phase, RowRecord& rec,
-                                         int* stats) {
+__device__ __forceinline__ void list_select_body(const ListEntry* list, int nlist, int mycnt, float A, float B,
+                                                 float GB, float Zrow, double target, float m0, Scratch3* sc,
+                                                 int& phase, RowRecord& rec, int* stats) {
   const int tid = threadIdx.x;
   struct { float z; int n; } pr{Zrow, nlist};
   const float lo = A;
@@ -406,6 +405,13 @@ __device__ __noinline__ void list_select(const ListEntry* list, int nlist, int m
     rec.xstar = okey_inv(unsigned(klo >> 32));
     rec.istar = int(0xffffffffu - unsigned(klo & 0xffffffffull));
   }
+}
+
+template <int kCap>
+__device__ __noinline__ void list_select(const ListEntry* list, int nlist, int mycnt, float A, float B, float GB,
+                                         float Zrow, double target, float m0, Scratch3* sc, int& phase,
+                                         RowRecord& rec, int* stats) {
+  list_select_body<kCap>(list, nlist, mycnt, A, B, GB, Zrow, target, m0, sc, phase, rec, stats);
 }
 
 // Nucleus boundary of one row by the block that finished it; `pr` describes the pass over

@@ -5,6 +5,7 @@
 
 #include "../../include/duodec.h"
 #include "ring_kernel.cuh"
+#include "resident_kernel.cuh"
 #include "stream_launch.h"
 
 namespace duodec {
@@ -65,9 +66,10 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
                   (size_t(c.d_ss) * elt) % 16 == 0 && al16(c.noise) && (c.noise_sb % 4) == 0;
   if (!ok) return false;
   const size_t rows = size_t(c.B) * size_t(2 * c.gamma + 1);
+  const bool resident = c.path == 4 && c.B <= 65535;
   const bool ring = (c.path == 3 || (c.path == 1 && c.Vt > kMaxSlices * kSlice)) && c.B <= 65535;
   const bool split = c.path == 1 && c.Vt <= kMaxSlices * kSlice && rows <= 65535 && c.B <= 65535;
-  if (ring || split) {
+  if (ring || split || resident) {
     SplitParams Q;
     Q.draft = c.draft;
     Q.target = c.target;
@@ -118,10 +120,31 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
     Q.lists = reinterpret_cast<ListEntry*>(w);
     Q.stats = c.stats;
     const dim3 g1(unsigned(Q.S), unsigned(rows)), g2(unsigned((c.Vt + kSlice3 - 1) / kSlice3), unsigned(c.B));
+    if (resident) {
+      const size_t smem = resident::ring_smem_bytes();
+      const int sms = stream_sm_count();
+      const int grid = int(rows) < sms ? int(rows) : sms;  // one block per SM
+      cudaError_t e;
+      if (c.dtype == DUODEC_F32) {
+        e = ensure_stream_smem(reinterpret_cast<const void*>(resident::row_resident_kernel<float>), smem);
+        if (e == cudaSuccess) {
+          resident::row_resident_kernel<float><<<grid, resident::kRT, smem, c.stream>>>(Q);
+          seq_sample_kernel<float><<<g2, kT3, 0, c.stream>>>(Q);
+        }
+      } else {
+        e = ensure_stream_smem(reinterpret_cast<const void*>(resident::row_resident_kernel<__nv_bfloat16>), smem);
+        if (e == cudaSuccess) {
+          resident::row_resident_kernel<__nv_bfloat16><<<grid, resident::kRT, smem, c.stream>>>(Q);
+          seq_sample_kernel<__nv_bfloat16><<<g2, kT3, 0, c.stream>>>(Q);
+        }
+      }
+      *rc = int(e != cudaSuccess ? e : cudaGetLastError());
+      return true;
+    }
     if (ring) {
       const size_t smem = ring_smem_bytes();
       const int sms = stream_sm_count();
-      const int grid = int(rows) < 2 * sms ? int(rows) : 2 * sms;
+      const int grid = int(rows) < 2 * sms ? int(rows) : 2 * sms;  // two blocks per SM
       cudaError_t e;
       if (c.dtype == DUODEC_F32) {
         e = ensure_stream_smem(reinterpret_cast<const void*>(row_ring_kernel<float>), smem);

@@ -60,7 +60,8 @@ FAST_PATH = 3  # row-ring scan kernel + sliced sample kernel
 
 def set_stream_path(path) -> None:
     """Test hook: device path of verify_fused.  True: the default fast path (3, row-ring scan kernel);
-    False / 0: the general team kernel; 1: sliced scan kernel; 2: first-generation persistent kernel."""
+    False / 0: the general team kernel; 1: sliced scan kernel; 2: first-generation persistent kernel;
+    4: resident-row scan kernel (experimental)."""
     if isinstance(path, bool):
         path = FAST_PATH if path else 0
     lib.duodec_set_stream_path(int(path))

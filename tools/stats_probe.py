@@ -16,7 +16,7 @@ for it in range(8):
     stats.zero_()
     out = ops.verify_fused(*sets[it % 4], bench.TEMP, bench.TOP_K, bench.TOP_P)
     torch.cuda.synchronize()
-    print("  list entries: sum", int(stats[21]), "max", int(stats[22]), " us per block (296 blocks): pass1 %.1f reduce %.1f pass2 %.1f resolve %.1f" % tuple(float(x) * 16 / 296 / 1965 for x in stats[24:28].tolist()))
+    print("  list entries: sum", int(stats[21]), "max", int(stats[22]), " us per block (148 blocks): P1 %.1f close %.1f levels %.1f select %.1f  [fine %.1f close %.1f take %.1f reduce %.1f]" % tuple(float(x) * 16 / 148 / 1965 for x in stats[24:32].tolist()))
     print("launch", it, "rows by extra L2 passes", stats[:16].tolist(), "rows", int(stats[16]), "cands", int(stats[18]))
 print("passes histogram", stats[:16].tolist(), "fast", int(stats[16]), "bisect", int(stats[17]), "cands", int(stats[18]))
 ops.set_stats_buffer(None)
