@@ -27,6 +27,7 @@ SIGNATURES = {
     "duodec_team_size": (c_int, [c_int, c_int]),
     "duodec_set_team_size": (None, [c_int]),
     "duodec_set_stream_path": (None, [c_int]),
+    "duodec_set_phase_mask": (None, [c_int]),
     "duodec_set_stats_buffer": (None, [c_void_p]),
     "duodec_norm_logits": (
         c_int,

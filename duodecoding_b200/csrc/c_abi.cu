@@ -19,6 +19,7 @@ namespace {
 constexpr size_t kMaxDynSmem = 232448;  // 227 KB opt-in limit per block on sm_100
 std::atomic<int> g_team_override{0};
 std::atomic<int> g_stream_path{3};
+std::atomic<int> g_phase_mask{3};
 std::atomic<int*> g_stats{nullptr};
 
 size_t team_smem_bytes(int V, int rows_resident, int C) {
@@ -112,6 +113,7 @@ int duodec_team_size(int V, int rows_resident) {
 void duodec_set_team_size(int team) { g_team_override.store(team); }
 
 void duodec_set_stream_path(int enabled) { g_stream_path.store(enabled); }
+void duodec_set_phase_mask(int mask) { g_phase_mask.store(mask); }
 
 void duodec_set_stats_buffer(int* device_counters) { g_stats.store(device_counters); }
 
@@ -188,7 +190,7 @@ int duodec_verify_fused(const void* draft, const void* target, int dtype, int64_
     c.draft_temperature = draft_temperature, c.draft_top_k = draft_top_k, c.draft_top_p = draft_top_p;
     c.accept_mask = accept_mask, c.sel_target_p = sel_target_p, c.sel_draft_p = sel_draft_p;
     c.accepted_len = accepted_len, c.token = token, c.all_accepted = all_accepted;
-    c.workspace = workspace, c.stats = g_stats.load(), c.path = g_stream_path.load(), c.stream = st;
+    c.workspace = workspace, c.stats = g_stats.load(), c.path = g_stream_path.load(), c.phases = g_phase_mask.load(), c.stream = st;
     int rc = 0;
     if (stream_try_launch(c, &rc)) return rc;
   }

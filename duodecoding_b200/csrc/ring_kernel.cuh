@@ -2,7 +2,7 @@
 //
 //   row_ring_kernel  persistent grid, two blocks per SM; every block OWNS whole logit rows
 //                    (row = block + k * grid), so the hot loop has no global atomics, fences or
-//                    cross-block hand-offs.  One producer lane keeps a ring of kStages 8 KB
+//                    cross-block hand-offs.  One producer lane keeps a ring of kStages (4) 8 KB
 //                    shared-memory stages full with TMA bulk copies (cp.async.bulk + mbarrier
 //                    complete_tx), running ahead across passes and row boundaries; 256 worker
 //                    threads take 8 entries each per stage (two conflict-free 128-bit shared loads).
@@ -33,7 +33,7 @@ namespace duodec {
 constexpr int kStageElems = 2048;                 // row entries per ring stage: 8 per worker thread
 constexpr int kStageBytes = kStageElems * 4;      // sized for fp32 rows; bf16 rows fill half of it
 #ifndef DUODEC_RING_STAGES
-#define DUODEC_RING_STAGES 8
+#define DUODEC_RING_STAGES 4
 #endif
 constexpr int kStages = DUODEC_RING_STAGES;
 constexpr int kRingPer = kListCap / kT3;           // boundary-bucket entries a worker thread can keep (its list column)

@@ -128,14 +128,14 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
       if (c.dtype == DUODEC_F32) {
         e = ensure_stream_smem(reinterpret_cast<const void*>(resident::row_resident_kernel<float>), smem);
         if (e == cudaSuccess) {
-          resident::row_resident_kernel<float><<<grid, resident::kRT, smem, c.stream>>>(Q);
-          seq_sample_kernel<float><<<g2, kT3, 0, c.stream>>>(Q);
+          if (c.phases & 1) resident::row_resident_kernel<float><<<grid, resident::kRT, smem, c.stream>>>(Q);
+          if (c.phases & 2) seq_sample_kernel<float><<<g2, kT3, 0, c.stream>>>(Q);
         }
       } else {
         e = ensure_stream_smem(reinterpret_cast<const void*>(resident::row_resident_kernel<__nv_bfloat16>), smem);
         if (e == cudaSuccess) {
-          resident::row_resident_kernel<__nv_bfloat16><<<grid, resident::kRT, smem, c.stream>>>(Q);
-          seq_sample_kernel<__nv_bfloat16><<<g2, kT3, 0, c.stream>>>(Q);
+          if (c.phases & 1) resident::row_resident_kernel<__nv_bfloat16><<<grid, resident::kRT, smem, c.stream>>>(Q);
+          if (c.phases & 2) seq_sample_kernel<__nv_bfloat16><<<g2, kT3, 0, c.stream>>>(Q);
         }
       }
       *rc = int(e != cudaSuccess ? e : cudaGetLastError());
@@ -149,25 +149,25 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
       if (c.dtype == DUODEC_F32) {
         e = ensure_stream_smem(reinterpret_cast<const void*>(row_ring_kernel<float>), smem);
         if (e == cudaSuccess) {
-          row_ring_kernel<float><<<grid, kRT, smem, c.stream>>>(Q);
-          seq_sample_kernel<float><<<g2, kT3, 0, c.stream>>>(Q);
+          if (c.phases & 1) row_ring_kernel<float><<<grid, kRT, smem, c.stream>>>(Q);
+          if (c.phases & 2) seq_sample_kernel<float><<<g2, kT3, 0, c.stream>>>(Q);
         }
       } else {
         e = ensure_stream_smem(reinterpret_cast<const void*>(row_ring_kernel<__nv_bfloat16>), smem);
         if (e == cudaSuccess) {
-          row_ring_kernel<__nv_bfloat16><<<grid, kRT, smem, c.stream>>>(Q);
-          seq_sample_kernel<__nv_bfloat16><<<g2, kT3, 0, c.stream>>>(Q);
+          if (c.phases & 1) row_ring_kernel<__nv_bfloat16><<<grid, kRT, smem, c.stream>>>(Q);
+          if (c.phases & 2) seq_sample_kernel<__nv_bfloat16><<<g2, kT3, 0, c.stream>>>(Q);
         }
       }
       *rc = int(e != cudaSuccess ? e : cudaGetLastError());
       return true;
     }
     if (c.dtype == DUODEC_F32) {
-      row_scan_kernel<float><<<g1, kT3, 0, c.stream>>>(Q);
-      seq_sample_kernel<float><<<g2, kT3, 0, c.stream>>>(Q);
+      if (c.phases & 1) row_scan_kernel<float><<<g1, kT3, 0, c.stream>>>(Q);
+      if (c.phases & 2) seq_sample_kernel<float><<<g2, kT3, 0, c.stream>>>(Q);
     } else {
-      row_scan_kernel<__nv_bfloat16><<<g1, kT3, 0, c.stream>>>(Q);
-      seq_sample_kernel<__nv_bfloat16><<<g2, kT3, 0, c.stream>>>(Q);
+      if (c.phases & 1) row_scan_kernel<__nv_bfloat16><<<g1, kT3, 0, c.stream>>>(Q);
+      if (c.phases & 2) seq_sample_kernel<__nv_bfloat16><<<g2, kT3, 0, c.stream>>>(Q);
     }
     *rc = int(cudaGetLastError());
     return true;

@@ -34,6 +34,7 @@ struct StreamCall {  // the arguments of duodec_verify_fused, verbatim
   uint8_t* all_accepted;
   void* workspace;
   int* stats;
+  int phases;  // bit 0: scan kernel, bit 1: sample kernel (3 = both; measurement hook)
   int path;  // 1: split kernels (row_scan + seq_sample), 2: persistent row-stream kernel
   cudaStream_t stream;
 };

@@ -67,6 +67,11 @@ def set_stream_path(path) -> None:
     lib.duodec_set_stream_path(int(path))
 
 
+def set_phase_mask(mask: int) -> None:
+    """Measurement hook: 1 = scan kernel only, 2 = sample kernel only, 3 = both (default)."""
+    lib.duodec_set_phase_mask(int(mask))
+
+
 def set_stats_buffer(buf: Optional[torch.Tensor]) -> None:
     """Tuning hook: int32[32] CUDA tensor the row-stream kernel counts into (None disables)."""
     if buf is not None and (not buf.is_cuda or buf.dtype != torch.int32 or buf.numel() < 32):

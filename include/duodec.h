@@ -46,10 +46,15 @@ int duodec_team_size(int V, int rows_resident);
 /* Override the team-size heuristic (0 = automatic).  Tuning / test hook. */
 void duodec_set_team_size(int team);
 
-/* duodec_verify_fused has two device paths: the persistent row-stream kernel
- * (rows <= 32768 entries, 16-byte aligned, no top-k, T > 0) and the general
- * team kernel.  0 forces the general kernel (test hook); default 1. */
+/* Device path of duodec_verify_fused for calls that qualify (equal vocabularies, 16-byte
+ * aligned rows, no top-k, T > 0): 3 (default) row-ring scan kernel + sliced sample kernel,
+ * 4 resident-row scan kernel, 1 sliced scan kernel, 2 first-generation persistent kernel;
+ * 0 forces the general team kernel, which every other call takes anyway (test hook). */
 void duodec_set_stream_path(int enabled);
+
+/* Measurement hook for the fast paths: bit 0 launches the scan kernel, bit 1 the sample kernel
+ * (default 3 = both).  bench.py uses 1 to time the dominant kernel alone for the roofline. */
+void duodec_set_phase_mask(int mask);
 
 /* Tuning hook: device int[32] that the row-stream kernel increments (0..15: rows by number of
  * nucleus search passes, 16: rows finished by the candidate ordering, 17: rows finished by the
