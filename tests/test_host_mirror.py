@@ -115,3 +115,25 @@ def test_transfer_size_rule_and_identity_paths():
     assert communication.apply_top_k_compression(p1, 10) is p1 and communication.apply_top_k_compression(None, 3).numel() == 0
     with pytest.raises(ValueError):
         communication.compress_rebuild_probs(torch.rand(4, 10), 3)
+
+
+def test_install_rebinds_reference_modules_when_present():
+    import os
+    import sys
+
+    if not os.path.isdir("/root/reference/src"):
+        pytest.skip("the reference tree only exists in the build container")
+    sys.path.insert(0, "/root/reference")
+    try:
+        from duodecoding_b200.install import install, uninstall
+        done = install("src")
+        import src.decoding_ops as ref_ops
+        import src.utils as ref_utils
+        assert ref_ops.finalize_verification is decoding_ops.finalize_verification
+        assert ref_utils.norm_logits.__module__ == "duodecoding_b200.utils" and len(done["decoding_ops"]) >= 12
+        with patch("src.decoding_ops.sample", return_value=torch.tensor([[1]])):  # late binding survives
+            pass
+        uninstall()
+        assert ref_ops.finalize_verification is not decoding_ops.finalize_verification
+    finally:
+        sys.path.remove("/root/reference")
