@@ -9,6 +9,7 @@
 #include "../../include/duodec.h"
 #include "prob_kernels.cuh"
 #include "row_kernels.cuh"
+#include "shard_kernels.cuh"
 #include "stream_launch.h"
 #include "verify_kernels.cuh"
 
@@ -358,6 +359,72 @@ int duodec_kv_truncate(int32_t* seq_len, const int64_t* end_pos_vec, int64_t end
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   kv_truncate_kernel<<<(B + 255) / 256, 256, 0, st>>>(seq_len, reinterpret_cast<const long long*>(end_pos_vec), B,
                                                       (long long)end_pos);
+  return int(cudaGetLastError());
+}
+
+// ---- vocabulary-sharded verification (shard_kernels.cuh) ------------------------------------
+static bool shard_rows_ok(const void* draft, const void* target, int dtype, int B, int gamma, int Vs) {
+  return B >= 0 && gamma >= 0 && gamma <= 32 && Vs > 0 && target && (gamma == 0 || draft) &&
+         (dtype == DUODEC_F32 || dtype == DUODEC_BF16);
+}
+
+int duodec_shard_stats(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss, int64_t t_sb,
+                       int64_t t_ss, int B, int gamma, int Vs, int v_begin, const int64_t* tokens, int64_t tok_sb,
+                       float temperature, float draft_temperature, float* stats, void* stream) {
+  if (!shard_rows_ok(draft, target, dtype, B, gamma, Vs) || temperature <= 0.0f || draft_temperature <= 0.0f)
+    return DUODEC_EINVAL;
+  if (B == 0) return 0;
+  if (!stats || (gamma > 0 && !tokens)) return DUODEC_EINVAL;
+  const ShardRows S{draft, target, d_sb, d_ss, t_sb, t_ss, B, gamma, Vs, v_begin, temperature, draft_temperature};
+  const int rows = B * (2 * gamma + 1);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dtype == DUODEC_F32)
+    shard_stats_kernel<float><<<rows, kThreads, 0, st>>>(S, reinterpret_cast<const long long*>(tokens), tok_sb,
+                                                         reinterpret_cast<float4*>(stats));
+  else
+    shard_stats_kernel<__nv_bfloat16><<<rows, kThreads, 0, st>>>(S, reinterpret_cast<const long long*>(tokens), tok_sb,
+                                                                 reinterpret_cast<float4*>(stats));
+  return int(cudaGetLastError());
+}
+
+int duodec_shard_accept(const float* gathered_stats, int world, int B, int gamma, const float* r, int64_t r_sb,
+                        uint8_t* accept_mask, float* sel_target_p, float* sel_draft_p, int64_t* accepted_len,
+                        uint8_t* all_accepted, void* plan, void* stream) {
+  if (world <= 0 || B < 0 || gamma < 0 || gamma > 32) return DUODEC_EINVAL;
+  if (B == 0) return 0;
+  if (!gathered_stats || !accepted_len || !all_accepted || !plan ||
+      (gamma > 0 && (!r || !accept_mask || !sel_target_p || !sel_draft_p)))
+    return DUODEC_EINVAL;
+  shard_accept_kernel<<<B, 32, 0, static_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const float4*>(gathered_stats), world, B, gamma, r, r_sb, accept_mask, sel_target_p,
+      sel_draft_p, reinterpret_cast<long long*>(accepted_len), all_accepted, static_cast<ShardPlan*>(plan));
+  return int(cudaGetLastError());
+}
+
+int duodec_shard_sample(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss, int64_t t_sb,
+                        int64_t t_ss, int B, int gamma, int Vs, int v_begin, float temperature,
+                        float draft_temperature, const void* plan, const float* noise, int64_t noise_sb,
+                        void* partial, void* stream) {
+  if (!shard_rows_ok(draft, target, dtype, B, gamma, Vs)) return DUODEC_EINVAL;
+  if (B == 0) return 0;
+  if (!plan || !noise || !partial) return DUODEC_EINVAL;
+  const ShardRows S{draft, target, d_sb, d_ss, t_sb, t_ss, B, gamma, Vs, v_begin, temperature, draft_temperature};
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dtype == DUODEC_F32)
+    shard_sample_kernel<float><<<B, kThreads, 0, st>>>(S, static_cast<const ShardPlan*>(plan), noise, noise_sb,
+                                                       static_cast<ShardPartial*>(partial));
+  else
+    shard_sample_kernel<__nv_bfloat16><<<B, kThreads, 0, st>>>(S, static_cast<const ShardPlan*>(plan), noise,
+                                                               noise_sb, static_cast<ShardPartial*>(partial));
+  return int(cudaGetLastError());
+}
+
+int duodec_shard_finish(const void* gathered_partials, int world, int B, int64_t* token, void* stream) {
+  if (world <= 0 || B < 0) return DUODEC_EINVAL;
+  if (B == 0) return 0;
+  if (!gathered_partials || !token) return DUODEC_EINVAL;
+  shard_finish_kernel<<<(B + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const ShardPartial*>(gathered_partials), world, B, reinterpret_cast<long long*>(token));
   return int(cudaGetLastError());
 }
 

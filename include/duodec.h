@@ -140,6 +140,28 @@ int duodec_topk_rebuild(const void* probs, int dtype, int64_t in_stride, void* o
  * scalar applies to every sequence. */
 int duodec_kv_truncate(int32_t* seq_len, const int64_t* end_pos_vec, int64_t end_pos, int B, void* stream);
 
+/* ---- vocabulary-sharded verification (V = 151936 over `world` GPUs) -------------------------
+ * Every rank holds the slice [v_begin, v_begin + Vs) of all draft / target rows (strides of the
+ * LOCAL slices).  The step is stats -> all-gather -> accept -> sample -> all-gather -> finish; the
+ * two all-gathers are the caller's (NCCL over NVLink in duodecoding_b200/sharded.py).  Replaces
+ * the same reference code as duodec_verify_fused, without top-k / top-p.
+ *   stats    [B*(2*gamma+1), 4] float32 per rank: slice max, sum exp(x - max), token logit, flag
+ *   plan     [B] 32-byte records (device scratch between accept and sample)
+ *   partial  [B] 24-byte records per rank: residual mass, best race key, zero-mass fallback key */
+#define DUODEC_SHARD_PLAN_BYTES 32
+#define DUODEC_SHARD_PARTIAL_BYTES 24
+int duodec_shard_stats(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss, int64_t t_sb,
+                       int64_t t_ss, int B, int gamma, int Vs, int v_begin, const int64_t* tokens, int64_t tok_sb,
+                       float temperature, float draft_temperature, float* stats, void* stream);
+int duodec_shard_accept(const float* gathered_stats, int world, int B, int gamma, const float* r, int64_t r_sb,
+                        uint8_t* accept_mask, float* sel_target_p, float* sel_draft_p, int64_t* accepted_len,
+                        uint8_t* all_accepted, void* plan, void* stream);
+int duodec_shard_sample(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss, int64_t t_sb,
+                        int64_t t_ss, int B, int gamma, int Vs, int v_begin, float temperature,
+                        float draft_temperature, const void* plan, const float* noise, int64_t noise_sb,
+                        void* partial, void* stream);
+int duodec_shard_finish(const void* gathered_partials, int world, int B, int64_t* token, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

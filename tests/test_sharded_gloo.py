@@ -1,0 +1,61 @@
+"""N > 1 host logic on CPU: ShardedVerifier's partition / all-gather / merge under gloo, world_size 2,
+with the oracle's CPU restatement of the shard kernels as backend; result == unsharded oracle."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import oracle
+from duodecoding_b200.sharded import ShardedVerifier, shard_bounds
+
+
+def _case(seed, B, gamma, V, sigma):
+    g = torch.Generator().manual_seed(seed)
+    tl = torch.randn(B, gamma + 1, V, generator=g) * 3
+    dl = tl[:, :gamma] + sigma * torch.randn(B, gamma, V, generator=g)
+    q = oracle.norm_logits(dl, 1.0, 0, 0.0)
+    toks = torch.stack([oracle.sample(q[:, j], torch.empty(B, V).exponential_(1, generator=g))[:, 0]
+                        for j in range(gamma)], 1)
+    r = torch.rand(B, gamma, generator=g)
+    noise = torch.empty(B, V).exponential_(1, generator=g)
+    return dl, tl, toks, r, noise
+
+
+def _worker(rank, world, port, ret):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from oracle.sharded_port import OracleShardBackend
+        ok = True
+        for seed, sigma in [(1, 0.5), (2, 1.5)]:
+            B, gamma, V = 5, 4, 1003
+            dl, tl, toks, r, noise = _case(seed, B, gamma, V, sigma)
+            sv = ShardedVerifier(V, backend=OracleShardBackend())
+            got = sv.verify(sv.slice_of(dl), sv.slice_of(tl), toks, r, sv.slice_of(noise), 1.0)
+            want = oracle.fused_verify(dl, tl, toks, r, noise, 1.0, 0, 0.0)
+            ok &= torch.equal(got["accepted_len"], want["accepted_len"]) and torch.equal(got["token"], want["token"])
+            ok &= torch.equal(got["accept_mask"], want["accept_mask"]) and sv.collectives == 2
+            ok &= torch.allclose(got["selected_target_p"], want["selected_target_p"], rtol=1e-5, atol=1e-9)
+        ret[rank] = bool(ok)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_shard_bounds_cover_and_align():
+    for V, world in [(151936, 8), (151936, 4), (32000, 2), (1003, 2), (7, 4)]:
+        edges = [shard_bounds(V, g, world) for g in range(world)]
+        assert edges[0][0] == 0 and edges[-1][1] == V
+        assert all(a[1] == b[0] for a, b in zip(edges, edges[1:])) and all(lo % 8 == 0 for lo, _ in edges if lo < V)
+
+
+def test_sharded_verify_world2_gloo():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ret = mp.Manager().dict()
+    mp.spawn(_worker, args=(2, port, ret), nprocs=2, join=True)
+    assert ret.get(0) is True and ret.get(1) is True
