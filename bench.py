@@ -342,18 +342,119 @@ def run_ours(args):
     return 0
 
 
+# ----------------------------------------------------------------------------- C5: vocabulary-sharded verify
+def run_c5(args):
+    """BASELINE.json config 5: B=256, gamma=6, V=151936, bf16, no filter, vocabulary sharded over the ranks
+    (strong scaling: the total work is fixed, every rank holds V/N columns of every row)."""
+    import torch.distributed as dist
+
+    from duodecoding_b200.sharded import ShardedVerifier
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the verification path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    Bc, Gc, Vc = 256, 6, 151936
+    sv = ShardedVerifier(Vc, rank=rank, world=world)
+    Vs = sv.v_end - sv.v_begin
+    g = torch.Generator(device=dev).manual_seed(4321 + rank)
+    gt = torch.Generator(device=dev).manual_seed(99)  # replicated tensors: same seed on every rank
+    sets = []
+    for _ in range(2 if world == 1 else 4):
+        tl = (torch.randn(Bc, Gc + 1, Vs, device=dev, generator=g) * 3).to(torch.bfloat16)
+        dl = (tl[:, :Gc].float() + torch.randn(Bc, Gc, Vs, device=dev, generator=g)).to(torch.bfloat16)
+        toks = torch.randint(0, Vc, (Bc, Gc), device=dev, generator=gt)
+        r = torch.rand(Bc, Gc, device=dev, generator=gt) * 0.05  # low thresholds: a mix of accepted lengths
+        noise = torch.empty(Bc, Vs, device=dev).exponential_(1.0, generator=g)
+        sets.append((dl, tl, toks, r, noise))
+    K, W = args.steps, max(args.warmup, 3)
+    for i in range(W):
+        out = sv.verify(*sets[i % len(sets)], 1.0)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    clocks = ClockSampler(local) if rank == 0 else None
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(K):
+        out = sv.verify(*sets[i % len(sets)], 1.0)
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    dt = e0.elapsed_time(e1) * 1e-3
+    if world > 1:
+        t = torch.tensor([dt], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = float(t.item())
+    # end to end through the public API: the replicated small inputs come from pinned host memory, the
+    # results go back to the host every step (the logit slices are produced on the device by the LM head)
+    h_toks, h_r = sets[0][2].cpu().pin_memory(), sets[0][3].cpu().pin_memory()
+    t0 = time.perf_counter()
+    Ke = max(3, min(K, 20))
+    for i in range(Ke):
+        s = sets[i % len(sets)]
+        res = sv.verify(s[0], s[1], h_toks.to(dev, non_blocking=True), h_r.to(dev, non_blocking=True), s[4], 1.0)
+        host = {k: v.cpu() for k, v in res.items()}
+        _ = int(host["accepted_len"][0])
+    dte = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([dte], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dte = float(t.item())
+    clk = clocks.stop() if clocks is not None else None
+    if rank == 0:
+        alg = 2 * Bc * (Gc + 1) * Vc * 2
+        peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        peak = float(json.load(open(peaks_path))["hbm_gbs"]) if os.path.exists(peaks_path) else 6650.0
+        ach = alg / world / (dt / K) / 1e9
+        line = {
+            "metric": METRIC, "value": Bc * (Gc + 1) * K / dt, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": dt / K * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": "C5 vocabulary-sharded verify: B=256, gamma+1=7, V=151936, bf16 logits, T=1.0, "
+                                   "no filter", "B": Bc, "gamma": Gc, "V": Vc, "sharding": f"vocab/{world}",
+                       "collectives_per_step": 2 if world > 1 else 0, "mean_accepted_len":
+                           float(out["accepted_len"].float().mean().item()),
+                       "l2": "per-rank inputs larger than L2 or rotated", "timing": "CUDA events around K steps"},
+            "clocks": clk, "gpu_launches": 4 * K,
+            "e2e": {"value": Bc * (Gc + 1) * Ke / dte, "unit": UNIT, "h2d_bytes_per_step": int(h_toks.numel() * 8 +
+                    h_r.numel() * 4), "d2h_bytes_per_step": int(sum(v.numel() * v.element_size() for v in host.values())),
+                    "api": "duodecoding_b200.sharded.ShardedVerifier.verify"},
+            "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                         "traffic": None, "kernel": "shard_stats_kernel<bf16> (+accept, sample, finish, 2 all-gathers)",
+                         "alg_bytes_per_launch": alg // world, "us_per_launch": dt / K * 1e6,
+                         "note": "per-GPU bytes of one step / whole step time"},
+            "cpu_baseline": None,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c2", choices=["c2", "c5"], help="c2: BASELINE config 2 (default, batch per rank); c5: vocabulary-sharded config 5")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--clock-seconds", type=float, default=0.6,
                     help="untimed replays of the same graph before and after the timed one, for the clock sampler")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
+    if args.workload == "c5":
+        return run_c5(args)
     return run_ours(args)
 
 

@@ -68,9 +68,9 @@ SIGNATURES = {
     "duodec_shard_sample": (
         c_int,
         [c_void_p, c_void_p, c_int, c_i64, c_i64, c_i64, c_i64, c_int, c_int, c_int, c_int, c_float, c_float]
-        + [c_void_p, c_void_p, c_i64, c_void_p, c_void_p],
+        + [c_void_p, c_void_p, c_i64, c_int, c_void_p, c_void_p],
     ),
-    "duodec_shard_finish": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p]),
+    "duodec_shard_finish": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
 }
 
 

@@ -404,27 +404,27 @@ int duodec_shard_accept(const float* gathered_stats, int world, int B, int gamma
 int duodec_shard_sample(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss, int64_t t_sb,
                         int64_t t_ss, int B, int gamma, int Vs, int v_begin, float temperature,
                         float draft_temperature, const void* plan, const float* noise, int64_t noise_sb,
-                        void* partial, void* stream) {
+                        int nslice, void* partial, void* stream) {
   if (!shard_rows_ok(draft, target, dtype, B, gamma, Vs)) return DUODEC_EINVAL;
   if (B == 0) return 0;
-  if (!plan || !noise || !partial) return DUODEC_EINVAL;
+  if (!plan || !noise || !partial || nslice <= 0 || nslice > 65535 || B > 65535) return DUODEC_EINVAL;
   const ShardRows S{draft, target, d_sb, d_ss, t_sb, t_ss, B, gamma, Vs, v_begin, temperature, draft_temperature};
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (dtype == DUODEC_F32)
-    shard_sample_kernel<float><<<B, kThreads, 0, st>>>(S, static_cast<const ShardPlan*>(plan), noise, noise_sb,
+    shard_sample_kernel<float><<<dim3(unsigned(nslice), unsigned(B)), kThreads, 0, st>>>(S, static_cast<const ShardPlan*>(plan), noise, noise_sb,
                                                        static_cast<ShardPartial*>(partial));
   else
-    shard_sample_kernel<__nv_bfloat16><<<B, kThreads, 0, st>>>(S, static_cast<const ShardPlan*>(plan), noise,
+    shard_sample_kernel<__nv_bfloat16><<<dim3(unsigned(nslice), unsigned(B)), kThreads, 0, st>>>(S, static_cast<const ShardPlan*>(plan), noise,
                                                                noise_sb, static_cast<ShardPartial*>(partial));
   return int(cudaGetLastError());
 }
 
-int duodec_shard_finish(const void* gathered_partials, int world, int B, int64_t* token, void* stream) {
-  if (world <= 0 || B < 0) return DUODEC_EINVAL;
+int duodec_shard_finish(const void* gathered_partials, int world, int B, int nslice, int64_t* token, void* stream) {
+  if (world <= 0 || B < 0 || nslice <= 0) return DUODEC_EINVAL;
   if (B == 0) return 0;
   if (!gathered_partials || !token) return DUODEC_EINVAL;
   shard_finish_kernel<<<(B + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const ShardPartial*>(gathered_partials), world, B, reinterpret_cast<long long*>(token));
+      static_cast<const ShardPartial*>(gathered_partials), world, B, nslice, reinterpret_cast<long long*>(token));
   return int(cudaGetLastError());
 }
 

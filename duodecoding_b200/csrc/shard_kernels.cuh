@@ -9,7 +9,7 @@
 //                        (M, Z) of the one row pair the token is drawn from
 //   shard_sample_kernel  per sequence, over the slice: residual d = max(0, p - q) (or p for the
 //                        bonus token): local mass, best race key (d / noise, global index), first
-//                        argmax(p - q) for the zero-mass fallback              -> 6 words per sequence
+//                        argmax(p - q) for the zero-mass fallback   -> 24 bytes per sequence and slice part
 //        -- exchange 2: all-gather of the partials --
 //   shard_finish_kernel  per sequence: total mass, best key over the ranks -> token
 //
@@ -36,7 +36,43 @@ __device__ __forceinline__ const TIn* shard_row(const ShardRows& S, int b, int j
                    : reinterpret_cast<const TIn*>(S.draft) + (long long)b * S.d_sb + (long long)j * S.d_ss;
 }
 
-// one block per row: slice max, then sum exp(x - max) (second read comes out of L1/L2)
+// eight consecutive entries of a row as floats (two 128-bit loads for fp32, one for bf16)
+template <class TIn>
+__device__ __forceinline__ void load8(const TIn* p, float (&x)[8]) {
+  if constexpr (sizeof(TIn) == 4) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+    x[0] = a.x, x[1] = a.y, x[2] = a.z, x[3] = a.w, x[4] = b.x, x[5] = b.y, x[6] = b.z, x[7] = b.w;
+  } else {
+    const uint4 u = __ldg(reinterpret_cast<const uint4*>(p));
+    x[0] = __uint_as_float(u.x << 16), x[1] = __uint_as_float(u.x & 0xffff0000u);
+    x[2] = __uint_as_float(u.y << 16), x[3] = __uint_as_float(u.y & 0xffff0000u);
+    x[4] = __uint_as_float(u.z << 16), x[5] = __uint_as_float(u.z & 0xffff0000u);
+    x[6] = __uint_as_float(u.w << 16), x[7] = __uint_as_float(u.w & 0xffff0000u);
+  }
+}
+template <class TIn>
+__device__ __forceinline__ bool row_vec8(const TIn* row, int n) {
+  return (n & 7) == 0 && (reinterpret_cast<uintptr_t>(row) & (8 * sizeof(TIn) - 1)) == 0;
+}
+__device__ __forceinline__ float ex2f(float t) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(t));
+  return y;
+}
+constexpr float kShardLog2e = 1.4426950408889634f;
+
+struct MaxSum {  // running (max, sum of exp(x - max)); merge is associative, fixed tree order
+  float m, s;
+};
+struct OpMaxSum {
+  __device__ __forceinline__ MaxSum operator()(MaxSum a, MaxSum b) const {
+    const float m = fmaxf(a.m, b.m);
+    if (m == -INFINITY) return MaxSum{m, 0.0f};
+    return MaxSum{m, a.s * ex2f((a.m - m) * kShardLog2e) + b.s * ex2f((b.m - m) * kShardLog2e)};
+  }
+};
+
+// one block per row, ONE pass: every thread keeps an online (max, sum), rescaled when its max moves
 template <class TIn>
 __global__ void __launch_bounds__(kThreads) shard_stats_kernel(const __grid_constant__ ShardRows S,
                                                                const long long* tokens, long long tok_sb,
@@ -47,20 +83,48 @@ __global__ void __launch_bounds__(kThreads) shard_stats_kernel(const __grid_cons
   const int is_target = (k == 2 * S.gamma) ? 1 : (k & 1), j = (k == 2 * S.gamma) ? S.gamma : (k >> 1);
   const TIn* row = shard_row<TIn>(S, b, j, is_target);
   const float temp = is_target ? S.t_temp : S.d_temp;
-  float mx = -INFINITY;
-  for (int i = threadIdx.x; i < S.Vs; i += kThreads) mx = fmaxf(mx, scale_logit(to_f32(row[i]), temp));
-  mx = block_allreduce(mx, OpMaxF(), &xc);
-  float s = 0.0f;
-  if (mx > -INFINITY)
-    for (int i = threadIdx.x; i < S.Vs; i += kThreads) s += expf(scale_logit(to_f32(row[i]), temp) - mx);
-  s = block_allreduce(s, OpSumF(), &xc);
+  MaxSum acc{-INFINITY, 0.0f};
+  auto push8 = [&](float (&x)[8]) {
+    float vm = x[0];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      x[i] = scale_logit(x[i], temp);
+      vm = fmaxf(vm, x[i]);
+    }
+    if (vm > acc.m) {
+      acc.s *= ex2f((acc.m - vm) * kShardLog2e);  // (0 * 0 on the first group)
+      acc.m = vm;
+    }
+    if (acc.m > -INFINITY) {
+      const float mo = acc.m * kShardLog2e;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc.s += ex2f(fmaf(x[i], kShardLog2e, -mo));
+    }
+  };
+  if (row_vec8(row, S.Vs)) {
+    for (int i = threadIdx.x * 8; i < S.Vs; i += kThreads * 8) {
+      float x[8];
+      load8<TIn>(row + i, x);
+      push8(x);
+    }
+  } else {
+    for (int i = threadIdx.x; i < S.Vs; i += kThreads) {
+      float x[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) x[u] = -INFINITY;
+      x[0] = to_f32(row[i]);
+      push8(x);
+    }
+  }
+  if (!(acc.s == acc.s)) acc.s = 0.0f;  // -inf - -inf on a thread that saw nothing
+  acc = block_allreduce(acc, OpMaxSum(), &xc);
   if (threadIdx.x == 0) {
     float tokx = 0.0f, has = 0.0f;
     if (j < S.gamma) {
       const long long t = tokens[(long long)b * tok_sb + j] - S.v_begin;
       if (t >= 0 && t < S.Vs) tokx = scale_logit(to_f32(row[t]), temp), has = 1.0f;
     }
-    stats[job] = make_float4(mx, s, tokx, has);
+    stats[job] = make_float4(acc.m, acc.s, tokx, has);
   }
 }
 
@@ -134,31 +198,51 @@ struct OpMaxKey2 {
   }
 };
 
-// one block per sequence over the local slice of the row pair named by the plan
+// grid (nslice, B): block (s, b) covers an eighth-aligned part of the local slice of the row pair
+// named by the plan and writes partial[b * nslice + s]
 template <class TIn>
 __global__ void __launch_bounds__(kThreads) shard_sample_kernel(const __grid_constant__ ShardRows S,
                                                                 const ShardPlan* plan, const float* noise,
                                                                 long long noise_sb, ShardPartial* out) {
   __shared__ Xchg xc;
-  const int b = blockIdx.x;
+  const int b = blockIdx.y, nslice = gridDim.x;
   const ShardPlan pl = plan[b];
   const TIn* prow = shard_row<TIn>(S, b, pl.n, 1);
   const TIn* qrow = shard_row<TIn>(S, b, pl.bonus ? 0 : pl.n, 0);
   const float* nz = noise + (long long)b * noise_sb;
+  int per = (S.Vs + nslice - 1) / nslice;
+  per = (per + 7) & ~7;
+  const int lo = min(int(blockIdx.x) * per, S.Vs), hi = min(lo + per, S.Vs);
+  const float rZp = __frcp_rn(pl.Zp), rZq = __frcp_rn(pl.Zq);
+  const float mp = pl.Mp * kShardLog2e, mq = pl.Mq * kShardLog2e;
   float mass = 0.0f;
   unsigned long long key = 0ull, bdk = 0ull;
-  for (int i = threadIdx.x; i < S.Vs; i += kThreads) {
-    float d = __fdiv_rn(expf(scale_logit(to_f32(prow[i]), S.t_temp) - pl.Mp), pl.Zp);
-    if (!pl.bonus) d -= __fdiv_rn(expf(scale_logit(to_f32(qrow[i]), S.d_temp) - pl.Mq), pl.Zq);
+  auto one = [&](float xp, float xq, float e, int i) {
+    float d = ex2f(fmaf(scale_logit(xp, S.t_temp), kShardLog2e, -mp)) * rZp;
+    if (!pl.bonus) d -= ex2f(fmaf(scale_logit(xq, S.d_temp), kShardLog2e, -mq)) * rZq;
     const unsigned gi = 0xffffffffu - unsigned(S.v_begin + i);
     if (d > 0.0f) {
       mass += d;
-      const unsigned long long k = ((unsigned long long)__float_as_uint(__fdiv_rn(d, nz[i])) << 32) | gi;
+      const unsigned long long k = ((unsigned long long)__float_as_uint(__fdiv_rn(d, e)) << 32) | gi;
       key = k > key ? k : key;
     }
     const float dz = (d == d && fabsf(d) != INFINITY) ? d : 0.0f;
     const unsigned long long k2 = ((unsigned long long)okey(dz) << 32) | gi;
     bdk = k2 > bdk ? k2 : bdk;
+  };
+  const bool vec = row_vec8(prow, S.Vs) && row_vec8(qrow, S.Vs) && (reinterpret_cast<uintptr_t>(nz) & 31) == 0;
+  if (vec) {
+    for (int i = lo + threadIdx.x * 8; i < hi; i += kThreads * 8) {
+      float xp[8], xq[8], e[8];
+      load8<TIn>(prow + i, xp);
+      if (!pl.bonus) load8<TIn>(qrow + i, xq);
+      load8<float>(nz + i, e);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) one(xp[u], pl.bonus ? 0.0f : xq[u], e[u], i + u);
+    }
+  } else {
+    for (int i = lo + threadIdx.x; i < hi; i += kThreads)
+      one(to_f32(prow[i]), pl.bonus ? 0.0f : to_f32(qrow[i]), nz[i], i);
   }
   mass = block_allreduce(mass, OpSumF(), &xc);
   const uint4 kk = block_allreduce(make_uint4(unsigned(key >> 32), unsigned(key), unsigned(bdk >> 32), unsigned(bdk)),
@@ -168,17 +252,17 @@ __global__ void __launch_bounds__(kThreads) shard_sample_kernel(const __grid_con
     p.mass = mass, p.pad = 0u;
     p.key = ((unsigned long long)kk.x << 32) | kk.y;
     p.bd = ((unsigned long long)kk.z << 32) | kk.w;
-    out[b] = p;
+    out[(long long)b * nslice + blockIdx.x] = p;
   }
 }
 
-__global__ void shard_finish_kernel(const ShardPartial* gathered, int G, int B, long long* token) {
+__global__ void shard_finish_kernel(const ShardPartial* gathered, int G, int B, int nslice, long long* token) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= B) return;
   float mass = 0.0f;
   unsigned long long key = 0ull, bd = 0ull;
-  for (int g = 0; g < G; ++g) {
-    const ShardPartial p = gathered[(long long)g * B + b];
+  for (int g = 0; g < G * nslice; ++g) {  // rank-major, then slice: the same order on every rank
+    const ShardPartial p = gathered[((long long)(g / nslice) * B + b) * nslice + (g % nslice)];
     mass += p.mass;
     key = p.key > key ? p.key : key;
     bd = p.bd > bd ? p.bd : bd;

@@ -80,20 +80,22 @@ class _CudaBackend:
 
     def sample_partial(self, draft, target, plan, noise, v_begin, t_temp, d_temp, gamma):
         B = target.shape[0]
-        partial = torch.empty((B, self.PARTIAL), dtype=torch.uint8, device=target.device)
+        nslice = max(1, min(-(-target.shape[-1] // 4096), -(-592 // max(B, 1))))  # >= 4 blocks per SM in total
+        partial = torch.empty((B, nslice, self.PARTIAL), dtype=torch.uint8, device=target.device)
         dp, dsb, dss = self._rows(draft)
         tp, tsb, tss = self._rows(target)
         with torch.cuda.device(target.device):
             self.check(self.lib.duodec_shard_sample(dp, tp, self.ops._code(target), dsb, dss, tsb, tss, B, gamma,
                                                     target.shape[-1], int(v_begin), float(t_temp), float(d_temp),
-                                                    plan.data_ptr(), noise.data_ptr(), noise.stride(0),
+                                                    plan.data_ptr(), noise.data_ptr(), noise.stride(0), nslice,
                                                     partial.data_ptr(), self.ops._stream()), "duodec_shard_sample")
         return partial
 
     def finish(self, gathered, B):
         token = torch.empty((B,), dtype=torch.int64, device=gathered.device)
         with torch.cuda.device(gathered.device):
-            self.check(self.lib.duodec_shard_finish(gathered.data_ptr(), gathered.shape[0], B, token.data_ptr(),
+            self.check(self.lib.duodec_shard_finish(gathered.data_ptr(), gathered.shape[0], B, gathered.shape[2],
+                                                    token.data_ptr(),
                                                     self.ops._stream()), "duodec_shard_finish")
         return token
 

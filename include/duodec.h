@@ -147,7 +147,8 @@ int duodec_kv_truncate(int32_t* seq_len, const int64_t* end_pos_vec, int64_t end
  * the same reference code as duodec_verify_fused, without top-k / top-p.
  *   stats    [B*(2*gamma+1), 4] float32 per rank: slice max, sum exp(x - max), token logit, flag
  *   plan     [B] 32-byte records (device scratch between accept and sample)
- *   partial  [B] 24-byte records per rank: residual mass, best race key, zero-mass fallback key */
+ *   partial  [B, nslice] 24-byte records per rank (the slice is cut in nslice parts for occupancy):
+ *            residual mass, best race key, zero-mass fallback key; gathered as [world, B, nslice] */
 #define DUODEC_SHARD_PLAN_BYTES 32
 #define DUODEC_SHARD_PARTIAL_BYTES 24
 int duodec_shard_stats(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss, int64_t t_sb,
@@ -159,8 +160,8 @@ int duodec_shard_accept(const float* gathered_stats, int world, int B, int gamma
 int duodec_shard_sample(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss, int64_t t_sb,
                         int64_t t_ss, int B, int gamma, int Vs, int v_begin, float temperature,
                         float draft_temperature, const void* plan, const float* noise, int64_t noise_sb,
-                        void* partial, void* stream);
-int duodec_shard_finish(const void* gathered_partials, int world, int B, int64_t* token, void* stream);
+                        int nslice, void* partial, void* stream);
+int duodec_shard_finish(const void* gathered_partials, int world, int B, int nslice, int64_t* token, void* stream);
 
 #ifdef __cplusplus
 }
