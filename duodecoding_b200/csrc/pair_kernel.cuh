@@ -1,0 +1,387 @@
+// Row-pair scan kernel: the streaming half of duodec_verify_fused, device path 5.
+//
+// Same algorithm as row_ring_kernel (ring_kernel.cuh: per-thread exponent histogram in pass 1, the
+// boundary bucket's entries in pass 2 out of L2, list_select), but a block works on TWO rows at a
+// time: its 256 workers are two halves of 128, each half with its own TMA stage ring (fed by its
+// own producer warp), histogram and half-barrier, streaming its own row.  With two blocks per SM
+// that is four rows in flight per SM - at the C2 shape every row of the step is in flight at once,
+// so the latency-bound row tails (bucket scan, second pass, select) overlap instead of queueing
+// behind each other.  The two halves join for the selects, which use all 256 threads
+// (list_select_body) on one row after the other; the list columns of the two rows are disjoint
+// (column = thread).
+#pragma once
+
+#include "ring_kernel.cuh"
+
+namespace duodec {
+namespace pair {
+
+constexpr int kHT = 128;                         // worker threads per half
+constexpr int kHW = kHT / 32;
+constexpr int kPT = kT3 + 64;                    // 256 workers + one producer warp per half
+#ifndef DUODEC_PAIR_STAGES
+#define DUODEC_PAIR_STAGES 2
+#endif
+constexpr int kPStages = DUODEC_PAIR_STAGES;     // 8 KB stages per half
+constexpr int kColD = 8;                         // list-column depth per worker thread (shared memory)
+constexpr int kPairCap = kColD * kT3;            // = the kCap of list_select: 2048
+constexpr int kOvfHalf = kT3;                    // overflow-list entries per row (shared memory)
+
+struct __align__(16) HalfRow {
+  double target;
+  float GB, Z, m0, mxl;
+  int state;  // 0 no row, 1 plain row (no filter), 2 select from the list, 3 general search, 4 keep everything
+  int pad[3];
+};
+
+struct __align__(16) PairSync {
+  unsigned long long full[2][kPStages];
+  unsigned long long empty[2][kPStages];
+  float hsum[2][kHB];
+  float2 hred[2][kHW];
+  HalfRow half[2];
+  int nlist;
+  int novf[2];  // overflow-list entries of the two rows
+  int pad;
+};
+
+constexpr size_t pair_smem_bytes() {
+  return size_t(2) * kPStages * kStageBytes + size_t(kHB) * kT3 * 4 + size_t(kPairCap + 2 * kOvfHalf) * sizeof(ListEntry) +
+         sizeof(Scratch3) + sizeof(PairSync) + 128;
+}
+
+__device__ __forceinline__ void barh(int h) {  // named barrier of one half (immediate ids: 2 and 3)
+  if (h == 0) asm volatile("bar.sync 2, 128;" ::: "memory");
+  else asm volatile("bar.sync 3, 128;" ::: "memory");
+}
+
+// one stage = 16 entries per half-thread: four 128-bit shared loads at (u * 128 + ht) * 4
+#define PAIR_STAGE_BEGIN(c)                                                                   \
+  const unsigned slot = seq % unsigned(kPStages);                                             \
+  mbar_wait(&ps->full[h][slot], (seq / unsigned(kPStages)) & 1u);                              \
+  const unsigned char* st = ring + size_t(slot) * kStageBytes;                                \
+  float4 v4[4];                                                                               \
+  _Pragma("unroll") for (int u = 0; u < 4; ++u) v4[u] = unpack4<TIn>(st + size_t((u * kHT + ht) * 4) * kElt); \
+  if (temp != 1.0f) {                                                                         \
+    _Pragma("unroll") for (int u = 0; u < 4; ++u) {                                           \
+      v4[u].x = __fdiv_rn(v4[u].x, temp), v4[u].y = __fdiv_rn(v4[u].y, temp);                 \
+      v4[u].z = __fdiv_rn(v4[u].z, temp), v4[u].w = __fdiv_rn(v4[u].w, temp);                 \
+    }                                                                                         \
+  }                                                                                           \
+  const int i00 = (c) * kStageElems + ht * 4;
+#define PAIR_STAGE_END()                                                                      \
+  __syncwarp();                                                                               \
+  if (lane == 0) mbar_arrive(&ps->empty[h][slot]);                                            \
+  ++seq;
+#define PAIR_EACH(F)                                                                          \
+  _Pragma("unroll") for (int u = 0; u < 4; ++u) {                                             \
+    const int iu = i00 + u * kHT * 4;                                                         \
+    if (iu < V) { F(v4[u].x, iu) F(v4[u].y, iu + 1) F(v4[u].z, iu + 2) F(v4[u].w, iu + 3) }   \
+  }
+
+// smallest float x whose histogram bucket (hist_bits of x*log2e - m0) is >= bits; false if the search
+// does not settle (the caller then takes the general search)
+__device__ __forceinline__ bool bucket_edge(int bits, float m0, float* edge) {
+  float g = (float(bits - __float_as_int(kHMagic)) - 0.5f + m0) * 0.6931471805599453f;
+  int it = 0;
+  while (hist_bits(fmaf(g, kLog2e, -m0)) >= bits && it < 128) g = nextafterf(g, -INFINITY), ++it;
+  while (hist_bits(fmaf(g, kLog2e, -m0)) < bits && it < 256) g = nextafterf(g, INFINITY), ++it;
+  *edge = g;
+  return it < 256 && hist_bits(fmaf(g, kLog2e, -m0)) >= bits &&
+         hist_bits(fmaf(nextafterf(g, -INFINITY), kLog2e, -m0)) < bits;
+}
+
+// General search of one row by the 256 workers (rare): exact row maximum first, then the windowed
+// search of split_kernels.cuh through L2.
+template <class TIn>
+__device__ __noinline__ RowRecord general_row(const TIn* row, int V, float temp, float top_p, bool nucleus, float m0,
+                                              ListEntry* glist, int* count, Scratch3* sc, int* stats) {
+  int phase = 0;
+  Pass3 pr = rescan_row<TIn, kListCap>(row, V, temp, m0, INFINITY, INFINITY, glist, count, sc, phase);
+  m0 = pr.mx * kLog2e;
+  pr = rescan_row<TIn, kListCap>(row, V, temp, m0, INFINITY, INFINITY, glist, count, sc, phase);
+  RowRecord rec;
+  rec.m0 = m0, rec.Z = pr.z, rec.xstar = -INFINITY, rec.istar = 0x7fffffff;
+  rec.sel = 0.0f, rec.mxl = m0, rec.dens = 0.0f;
+  float theta = pr.mx, dens = 0.0f;
+  if (nucleus)
+    resolve_row3<TIn, kListCap>(row, V, temp, top_p, m0, pr, INFINITY, INFINITY, 0.0f, glist, count, sc, phase, rec,
+                                &theta, &dens, stats);
+  return rec;
+}
+
+template <class TIn>
+__global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant__ SplitParams P) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  float* hist_all = reinterpret_cast<float*>(smem + size_t(2) * kPStages * kStageBytes);
+  ListEntry* slist = reinterpret_cast<ListEntry*>(hist_all + kHB * kT3);  // [kColD][256] columns, then 2 x overflow
+  ListEntry* sovf = slist + kPairCap;
+  Scratch3* sc = reinterpret_cast<Scratch3*>(sovf + 2 * kOvfHalf);
+  PairSync* ps = reinterpret_cast<PairSync*>(sc + 1);
+
+  const int tid = threadIdx.x;
+  const int gamma = P.gamma, V = P.V;
+  const int njobs = P.B * (2 * gamma + 1);
+  const int npairs = (njobs + 1) / 2;
+  const int nchunk = (V + kStageElems - 1) / kStageElems;
+  constexpr int kElt = int(sizeof(TIn));
+
+  if (tid == 0) {
+    for (int hh = 0; hh < 2; ++hh)
+      for (int s = 0; s < kPStages; ++s) {
+        mbar_init(&ps->full[hh][s], 1);
+        mbar_init(&ps->empty[hh][s], kHW);
+      }
+    mbar_fence_init();
+    ps->nlist = 0;
+    ps->novf[0] = ps->novf[1] = 0;
+  }
+  __syncthreads();
+
+  if (tid >= kT3) {
+    // ---- producers: lane 0 of warp 8 feeds half 0, lane 0 of warp 9 feeds half 1
+    const int h = (tid - kT3) >> 5;
+    if (((tid - kT3) & 31) == 0) {
+      unsigned char* ring = smem + size_t(h) * kPStages * kStageBytes;
+      unsigned seq = 0;
+      for (int pr = blockIdx.x; pr < npairs; pr += gridDim.x) {
+        const int job = 2 * pr + h;
+        if (job >= njobs) continue;
+        const RowJob jb = decode_job(job, gamma);
+        const TIn* row = split_row<TIn>(P, jb);
+#ifdef ABL_NOPASS2
+        const int passes = 1;
+#else
+        const int passes = (jb.is_target ? P.t_top_p : P.d_top_p) > 0.0f ? 2 : 1;
+#endif
+        for (int pass = 0; pass < passes; ++pass)
+          for (int c = 0; c < nchunk; ++c, ++seq) {
+            const unsigned slot = seq % unsigned(kPStages);
+            if (seq >= unsigned(kPStages))
+              mbar_wait(&ps->empty[h][slot], ((seq / unsigned(kPStages)) - 1u) & 1u);
+            const int e0 = c * kStageElems;
+            const int ne = (V - e0) < kStageElems ? (V - e0) : kStageElems;
+            mbar_expect_tx(&ps->full[h][slot], unsigned(ne * kElt));
+            bulk_g2s(ring + size_t(slot) * kStageBytes, row + e0, unsigned(ne * kElt), &ps->full[h][slot]);
+          }
+      }
+    }
+    return;
+  }
+
+  // ---- workers: half h = threads [128 h, 128 h + 128)
+  const int h = tid >> 7, ht = tid & (kHT - 1), lane = tid & 31, hw = ht >> 5;
+  unsigned char* ring = smem + size_t(h) * kPStages * kStageBytes;
+  float* hist = hist_all + h * kHB * kHT;  // this half's [bucket][thread] histogram
+  float* hp = hist + ht;
+  const int bits0 = __float_as_int(kHTmin + kHMagic);
+  ListEntry* list = P.lists + (long long)blockIdx.x * kListCap;
+  ListEntry* col = slist + tid;  // this thread's column (shared memory): entry j at slist[j * 256 + tid]
+  ListEntry* ovf_base = sovf;    // entries beyond a full column: the half's overflow list
+  int phase = 0;
+  unsigned seq = 0;
+#pragma unroll
+  for (int b = 0; b < kHB; ++b) hp[b * kHT] = 0.0f;
+
+#pragma unroll 1
+  for (int pr = blockIdx.x; pr < npairs; pr += gridDim.x) {
+    const int job = 2 * pr + h;
+    const bool have = job < njobs;
+    const RowJob jb = decode_job(have ? job : 0, gamma);
+    const TIn* row = split_row<TIn>(P, jb);
+    const float temp = jb.is_target ? P.t_temp : P.d_temp;
+    const float top_p = jb.is_target ? P.t_top_p : P.d_top_p;
+    const bool nucleus = top_p > 0.0f;
+
+    // the drafted token's logit is needed when the row closes: fetch it now (first thread of the half)
+    long long tok = -1;
+    float xtok = 0.0f;
+    if (have && ht == 0 && jb.j < gamma) {
+      tok = P.tokens[(long long)jb.b * P.tok_sb + jb.j];
+      if (tok >= 0 && tok < V) xtok = scale_logit(to_f32(__ldcg(row + tok)), temp);
+    }
+    const uint4 hint = __ldg(reinterpret_cast<const uint4*>(&P.hints[jb.is_target]));
+    const float m0 = int(hint.w) != 0 ? __uint_as_float(hint.x) : 0.0f;
+
+    int mycnt = 0, state = 0;
+    float Z = 0.0f, mxl = m0, GB = 0.0f;
+    double target = 0.0;
+    if (have && !nucleus) {
+      float z = 0.0f, mx = -INFINITY;
+#pragma unroll 1
+      for (int c = 0; c < nchunk; ++c) {
+        PAIR_STAGE_BEGIN(c)
+#define FP_PLAIN(x, i) z += row_exp(x, m0), mx = fmaxf(mx, x);
+        PAIR_EACH(FP_PLAIN)
+        PAIR_STAGE_END()
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        z += __shfl_xor_sync(0xffffffffu, z, o);
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+      }
+      if (lane == 0) ps->hred[h][hw] = make_float2(mx, z);
+      barh(h);
+      mx = -INFINITY, z = 0.0f;
+#pragma unroll
+      for (int w = 0; w < kHW; ++w) mx = fmaxf(mx, ps->hred[h][w].x), z += ps->hred[h][w].y;
+      Z = z;
+      mxl = mx * kLog2e;
+      state = (!(fabsf(mxl - m0) <= 32.0f) || !(Z < INFINITY) || !(Z > 0.0f)) ? 3 : 1;
+    } else if (have) {
+      // ---- pass 1: per-thread mass histogram over the exponent
+#pragma unroll 1
+      for (int c = 0; c < nchunk; ++c) {
+        PAIR_STAGE_BEGIN(c)
+#define FP_HIST(x, i)                                 \
+  {                                                   \
+    const float t = fmaf(x, kLog2e, -m0);             \
+    float* a = hp + (hist_bits(t) - bits0) * kHT;     \
+    *a += ex2_approx(t);                              \
+  }
+        PAIR_EACH(FP_HIST)
+        PAIR_STAGE_END()
+      }
+      barh(h);
+      // bucket sums: warp w of the half owns buckets 8w .. 8w+7 (fixed order: deterministic)
+#pragma unroll
+      for (int q = 0; q < kHB / kHW; ++q) {
+        const int b = hw * (kHB / kHW) + q;
+        float s = 0.0f;
+#pragma unroll
+        for (int k = 0; k < kHT / 32; ++k) {
+          s += hist[b * kHT + k * 32 + lane];
+          hist[b * kHT + k * 32 + lane] = 0.0f;  // ready for the next row
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (lane == 0) ps->hsum[h][b] = s;
+      }
+      barh(h);
+      // every warp scans the 32 bucket sums from the top (lane l holds bucket 31 - l)
+      const float hb = ps->hsum[h][kHB - 1 - lane];
+      float incl = hb;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const float o = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += o;
+      }
+      Z = __shfl_sync(0xffffffffu, incl, 31);
+      const unsigned nonempty = __ballot_sync(0xffffffffu, hb > 0.0f);
+      const int btop = nonempty ? kHB - 1 - (__ffs(nonempty) - 1) : -1;
+      mxl = m0 + (btop == kHB - 1 ? fmaxf(kHTmax, log2f(__shfl_sync(0xffffffffu, hb, 0))) : float(btop) + kHTmin);
+      bool slow = !(Z < INFINITY) || !(Z > 0.0f);
+      target = double(top_p) * double(Z);
+      int bstar = -1;
+      if (!slow && target < double(Z)) {
+        const unsigned crossed = __ballot_sync(0xffffffffu, double(incl) > target);
+        if (crossed) {
+          const int l = __ffs(crossed) - 1;
+          bstar = kHB - 1 - l;
+          GB = __shfl_sync(0xffffffffu, incl - hb, l);
+        }
+        if (bstar <= 0) slow = true;  // the lower end bucket is unbounded below
+      }
+      // ---- pass 2: the boundary bucket's entries (always consumed: the producer streams the row twice).
+      // The bucket is an interval [xa, xb) of scaled logits (the bucket function is monotone): two compares.
+      float xa = INFINITY, xb = INFINITY;
+      if (bstar > 0 && !slow) {
+        if (!bucket_edge(bits0 + bstar, m0, &xa)) slow = true;
+        if (bstar < kHB - 1 && !bucket_edge(bits0 + bstar + 1, m0, &xb)) slow = true;
+        if (slow) xa = INFINITY;
+      }
+#define FP_PICK(x, i)                                                 \
+  if (x >= xa && x < xb) {                                            \
+    if (mycnt < kColD) {                                              \
+      col[mycnt * kT3] = ListEntry{x, i};                             \
+    } else {                                                          \
+      const int pos = atomicAdd(&ps->novf[h], 1);                     \
+      if (pos < kOvfHalf) ovf_base[h * kOvfHalf + pos] = ListEntry{x, i}; \
+    }                                                                 \
+    ++mycnt;                                                          \
+  }
+#ifndef ABL_NOPASS2
+#pragma unroll 1
+      for (int c = 0; c < nchunk; ++c) {
+        PAIR_STAGE_BEGIN(c)
+#ifdef ABL_NOPICK
+        if (v4[0].x == 12345.678f) mycnt += i00;
+#else
+        PAIR_EACH(FP_PICK)
+#endif
+        PAIR_STAGE_END()
+      }
+#endif
+      state = slow ? 3 : (bstar > 0 ? 2 : 4);
+#if defined(ABL_NOPASS2) || defined(ABL_NOSELECT) || defined(ABL_NOPICK)
+      state = 4;
+#endif
+    }
+    if (ht == 0) {
+      HalfRow hr;
+      hr.target = target, hr.GB = GB, hr.Z = Z, hr.m0 = m0, hr.mxl = mxl, hr.state = state;
+      hr.pad[0] = hr.pad[1] = hr.pad[2] = 0;
+      ps->half[h] = hr;
+    }
+    bar3();  // ---- the halves join: both rows' parameters and list columns are visible
+
+    int st[2] = {ps->half[0].state, ps->half[1].state};
+#pragma unroll
+    for (int hh = 0; hh < 2; ++hh) {
+      if (st[hh] == 0) continue;
+      const HalfRow hr = ps->half[hh];
+      RowRecord rec;
+      rec.m0 = hr.m0, rec.Z = hr.Z, rec.xstar = -INFINITY, rec.istar = 0x7fffffff;
+      rec.sel = 0.0f, rec.mxl = hr.mxl, rec.dens = 0.0f;
+      if (st[hh] == 2) {
+        const int mine = (h == hh) ? mycnt : 0;
+        const int novf = ps->novf[hh];
+        if (novf > kOvfHalf) {
+          st[hh] = 3;  // more overflow than the list holds: general search below
+        } else {
+          if (P.stats) {
+            const int n = reduce3_small(mine, OpSumI(), sc, phase);
+            if (tid == 0) {
+              atomicAdd(&P.stats[0], 1);
+              atomicAdd(&P.stats[16], 1);
+              atomicAdd(&P.stats[21], n);
+              atomicMax(&P.stats[22], n);
+            }
+          }
+          list_select_body<kPairCap>(slist, 0, mine, 0.0f, 0.0f, hr.GB, hr.Z, hr.target, hr.m0, sc, phase, rec,
+                                     P.stats, sovf + hh * kOvfHalf, novf);
+        }
+      }
+      if (st[hh] != 3 && tid == hh * kHT) {
+        if (tok >= 0 && tok < V) {
+          const float e = kept(rec, xtok, int(tok)) ? row_exp(xtok, rec.m0) : 0.0f;
+          rec.sel = __fdiv_rn(e, rec.Z);
+        }
+        store_record(&P.records[2 * pr + hh], rec);
+      }
+    }
+#pragma unroll 1
+    for (int hh = 0; hh < 2; ++hh) {
+      if (st[hh] != 3) continue;
+      // general search by all 256 workers (rare): exact row maximum first, then the windowed search through L2
+      const RowJob j2 = decode_job(2 * pr + hh, gamma);
+      bar3();
+      RowRecord rec = general_row<TIn>(split_row<TIn>(P, j2), V, j2.is_target ? P.t_temp : P.d_temp,
+                                       j2.is_target ? P.t_top_p : P.d_top_p,
+                                       (j2.is_target ? P.t_top_p : P.d_top_p) > 0.0f, ps->half[hh].m0, list,
+                                       &ps->nlist, sc, P.stats);
+      if (tid == hh * kHT) {
+        if (tok >= 0 && tok < V) {
+          const float e = kept(rec, xtok, int(tok)) ? row_exp(xtok, rec.m0) : 0.0f;
+          rec.sel = __fdiv_rn(e, rec.Z);
+        }
+        store_record(&P.records[2 * pr + hh], rec);
+      }
+    }
+    if (tid == 0) ps->novf[0] = ps->novf[1] = 0;
+    bar3();  // lists, scratch and the half records are free for the next pair
+  }
+}
+
+}  // namespace pair
+}  // namespace duodec

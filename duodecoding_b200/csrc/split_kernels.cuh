@@ -195,7 +195,8 @@ __device__ __noinline__ Pass3 rescan_row(const TIn* row, int V, float temp, floa
 template <int kCap>
 __device__ __forceinline__ void list_select_body(const ListEntry* list, int nlist, int mycnt, float A, float B,
                                                  float GB, float Zrow, double target, float m0, Scratch3* sc,
-                                                 int& phase, RowRecord& rec, int* stats) {
+                                                 int& phase, RowRecord& rec, int* stats,
+                                                 const ListEntry* ovf = nullptr, int novf = 0) {
   const int tid = threadIdx.x;
   struct { float z; int n; } pr{Zrow, nlist};
   const float lo = A;
@@ -205,7 +206,9 @@ __device__ __forceinline__ void list_select_body(const ListEntry* list, int nlis
   // of [A, B) over 256 value buckets (mass and count packed in one 64-bit word), a suffix scan
   // finds the bucket in which the kept mass crosses top_p * Z; with <= kCandMax entries in it
   // the all-pairs finish below orders them exactly like the reference's sort.
-  constexpr int kPer = kCap / kT3;
+  constexpr int kCol = kCap / kT3;  // entries of this thread's list column
+  constexpr int kPer = kCol + 2;    // + two entries of the overflow list (ovf[k * 256 + tid], k < 2)
+  auto entry = [&](int j) { return j < kCol ? &list[j * kT3 + tid] : &ovf[(j - kCol) * kT3 + tid]; };
   constexpr unsigned long long kMassMask = (1ull << 50) - 1ull;
   const int ez = int(__float_as_uint(pr.z) >> 23) - 126;               // Z = f * 2^ez, f in [0.5, 1)
   const float S = __uint_as_float(unsigned(127 + 38 - ez) << 23);      // 2^(38 - ez)
@@ -219,10 +222,10 @@ __device__ __forceinline__ void list_select_body(const ListEntry* list, int nlis
 #pragma unroll
   for (int j = 0; j < kPer; ++j) {
     const int p = j * kT3 + tid;
-    const bool have = mycnt >= 0 ? j < mycnt : p < pr.n;
+    const bool have = j < kCol ? (mycnt >= 0 ? j < mycnt : p < pr.n) : ((j - kCol) * kT3 + tid < novf);
     float x = -INFINITY;
     if (have) {
-      x = ld_list_x(&list[p]);
+      x = ld_list_x(entry(j));
       emx = fmaxf(emx, x), engmn = fmaxf(engmn, -x);
     }
     cx[j] = x;
@@ -284,7 +287,7 @@ __device__ __forceinline__ void list_select_body(const ListEntry* list, int nlis
 #pragma unroll
       for (int j = 0; j < kPer; ++j) {
         if (cx[j] >= A && cx[j] < B) {
-          const unsigned idx = unsigned(ld_list_i(&list[j * kT3 + tid]));
+          const unsigned idx = unsigned(ld_list_i(entry(j)));
           const unsigned long long k2 = ((unsigned long long)okey(cx[j]) << 32) | (0xffffffffu - idx);
           kk = k2 < kk ? k2 : kk;
         }
@@ -317,7 +320,7 @@ __device__ __forceinline__ void list_select_body(const ListEntry* list, int nlis
             const int pos = atomicAdd(&sc->ncand, 1);
             sc->cand_x[pos] = cx[j];
             sc->cand_f[pos] = fx(cx[j]);
-            sc->cand_i[pos] = ld_list_i(&list[j * kT3 + tid]);
+            sc->cand_i[pos] = ld_list_i(entry(j));
           }
         }
       }
@@ -388,7 +391,7 @@ __device__ __forceinline__ void list_select_body(const ListEntry* list, int nlis
 #pragma unroll
       for (int j = 0; j < kPer; ++j) {
         if (cx[j] >= A && cx[j] < B) {
-          const unsigned idx = unsigned(ld_list_i(&list[j * kT3 + tid]));
+          const unsigned idx = unsigned(ld_list_i(entry(j)));
           const unsigned long long kk = ((unsigned long long)okey(cx[j]) << 32) | (0xffffffffu - idx);
           if (kk >= K) s += fx(cx[j]);
         }

@@ -6,6 +6,7 @@
 #include "../../include/duodec.h"
 #include "ring_kernel.cuh"
 #include "resident_kernel.cuh"
+#include "pair_kernel.cuh"
 #include "stream_launch.h"
 
 namespace duodec {
@@ -53,7 +54,7 @@ constexpr int kMaxSlices = 32;  // row_scan slices the workspace is sized for (V
 size_t stream_workspace_bytes(int B, int gamma) {
   const size_t rows = size_t(B) * size_t(2 * gamma + 1);
   return 4 * sizeof(StreamHint) + rows * sizeof(RowRecord) + rows * kMaxSlices * sizeof(RowPartial) + rows * 8 +
-         size_t(B) * 24 + rows * size_t(kListCap) * sizeof(ListEntry);
+         size_t(B) * 24 + (rows + 2) * size_t(kListCap) * sizeof(ListEntry);
 }
 
 bool stream_try_launch(const StreamCall& c, int* rc) {
@@ -67,9 +68,10 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
   if (!ok) return false;
   const size_t rows = size_t(c.B) * size_t(2 * c.gamma + 1);
   const bool resident = c.path == 4 && c.B <= 65535;
+  const bool pairp = c.path == 5 && c.B <= 65535;
   const bool ring = (c.path == 3 || (c.path == 1 && c.Vt > kMaxSlices * kSlice)) && c.B <= 65535;
   const bool split = c.path == 1 && c.Vt <= kMaxSlices * kSlice && rows <= 65535 && c.B <= 65535;
-  if (ring || split || resident) {
+  if (ring || split || resident || pairp) {
     SplitParams Q;
     Q.draft = c.draft;
     Q.target = c.target;
@@ -120,6 +122,28 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
     Q.lists = reinterpret_cast<ListEntry*>(w);
     Q.stats = c.stats;
     const dim3 g1(unsigned(Q.S), unsigned(rows)), g2(unsigned((c.Vt + kSlice3 - 1) / kSlice3), unsigned(c.B));
+    if (pairp) {
+      const size_t smem = pair::pair_smem_bytes();
+      const int sms = stream_sm_count();
+      const int npairs = int((rows + 1) / 2);
+      const int grid = npairs < 2 * sms ? npairs : 2 * sms;  // two blocks per SM, two rows per block
+      cudaError_t e;
+      if (c.dtype == DUODEC_F32) {
+        e = ensure_stream_smem(reinterpret_cast<const void*>(pair::row_pair_kernel<float>), smem);
+        if (e == cudaSuccess) {
+          if (c.phases & 1) pair::row_pair_kernel<float><<<grid, pair::kPT, smem, c.stream>>>(Q);
+          if (c.phases & 2) seq_sample_kernel<float><<<g2, kT3, 0, c.stream>>>(Q);
+        }
+      } else {
+        e = ensure_stream_smem(reinterpret_cast<const void*>(pair::row_pair_kernel<__nv_bfloat16>), smem);
+        if (e == cudaSuccess) {
+          if (c.phases & 1) pair::row_pair_kernel<__nv_bfloat16><<<grid, pair::kPT, smem, c.stream>>>(Q);
+          if (c.phases & 2) seq_sample_kernel<__nv_bfloat16><<<g2, kT3, 0, c.stream>>>(Q);
+        }
+      }
+      *rc = int(e != cudaSuccess ? e : cudaGetLastError());
+      return true;
+    }
     if (resident) {
       const size_t smem = resident::ring_smem_bytes();
       const int sms = stream_sm_count();

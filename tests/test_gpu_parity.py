@@ -216,7 +216,7 @@ def _make_case(seed, B, gamma, V, sigma, T, k, p, dtype=torch.float32, Vd=None):
     return dl, tl, toks, r, noise
 
 
-@pytest.mark.parametrize("team", [-4, -3, -1, 0, 1, 2, 4, 8])  # -4 / -3 / -1: fast paths 4 (resident rows) / 3 (row ring) / 1 (sliced), else team kernel
+@pytest.mark.parametrize("team", [-5, -4, -3, -1, 0, 1, 2, 4, 8])  # -5 / -4 / -3 / -1: fast paths 5 (row pairs) / 4 (resident rows) / 3 (row ring) / 1 (sliced), else team kernel
 @pytest.mark.parametrize(
     "warp", [(1.0, 0, 0.0), (1.0, 0, 0.9), (0.8, 40, 0.0), (1.2, 200, 0.7), (0.0, 0, 0.0), (0.7, 0, 0.5)]
 )
@@ -234,7 +234,7 @@ def test_verify_fused_vs_oracle(ops, dev, team, warp):
     _check_verify(got, want, NUCLEUS_RTOL if p > 0 else RTOL)
 
 
-@pytest.mark.parametrize("stream", [4, 3, 1, 0])
+@pytest.mark.parametrize("stream", [5, 4, 3, 1, 0])
 @pytest.mark.parametrize("sigma", [0.3, 1.0, 2.0])
 def test_verify_fused_vocab_32000(ops, dev, sigma, stream):
     dl, tl, toks, r, noise = _make_case(22, 8, 4, 32000, sigma, 1.0, 0, 0.9)
@@ -247,7 +247,7 @@ def test_verify_fused_vocab_32000(ops, dev, sigma, stream):
     _check_verify(got, want, NUCLEUS_RTOL)
 
 
-@pytest.mark.parametrize("stream", [4, 3, 1, 0])
+@pytest.mark.parametrize("stream", [5, 4, 3, 1, 0])
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_verify_fused_peaked_rows_are_exact(ops, dev, stream, dtype):
     # LM-like rows: nucleus of a few tokens, boundary margins far above fp32 noise -> 1e-5 everywhere
@@ -330,8 +330,8 @@ def test_verify_fused_repeatable_and_workspace_self_cleaning(ops, dev):
     args = [t.to(dev) for t in (dl, tl, toks, r, noise)]
     first = ops.verify_fused(*args, 1.0, 0, 0.9)
     first = {k: v.clone() for k, v in first.items()}
-    for it in range(8):
-        ops.set_stream_path([3, 0, 1, 4][it % 4])  # the device paths share (and must restore) the workspace
+    for it in range(10):
+        ops.set_stream_path([3, 0, 1, 4, 5][it % 5])  # the device paths share (and must restore) the workspace
         again = ops.verify_fused(*args, 1.0, 0, 0.9)
         ops.set_stream_path(True)
         for k in first:

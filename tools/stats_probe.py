@@ -9,6 +9,8 @@ import bench
 import duodecoding_b200.ops as ops
 
 dev = torch.device("cuda:0")
+if len(sys.argv) > 1:
+    ops.set_stream_path(int(sys.argv[1]))
 sets = bench.make_sets(dev, 4, 1234)
 stats = torch.zeros(32, dtype=torch.int32, device=dev)
 ops.set_stats_buffer(stats)
