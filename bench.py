@@ -304,14 +304,14 @@ def run_ours(args):
     tp = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tp):
         try:
-            traffic = json.load(open(tp)).get("row_ring_kernel_bytes_per_launch")
+            traffic = json.load(open(tp)).get("scan_kernel_bytes_per_launch")
         except (ValueError, OSError):
             traffic = None
     roofline = {
         "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-        "traffic": traffic, "kernel": "row_ring_kernel<float>", "alg_bytes_per_launch": alg_bytes,
+        "traffic": traffic, "kernel": "pair::row_pair_kernel<float>", "alg_bytes_per_launch": alg_bytes,
         "us_per_launch": scan_us, "peak_source": peak_src, "frac_of_8TBps_nominal": achieved / 8000.0,
-        "step_us": us_launch, "step_kernels": ["row_ring_kernel<float>", "seq_sample_kernel<float>"],
+        "step_us": us_launch, "step_kernels": ["pair::row_pair_kernel<float>", "seq_sample_kernel<float>"],
         "step_frac": alg_bytes / (us_launch * 1e-6) / 1e9 / peak,
     }
 

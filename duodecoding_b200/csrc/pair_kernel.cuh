@@ -290,8 +290,10 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
         if (bstar < kHB - 1 && !bucket_edge(bits0 + bstar + 1, m0, &xb)) slow = true;
         if (slow) xa = INFINITY;
       }
-#define FP_PICK(x, i)                                                 \
-  if (x >= xa && x < xb) {                                            \
+      // a hit goes to this thread's list column (predicated store, no divergence inside a group of four);
+      // groups without a hit - most of them - cost eight compares
+#define FP_PUT(x, i, hit)                                             \
+  if (hit) {                                                          \
     if (mycnt < kColD) {                                              \
       col[mycnt * kT3] = ListEntry{x, i};                             \
     } else {                                                          \
@@ -300,6 +302,14 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
     }                                                                 \
     ++mycnt;                                                          \
   }
+#define FP_PICK4(v, iu)                                               \
+  {                                                                   \
+    const bool h0 = v.x >= xa && v.x < xb, h1 = v.y >= xa && v.y < xb; \
+    const bool h2 = v.z >= xa && v.z < xb, h3 = v.w >= xa && v.w < xb; \
+    if (h0 | h1 | h2 | h3) {                                          \
+      FP_PUT(v.x, iu, h0) FP_PUT(v.y, iu + 1, h1) FP_PUT(v.z, iu + 2, h2) FP_PUT(v.w, iu + 3, h3) \
+    }                                                                 \
+  }
 #ifndef ABL_NOPASS2
 #pragma unroll 1
       for (int c = 0; c < nchunk; ++c) {
@@ -307,7 +317,10 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
 #ifdef ABL_NOPICK
         if (v4[0].x == 12345.678f) mycnt += i00;
 #else
-        PAIR_EACH(FP_PICK)
+        _Pragma("unroll") for (int u = 0; u < 4; ++u) {
+          const int iu = i00 + u * kHT * 4;
+          if (iu < V) FP_PICK4(v4[u], iu)
+        }
 #endif
         PAIR_STAGE_END()
       }

@@ -746,9 +746,21 @@ __global__ void __launch_bounds__(kT3, 4) seq_sample_kernel(const __grid_constan
     }
     bar3();
   }
+  // the noise slice does not depend on the records: put its loads in flight first
+  const float* nz = P.noise + (long long)b * P.noise_sb;
+  const int s0 = slice * kSlice3;
+  float4 nv4[kSlice3 / (4 * kT3)];
+#pragma unroll
+  for (int u = 0; u < kSlice3 / (4 * kT3); ++u) {
+    const int i0 = s0 + u * 4 * kT3 + 4 * tid;
+    if (i0 < V) nv4[u] = __ldg(reinterpret_cast<const float4*>(nz + i0));
+  }
+  // every record of the sequence is read ONCE (one L2 round trip) and kept in shared memory
+  __shared__ RowRecord srec[2 * 64 + 1];
+  if (tid <= 2 * gamma) srec[tid] = load_record(&P.records[base + tid]);
+  bar3();
   if (tid < gamma) {
-    const RowRecord rq = load_record(&P.records[base + 2 * tid]);
-    const RowRecord rp = load_record(&P.records[base + 2 * tid + 1]);
+    const RowRecord rq = srec[2 * tid], rp = srec[2 * tid + 1];
     const int accept = P.r[(long long)b * P.r_sb + tid] <= __fdiv_rn(rp.sel, rq.sel);  // raw IEEE division
     sc.seq_acc[tid] = accept;
     if (slice == 0) {
@@ -762,16 +774,14 @@ __global__ void __launch_bounds__(kT3, 4) seq_sample_kernel(const __grid_constan
   int n = 0;
   while (n < gamma && sc.seq_acc[n] != 0) ++n;
   const bool bonus = (n == gamma);
-  const RowRecord rp = load_record(&P.records[base + (bonus ? 2 * gamma : 2 * n + 1)]);
-  const RowRecord rq = bonus ? rp : load_record(&P.records[base + 2 * n]);
+  const RowRecord rp = srec[bonus ? 2 * gamma : 2 * n + 1];
+  const RowRecord rq = bonus ? rp : srec[2 * n];
   const TIn* prow = split_row<TIn>(P, RowJob{b, n, 1});
   const TIn* qrow = bonus ? prow : split_row<TIn>(P, RowJob{b, n, 0});
-  const float* nz = P.noise + (long long)b * P.noise_sb;
   const float invZp = __frcp_rn(rp.Z), invZq = __frcp_rn(rq.Z);
 
   float mass = 0.0f, bkey = -1.0f, bdv = -INFINITY;
   int bidx = 0x7fffffff, bdi = 0x7fffffff;
-  const int s0 = slice * kSlice3;
 #pragma unroll
   for (int u = 0; u < kSlice3 / (4 * kT3); ++u) {
     const int i0 = s0 + u * 4 * kT3 + 4 * tid;
@@ -779,7 +789,7 @@ __global__ void __launch_bounds__(kT3, 4) seq_sample_kernel(const __grid_constan
       float4 xp = load4_scaled<TIn>(prow + i0, P.t_temp);
       float4 xq = make_float4(0.f, 0.f, 0.f, 0.f);
       if (!bonus) xq = load4_scaled<TIn>(qrow + i0, P.d_temp);
-      float4 nv = __ldg(reinterpret_cast<const float4*>(nz + i0));
+      float4 nv = nv4[u];
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         const float x = f4c(xp, k);

@@ -55,13 +55,13 @@ def set_team_size(team: int) -> None:
     lib.duodec_set_team_size(int(team))
 
 
-FAST_PATH = 3  # row-ring scan kernel + sliced sample kernel
+FAST_PATH = 5  # row-pair scan kernel + sliced sample kernel
 
 
 def set_stream_path(path) -> None:
-    """Test hook: device path of verify_fused.  True: the default fast path (3, row-ring scan kernel);
+    """Test hook: device path of verify_fused.  True: the default fast path (5, row-pair scan kernel);
     False / 0: the general team kernel; 1: sliced scan kernel; 2: first-generation persistent kernel;
-    4: resident-row scan kernel (experimental)."""
+    3: row-ring scan kernel; 4: resident-row scan kernel (experimental)."""
     if isinstance(path, bool):
         path = FAST_PATH if path else 0
     lib.duodec_set_stream_path(int(path))

@@ -47,8 +47,9 @@ int duodec_team_size(int V, int rows_resident);
 void duodec_set_team_size(int team);
 
 /* Device path of duodec_verify_fused for calls that qualify (equal vocabularies, 16-byte
- * aligned rows, no top-k, T > 0): 3 (default) row-ring scan kernel + sliced sample kernel,
- * 4 resident-row scan kernel, 1 sliced scan kernel, 2 first-generation persistent kernel;
+ * aligned rows, no top-k, T > 0): 5 (default) row-pair scan kernel + sliced sample kernel,
+ * 3 row-ring scan kernel, 4 resident-row scan kernel, 1 sliced scan kernel, 2 first-generation
+ * persistent kernel;
  * 0 forces the general team kernel, which every other call takes anyway (test hook). */
 void duodec_set_stream_path(int enabled);
 
