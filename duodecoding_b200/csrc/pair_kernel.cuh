@@ -45,9 +45,26 @@ struct __align__(16) PairSync {
   int pad;
 };
 
+// Scratch of one half's own select (half_select below): the level histogram in native 32-bit
+// shared-memory atomics - count, and the 38-bit fixed-point mass split into two 19-bit parts.
+struct __align__(16) HalfScratch {
+  unsigned hcnt[kHT], hlo[kHT], hhi[kHT];
+  unsigned long long cand_f[kHT];
+  float cand_x[kHT];
+  int cand_i[kHT];
+  unsigned long long wscan[kHW];
+  float2 red[kHW];
+  unsigned long long gb_new, lastkey;
+  unsigned kmin, kmax;
+  int bstar, bcount, ncand, res_ok;
+  float res_x;
+  int res_i;
+  int pad[2];
+};
+
 constexpr size_t pair_smem_bytes() {
   return size_t(2) * kPStages * kStageBytes + size_t(kHB) * kT3 * 4 + size_t(kPairCap + 2 * kOvfHalf) * sizeof(ListEntry) +
-         sizeof(Scratch3) + sizeof(PairSync) + 128;
+         sizeof(Scratch3) + sizeof(PairSync) + 2 * sizeof(HalfScratch) + 128;
 }
 
 __device__ __forceinline__ void barh(int h) {  // named barrier of one half (immediate ids: 2 and 3)
@@ -73,11 +90,39 @@ __device__ __forceinline__ void barh(int h) {  // named barrier of one half (imm
   __syncwarp();                                                                               \
   if (lane == 0) mbar_arrive(&ps->empty[h][slot]);                                            \
   ++seq;
+#ifdef PAIR_ONEBRANCH
+// one branch per stage: only the row's last stage can be ragged
+#define PAIR_EACH(F)                                                                          \
+  if (i00 + 3 * kHT * 4 < V) {                                                                \
+    _Pragma("unroll") for (int u = 0; u < 4; ++u) {                                           \
+      const int iu = i00 + u * kHT * 4;                                                       \
+      F(v4[u].x, iu) F(v4[u].y, iu + 1) F(v4[u].z, iu + 2) F(v4[u].w, iu + 3)                 \
+    }                                                                                         \
+  } else {                                                                                    \
+    _Pragma("unroll") for (int u = 0; u < 4; ++u) {                                           \
+      const int iu = i00 + u * kHT * 4;                                                       \
+      if (iu < V) { F(v4[u].x, iu) F(v4[u].y, iu + 1) F(v4[u].z, iu + 2) F(v4[u].w, iu + 3) } \
+    }                                                                                         \
+  }
+#define PAIR_EACH4(G)                                                                         \
+  if (i00 + 3 * kHT * 4 < V) {                                                                \
+    _Pragma("unroll") for (int u = 0; u < 4; ++u) { G(v4[u]) }                                \
+  } else {                                                                                    \
+    _Pragma("unroll") for (int u = 0; u < 4; ++u) {                                           \
+      if (i00 + u * kHT * 4 < V) { G(v4[u]) }                                                 \
+    }                                                                                         \
+  }
+#else
 #define PAIR_EACH(F)                                                                          \
   _Pragma("unroll") for (int u = 0; u < 4; ++u) {                                             \
     const int iu = i00 + u * kHT * 4;                                                         \
     if (iu < V) { F(v4[u].x, iu) F(v4[u].y, iu + 1) F(v4[u].z, iu + 2) F(v4[u].w, iu + 3) }   \
   }
+#define PAIR_EACH4(G)                                                                         \
+  _Pragma("unroll") for (int u = 0; u < 4; ++u) {                                             \
+    if (i00 + u * kHT * 4 < V) { G(v4[u]) }                                                   \
+  }
+#endif
 
 // smallest float x whose histogram bucket (hist_bits of x*log2e - m0) is >= bits; false if the search
 // does not settle (the caller then takes the general search)
@@ -89,6 +134,202 @@ __device__ __forceinline__ bool bucket_edge(int bits, float m0, float* edge) {
   *edge = g;
   return it < 256 && hist_bits(fmaf(g, kLog2e, -m0)) >= bits &&
          hist_bits(fmaf(nextafterf(g, -INFINITY), kLog2e, -m0)) < bits;
+}
+
+// Nucleus boundary of one row by ITS OWN half (128 threads, half barrier), so that the two rows of a
+// pair are finished side by side.  Same exact arithmetic and the same answer as list_select_body
+// (split_kernels.cuh): 38-bit fixed-point masses, a level of 128 value buckets over the entries'
+// value range, suffix scan, all-pairs order of the <= 128 entries of the crossing bucket.  The
+// entries are this thread's list column (col[j * 256], j < mycnt) and its share of the half's
+// overflow list.  Returns false when the row needs the tie bisection: the caller then runs
+// list_select_body with the whole block.
+__device__ __forceinline__ bool half_select(const ListEntry* col, int mycnt, const ListEntry* ovf, int novf, int h,
+                                            int ht, float GB, float Zrow, double target, float m0, HalfScratch* hs,
+                                            RowRecord& rec, int* ncand_out) {
+  constexpr int kPer = kColD + kOvfHalf / kHT;
+  constexpr unsigned long long kNone = 0xffffffffffffffffull;
+  const int lane = ht & 31, hw = ht >> 5;
+  const int ez = int(__float_as_uint(Zrow) >> 23) - 126;               // Z = f * 2^ez, f in [0.5, 1)
+  const float S = __uint_as_float(unsigned(127 + 38 - ez) << 23);      // 2^(38 - ez)
+  const unsigned long long tgt = (unsigned long long)(target * double(S));  // floor
+  unsigned long long GBf = (unsigned long long)(double(GB) * double(S));    // floor: GBf <= tgt
+  auto entry = [&](int j) { return j < kColD ? &col[j * kT3] : &ovf[(j - kColD) * kHT + ht]; };
+  auto fx = [&](float x) { return __float2ull_rn(row_exp(x, m0) * S); };  // fixed-point mass of an entry
+  float cx[kPer];
+  float emx = -INFINITY, engmn = -INFINITY;
+#pragma unroll
+  for (int j = 0; j < kPer; ++j) {
+    const bool have = j < kColD ? j < mycnt : (j - kColD) * kHT + ht < novf;
+    float x = -INFINITY;
+    if (have) {
+      x = ld_list_x(entry(j));
+      emx = fmaxf(emx, x), engmn = fmaxf(engmn, -x);
+    }
+    cx[j] = x;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    emx = fmaxf(emx, __shfl_xor_sync(0xffffffffu, emx, o));
+    engmn = fmaxf(engmn, __shfl_xor_sync(0xffffffffu, engmn, o));
+  }
+  if (lane == 0) hs->red[hw] = make_float2(emx, engmn);
+  barh(h);
+#pragma unroll
+  for (int w = 0; w < kHW; ++w) emx = fmaxf(emx, hs->red[w].x), engmn = fmaxf(engmn, hs->red[w].y);
+  float A = -engmn, B = nextafterf(emx, INFINITY);  // the bracket is the value range of the entries
+  bool solved = false, tie_mode = false;
+  *ncand_out = 0;
+#pragma unroll 1
+  for (int level = 0; level < 8 && !solved && !tie_mode; ++level) {
+    hs->hcnt[ht] = 0u, hs->hlo[ht] = 0u, hs->hhi[ht] = 0u;
+    if (ht == 0) {
+      hs->bstar = -1;
+      hs->kmin = 0xffffffffu;
+      hs->kmax = 0u;
+      hs->ncand = 0;
+      hs->res_ok = 0;
+      hs->lastkey = kNone;
+    }
+    barh(h);
+    const float bsc = float(kHT) / (B - A);
+    auto bucket = [&](float x) {
+      const int bk = int((x - A) * bsc);
+      return bk < 0 ? 0 : (bk > kHT - 1 ? kHT - 1 : bk);
+    };
+#pragma unroll
+    for (int j = 0; j < kPer; ++j) {
+      if (cx[j] >= A && cx[j] < B) {
+        const int bk = bucket(cx[j]);
+        const unsigned long long f = fx(cx[j]);
+        atomicAdd(&hs->hcnt[bk], 1u);
+        atomicAdd(&hs->hlo[bk], unsigned(f) & 0x7ffffu);
+        atomicAdd(&hs->hhi[bk], unsigned(f >> 19));
+      }
+    }
+    barh(h);
+    // suffix scan over buckets 127..0 (thread t owns bucket 127 - t)
+    const unsigned hc = hs->hcnt[kHT - 1 - ht];
+    const unsigned long long hv = ((unsigned long long)hs->hhi[kHT - 1 - ht] << 19) + hs->hlo[kHT - 1 - ht];
+    unsigned long long inc = hv;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const unsigned long long o = __shfl_up_sync(0xffffffffu, inc, d);
+      if (lane >= d) inc += o;
+    }
+    if (lane == 31) hs->wscan[hw] = inc;
+    barh(h);
+#pragma unroll
+    for (int w = 0; w < kHW; ++w)
+      if (w < hw) inc += hs->wscan[w];
+    const unsigned long long m_incl = GBf + inc, m_excl = m_incl - hv;
+    if (hc != 0u && m_incl > tgt && m_excl <= tgt) {
+      hs->bstar = kHT - 1 - ht;
+      hs->gb_new = m_excl;
+      hs->bcount = int(hc);
+    }
+    if (ht == kHT - 1 && m_incl <= tgt) hs->bstar = -2;  // rounding only: the whole bracket is kept
+    barh(h);
+    const int bstar = hs->bstar;
+    if (bstar < 0) {
+      // keep everything down to the last entry of the bracket in the reference's order
+      unsigned long long kk = kNone;
+#pragma unroll
+      for (int j = 0; j < kPer; ++j) {
+        if (cx[j] >= A && cx[j] < B) {
+          const unsigned idx = unsigned(ld_list_i(entry(j)));
+          const unsigned long long k2 = ((unsigned long long)okey(cx[j]) << 32) | (0xffffffffu - idx);
+          kk = k2 < kk ? k2 : kk;
+        }
+      }
+      if (kk != kNone) atomicMin(&hs->lastkey, kk);
+      barh(h);
+      const unsigned long long lk = hs->lastkey;
+      if (ht == kHT - 1) hs->gb_new = m_incl;  // the bracket's total is this thread's inclusive sum
+      barh(h);
+      if (lk != kNone) {
+        rec.Z = float(double(hs->gb_new) / double(S));
+        rec.xstar = okey_inv(unsigned(lk >> 32));
+        rec.istar = int(0xffffffffu - unsigned(lk & 0xffffffffull));
+        solved = true;
+      } else {
+        tie_mode = true;
+      }
+      break;
+    }
+    const int bcount = hs->bcount;
+    const unsigned long long gb_new = hs->gb_new;
+    if (bcount <= kHT) {
+      // ---- the bucket's entries, ordered exactly like the reference's sort
+#pragma unroll
+      for (int j = 0; j < kPer; ++j) {
+        if (cx[j] >= A && cx[j] < B && bucket(cx[j]) == bstar) {
+          const int pos = atomicAdd(&hs->ncand, 1);
+          hs->cand_x[pos] = cx[j];
+          hs->cand_f[pos] = fx(cx[j]);
+          hs->cand_i[pos] = ld_list_i(entry(j));
+        }
+      }
+      barh(h);
+      const int n = hs->ncand;
+      *ncand_out = n;
+      int Pn = 16;
+      while (Pn < n) Pn <<= 1;
+      const int parts = kHT / Pn;  // 1..8 threads share one candidate (same warp)
+      const int t = ht / parts, part = ht - t * parts;
+      unsigned long long cum = 0ull, fme = 0ull;
+      float xx = 0.0f;
+      int ii = 0;
+      if (t < n) {
+        fme = hs->cand_f[t], xx = hs->cand_x[t], ii = hs->cand_i[t];
+        for (int j = part; j < n; j += parts) {
+          const float xj = hs->cand_x[j];
+          const int ij = hs->cand_i[j];
+          if (xj > xx || (xj == xx && ij <= ii)) cum += hs->cand_f[j];
+        }
+      }
+      for (int o = parts >> 1; o > 0; o >>= 1) cum += __shfl_xor_sync(0xffffffffu, cum, o);
+      const unsigned long long incl = gb_new + cum;
+      if (t < n && part == 0 && incl > tgt && incl - fme <= tgt) {
+        hs->res_x = xx;
+        hs->res_i = ii;
+        hs->gb_new = incl;
+        hs->res_ok = 1;
+      }
+      barh(h);
+      if (hs->res_ok) {
+        solved = true;
+        rec.Z = float(double(hs->gb_new) / double(S));
+        rec.xstar = hs->res_x;
+        rec.istar = hs->res_i;
+      } else {
+        tie_mode = true;  // cannot happen with exact sums; stay safe
+      }
+      break;
+    }
+    // crowded bucket: shrink the bracket to the bucket's value range and go one level down
+#pragma unroll
+    for (int j = 0; j < kPer; ++j) {
+      if (cx[j] >= A && cx[j] < B && bucket(cx[j]) == bstar) {
+        atomicMin(&hs->kmin, okey(cx[j]));
+        atomicMax(&hs->kmax, okey(cx[j]));
+      }
+    }
+    barh(h);
+    const unsigned kmin = hs->kmin, kmax = hs->kmax;
+    A = okey_inv(kmin);
+    B = nextafterf(okey_inv(kmax), INFINITY);
+    GBf = gb_new;
+    if (kmin == kmax) tie_mode = true;  // more equal values than the finish can order
+    barh(h);
+  }
+  return solved;
+}
+
+// The whole block's select of one row (rows half_select hands back: ties).  Out of line: rare.
+__device__ __noinline__ void joint_select(const ListEntry* slist, int mine, float GB, float Z, double target, float m0,
+                                          Scratch3* sc, int& phase, RowRecord& rec, int* stats, const ListEntry* ovf,
+                                          int novf) {
+  list_select_body<kPairCap>(slist, 0, mine, 0.0f, 0.0f, GB, Z, target, m0, sc, phase, rec, stats, ovf, novf);
 }
 
 // General search of one row by the 256 workers (rare): exact row maximum first, then the windowed
@@ -118,6 +359,7 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
   ListEntry* sovf = slist + kPairCap;
   Scratch3* sc = reinterpret_cast<Scratch3*>(sovf + 2 * kOvfHalf);
   PairSync* ps = reinterpret_cast<PairSync*>(sc + 1);
+  HalfScratch* hsc = reinterpret_cast<HalfScratch*>(ps + 1);
 
   const int tid = threadIdx.x;
   const int gamma = P.gamma, V = P.V;
@@ -137,6 +379,9 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
     ps->novf[0] = ps->novf[1] = 0;
   }
   __syncthreads();
+  // nothing above touches global memory; inputs, hints and the workspace are ordered from here on
+  grid_dep_wait();
+  grid_dep_launch();
 
   if (tid >= kT3) {
     // ---- producers: lane 0 of warp 8 feeds half 0, lane 0 of warp 9 feeds half 1
@@ -239,7 +484,25 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
     float* a = hp + (hist_bits(t) - bits0) * kHT;     \
     *a += ex2_approx(t);                              \
   }
+// two entries per round: both bucket cells are read before either is written (the second takes the
+// first's sum when the two fall into the same cell), which halves the dependent shared-memory chain
+#define FP_HIST2(xa_, xb_)                                          \
+  {                                                                 \
+    const float t0 = fmaf(xa_, kLog2e, -m0), t1 = fmaf(xb_, kLog2e, -m0); \
+    float* a0 = hp + (hist_bits(t0) - bits0) * kHT;                 \
+    float* a1 = hp + (hist_bits(t1) - bits0) * kHT;                 \
+    const float h0 = *a0, h1 = *a1;                                 \
+    const float s0 = h0 + ex2_approx(t0);                           \
+    const float s1 = (a1 == a0 ? s0 : h1) + ex2_approx(t1);         \
+    *a0 = s0;                                                       \
+    *a1 = s1;                                                       \
+  }
+#define FP_HIST4(v) FP_HIST2(v.x, v.y) FP_HIST2(v.z, v.w)
+#ifdef PAIR_RMW2
+        PAIR_EACH4(FP_HIST4)
+#else
         PAIR_EACH(FP_HIST)
+#endif
         PAIR_STAGE_END()
       }
       barh(h);
@@ -290,8 +553,7 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
         if (bstar < kHB - 1 && !bucket_edge(bits0 + bstar + 1, m0, &xb)) slow = true;
         if (slow) xa = INFINITY;
       }
-      // a hit goes to this thread's list column (predicated store, no divergence inside a group of four);
-      // groups without a hit - most of them - cost eight compares
+      // a hit goes to this thread's list column, beyond its depth to the half's overflow list
 #define FP_PUT(x, i, hit)                                             \
   if (hit) {                                                          \
     if (mycnt < kColD) {                                              \
@@ -302,14 +564,6 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
     }                                                                 \
     ++mycnt;                                                          \
   }
-#define FP_PICK4(v, iu)                                               \
-  {                                                                   \
-    const bool h0 = v.x >= xa && v.x < xb, h1 = v.y >= xa && v.y < xb; \
-    const bool h2 = v.z >= xa && v.z < xb, h3 = v.w >= xa && v.w < xb; \
-    if (h0 | h1 | h2 | h3) {                                          \
-      FP_PUT(v.x, iu, h0) FP_PUT(v.y, iu + 1, h1) FP_PUT(v.z, iu + 2, h2) FP_PUT(v.w, iu + 3, h3) \
-    }                                                                 \
-  }
 #ifndef ABL_NOPASS2
 #pragma unroll 1
       for (int c = 0; c < nchunk; ++c) {
@@ -317,9 +571,24 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
 #ifdef ABL_NOPICK
         if (v4[0].x == 12345.678f) mycnt += i00;
 #else
+        // hit mask of the thread's 16 entries first (two compares and a bit each), then one trip per hit:
+        // the entry is read back from the stage by its position
+        unsigned hm = 0;
         _Pragma("unroll") for (int u = 0; u < 4; ++u) {
-          const int iu = i00 + u * kHT * 4;
-          if (iu < V) FP_PICK4(v4[u], iu)
+          if (i00 + u * kHT * 4 < V) {
+            hm |= (v4[u].x >= xa && v4[u].x < xb) ? (1u << (4 * u)) : 0u;
+            hm |= (v4[u].y >= xa && v4[u].y < xb) ? (2u << (4 * u)) : 0u;
+            hm |= (v4[u].z >= xa && v4[u].z < xb) ? (4u << (4 * u)) : 0u;
+            hm |= (v4[u].w >= xa && v4[u].w < xb) ? (8u << (4 * u)) : 0u;
+          }
+        }
+        while (hm) {
+          const int k = __ffs(hm) - 1;
+          hm &= hm - 1;
+          const int off = ((k >> 2) * kHT + ht) * 4 + (k & 3);
+          float x = to_f32(reinterpret_cast<const TIn*>(st)[off]);
+          if (temp != 1.0f) x = __fdiv_rn(x, temp);
+          FP_PUT(x, (c) * kStageElems + off, true)
         }
 #endif
         PAIR_STAGE_END()
@@ -330,47 +599,58 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
       state = 4;
 #endif
     }
+    // ---- each half closes its own row: the two selects of a pair run side by side
+    RowRecord rec;
+    rec.m0 = m0, rec.Z = Z, rec.xstar = -INFINITY, rec.istar = 0x7fffffff;
+    rec.sel = 0.0f, rec.mxl = mxl, rec.dens = 0.0f;
+    if (state == 2) {
+      barh(h);  // the half's list columns and its overflow count are complete
+      const int novf = ps->novf[h];
+      if (novf > kOvfHalf) {
+        state = 3;  // more overflow than the list holds: general search below
+      } else {
+        int ncand = 0;
+        const bool ok = half_select(col, mycnt, sovf + h * kOvfHalf, novf, h, ht, GB, Z, target, m0, hsc + h, rec, &ncand);
+        if (!ok) state = 5;  // ties: the whole block's bisection below
+        if (P.stats && ht == 0) {
+          atomicAdd(&P.stats[0], 1);
+          atomicAdd(&P.stats[ok ? 16 : 17], 1);
+          atomicAdd(&P.stats[18], ncand);
+        }
+      }
+    }
     if (ht == 0) {
       HalfRow hr;
       hr.target = target, hr.GB = GB, hr.Z = Z, hr.m0 = m0, hr.mxl = mxl, hr.state = state;
       hr.pad[0] = hr.pad[1] = hr.pad[2] = 0;
       ps->half[h] = hr;
-    }
-    bar3();  // ---- the halves join: both rows' parameters and list columns are visible
-
-    int st[2] = {ps->half[0].state, ps->half[1].state};
-#pragma unroll
-    for (int hh = 0; hh < 2; ++hh) {
-      if (st[hh] == 0) continue;
-      const HalfRow hr = ps->half[hh];
-      RowRecord rec;
-      rec.m0 = hr.m0, rec.Z = hr.Z, rec.xstar = -INFINITY, rec.istar = 0x7fffffff;
-      rec.sel = 0.0f, rec.mxl = hr.mxl, rec.dens = 0.0f;
-      if (st[hh] == 2) {
-        const int mine = (h == hh) ? mycnt : 0;
-        const int novf = ps->novf[hh];
-        if (novf > kOvfHalf) {
-          st[hh] = 3;  // more overflow than the list holds: general search below
-        } else {
-          if (P.stats) {
-            const int n = reduce3_small(mine, OpSumI(), sc, phase);
-            if (tid == 0) {
-              atomicAdd(&P.stats[0], 1);
-              atomicAdd(&P.stats[16], 1);
-              atomicAdd(&P.stats[21], n);
-              atomicMax(&P.stats[22], n);
-            }
-          }
-          list_select_body<kPairCap>(slist, 0, mine, 0.0f, 0.0f, hr.GB, hr.Z, hr.target, hr.m0, sc, phase, rec,
-                                     P.stats, sovf + hh * kOvfHalf, novf);
-        }
-      }
-      if (st[hh] != 3 && tid == hh * kHT) {
+      if (state == 1 || state == 2 || state == 4) {
         if (tok >= 0 && tok < V) {
           const float e = kept(rec, xtok, int(tok)) ? row_exp(xtok, rec.m0) : 0.0f;
           rec.sel = __fdiv_rn(e, rec.Z);
         }
-        store_record(&P.records[2 * pr + hh], rec);
+        store_record(&P.records[2 * pr + h], rec);
+      }
+    }
+    bar3();  // ---- the halves join: rows that need the whole block (rare) are finished one after the other
+
+    const int st[2] = {ps->half[0].state, ps->half[1].state};
+#pragma unroll 1
+    for (int hh = 0; hh < 2; ++hh) {
+      if (st[hh] != 5) continue;
+      const HalfRow hr = ps->half[hh];
+      RowRecord r2;
+      r2.m0 = hr.m0, r2.Z = hr.Z, r2.xstar = -INFINITY, r2.istar = 0x7fffffff;
+      r2.sel = 0.0f, r2.mxl = hr.mxl, r2.dens = 0.0f;
+      const int mine = (h == hh) ? mycnt : 0;
+      joint_select(slist, mine, hr.GB, hr.Z, hr.target, hr.m0, sc, phase, r2, P.stats, sovf + hh * kOvfHalf,
+                   ps->novf[hh]);
+      if (tid == hh * kHT) {
+        if (tok >= 0 && tok < V) {
+          const float e = kept(r2, xtok, int(tok)) ? row_exp(xtok, r2.m0) : 0.0f;
+          r2.sel = __fdiv_rn(e, r2.Z);
+        }
+        store_record(&P.records[2 * pr + hh], r2);
       }
     }
 #pragma unroll 1

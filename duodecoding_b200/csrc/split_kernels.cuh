@@ -37,6 +37,12 @@ __device__ __forceinline__ void bar3() { asm volatile("bar.sync 1, 256;" ::: "me
 struct RowPartial {
   float mx, z, ghi, gwin;
 };
+// Programmatic dependent launch (stream_launch.cu: launch_pdl).  wait: everything the previous kernel
+// in the stream wrote is visible afterwards (no-op for a plain launch); launch: the next kernel in
+// the stream may start becoming resident.
+__device__ __forceinline__ void grid_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void grid_dep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 struct ListEntry {
   float x;
   int idx;
@@ -705,7 +711,23 @@ __global__ void __launch_bounds__(kT3, 4) seq_sample_kernel(const __grid_constan
   const int gamma = P.gamma, V = P.V;
   const int base = b * (2 * gamma + 1);
 
-  if (slice == 0 && b == 0) {
+  // the noise slice does not depend on the scan kernel: its loads go out before the grid dependency
+  // resolves (the caller wrote the noise before the scan kernel was launched)
+  const float* nz = P.noise + (long long)b * P.noise_sb;
+  const int s0 = slice * kSlice3;
+  float4 nv4[kSlice3 / (4 * kT3)];
+#pragma unroll
+  for (int u = 0; u < kSlice3 / (4 * kT3); ++u) {
+    const int i0 = s0 + u * 4 * kT3 + 4 * tid;
+    if (i0 < V && b < P.B) nv4[u] = __ldg(reinterpret_cast<const float4*>(nz + i0));
+  }
+  float rj = 0.0f;  // the acceptance draw of position tid: an input as well
+  if (b < P.B && tid < gamma) rj = __ldg(&P.r[(long long)b * P.r_sb + tid]);
+  grid_dep_wait();
+  grid_dep_launch();
+
+  if (b == P.B) {  // the extra block row: block 0 of it aggregates the next launch's prediction, off the critical path
+    if (slice != 0) return;
     // prediction for the next launch, per row kind: mean exponent offset, mean / spread of the
     // nucleus boundary and mean list density over this launch's rows (fixed order: deterministic)
     int phase = 0;
@@ -744,16 +766,7 @@ __global__ void __launch_bounds__(kT3, 4) seq_sample_kernel(const __grid_constan
         P.hints[kind] = hn;
       }
     }
-    bar3();
-  }
-  // the noise slice does not depend on the records: put its loads in flight first
-  const float* nz = P.noise + (long long)b * P.noise_sb;
-  const int s0 = slice * kSlice3;
-  float4 nv4[kSlice3 / (4 * kT3)];
-#pragma unroll
-  for (int u = 0; u < kSlice3 / (4 * kT3); ++u) {
-    const int i0 = s0 + u * 4 * kT3 + 4 * tid;
-    if (i0 < V) nv4[u] = __ldg(reinterpret_cast<const float4*>(nz + i0));
+    return;
   }
   // every record of the sequence is read ONCE (one L2 round trip) and kept in shared memory
   __shared__ RowRecord srec[2 * 64 + 1];
@@ -761,7 +774,7 @@ __global__ void __launch_bounds__(kT3, 4) seq_sample_kernel(const __grid_constan
   bar3();
   if (tid < gamma) {
     const RowRecord rq = srec[2 * tid], rp = srec[2 * tid + 1];
-    const int accept = P.r[(long long)b * P.r_sb + tid] <= __fdiv_rn(rp.sel, rq.sel);  // raw IEEE division
+    const int accept = rj <= __fdiv_rn(rp.sel, rq.sel);  // raw IEEE division
     sc.seq_acc[tid] = accept;
     if (slice == 0) {
       const long long o = (long long)b * gamma + tid;

@@ -47,6 +47,24 @@ int stream_sm_count() {
   return cached[dev];
 }
 
+// Launch with programmatic stream serialization: the kernel may become resident while the one
+// before it in the stream drains; it orders itself with griddepcontrol.wait (grid_dep_wait()).
+template <class... KArgs, class... Args>
+cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                       Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
+
 }  // namespace
 
 constexpr int kMaxSlices = 32;  // row_scan slices the workspace is sized for (V <= 262144)
@@ -121,7 +139,7 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
     w += size_t(c.B) * 4;
     Q.lists = reinterpret_cast<ListEntry*>(w);
     Q.stats = c.stats;
-    const dim3 g1(unsigned(Q.S), unsigned(rows)), g2(unsigned((c.Vt + kSlice3 - 1) / kSlice3), unsigned(c.B));
+    const dim3 g1(unsigned(Q.S), unsigned(rows)), g2(unsigned((c.Vt + kSlice3 - 1) / kSlice3), unsigned(c.B) + 1u);  // + the block row that aggregates the hints
     if (pairp) {
       const size_t smem = pair::pair_smem_bytes();
       const int sms = stream_sm_count();
@@ -131,14 +149,14 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
       if (c.dtype == DUODEC_F32) {
         e = ensure_stream_smem(reinterpret_cast<const void*>(pair::row_pair_kernel<float>), smem);
         if (e == cudaSuccess) {
-          if (c.phases & 1) pair::row_pair_kernel<float><<<grid, pair::kPT, smem, c.stream>>>(Q);
-          if (c.phases & 2) seq_sample_kernel<float><<<g2, kT3, 0, c.stream>>>(Q);
+          if (c.phases & 1) launch_pdl(pair::row_pair_kernel<float>, dim3(grid), dim3(pair::kPT), smem, c.stream, Q);
+          if (c.phases & 2) launch_pdl(seq_sample_kernel<float>, g2, dim3(kT3), 0, c.stream, Q);
         }
       } else {
         e = ensure_stream_smem(reinterpret_cast<const void*>(pair::row_pair_kernel<__nv_bfloat16>), smem);
         if (e == cudaSuccess) {
-          if (c.phases & 1) pair::row_pair_kernel<__nv_bfloat16><<<grid, pair::kPT, smem, c.stream>>>(Q);
-          if (c.phases & 2) seq_sample_kernel<__nv_bfloat16><<<g2, kT3, 0, c.stream>>>(Q);
+          if (c.phases & 1) launch_pdl(pair::row_pair_kernel<__nv_bfloat16>, dim3(grid), dim3(pair::kPT), smem, c.stream, Q);
+          if (c.phases & 2) launch_pdl(seq_sample_kernel<__nv_bfloat16>, g2, dim3(kT3), 0, c.stream, Q);
         }
       }
       *rc = int(e != cudaSuccess ? e : cudaGetLastError());
@@ -153,13 +171,13 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
         e = ensure_stream_smem(reinterpret_cast<const void*>(resident::row_resident_kernel<float>), smem);
         if (e == cudaSuccess) {
           if (c.phases & 1) resident::row_resident_kernel<float><<<grid, resident::kRT, smem, c.stream>>>(Q);
-          if (c.phases & 2) seq_sample_kernel<float><<<g2, kT3, 0, c.stream>>>(Q);
+          if (c.phases & 2) launch_pdl(seq_sample_kernel<float>, g2, dim3(kT3), 0, c.stream, Q);
         }
       } else {
         e = ensure_stream_smem(reinterpret_cast<const void*>(resident::row_resident_kernel<__nv_bfloat16>), smem);
         if (e == cudaSuccess) {
           if (c.phases & 1) resident::row_resident_kernel<__nv_bfloat16><<<grid, resident::kRT, smem, c.stream>>>(Q);
-          if (c.phases & 2) seq_sample_kernel<__nv_bfloat16><<<g2, kT3, 0, c.stream>>>(Q);
+          if (c.phases & 2) launch_pdl(seq_sample_kernel<__nv_bfloat16>, g2, dim3(kT3), 0, c.stream, Q);
         }
       }
       *rc = int(e != cudaSuccess ? e : cudaGetLastError());
@@ -174,13 +192,13 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
         e = ensure_stream_smem(reinterpret_cast<const void*>(row_ring_kernel<float>), smem);
         if (e == cudaSuccess) {
           if (c.phases & 1) row_ring_kernel<float><<<grid, kRT, smem, c.stream>>>(Q);
-          if (c.phases & 2) seq_sample_kernel<float><<<g2, kT3, 0, c.stream>>>(Q);
+          if (c.phases & 2) launch_pdl(seq_sample_kernel<float>, g2, dim3(kT3), 0, c.stream, Q);
         }
       } else {
         e = ensure_stream_smem(reinterpret_cast<const void*>(row_ring_kernel<__nv_bfloat16>), smem);
         if (e == cudaSuccess) {
           if (c.phases & 1) row_ring_kernel<__nv_bfloat16><<<grid, kRT, smem, c.stream>>>(Q);
-          if (c.phases & 2) seq_sample_kernel<__nv_bfloat16><<<g2, kT3, 0, c.stream>>>(Q);
+          if (c.phases & 2) launch_pdl(seq_sample_kernel<__nv_bfloat16>, g2, dim3(kT3), 0, c.stream, Q);
         }
       }
       *rc = int(e != cudaSuccess ? e : cudaGetLastError());
@@ -188,10 +206,10 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
     }
     if (c.dtype == DUODEC_F32) {
       if (c.phases & 1) row_scan_kernel<float><<<g1, kT3, 0, c.stream>>>(Q);
-      if (c.phases & 2) seq_sample_kernel<float><<<g2, kT3, 0, c.stream>>>(Q);
+      if (c.phases & 2) launch_pdl(seq_sample_kernel<float>, g2, dim3(kT3), 0, c.stream, Q);
     } else {
       if (c.phases & 1) row_scan_kernel<__nv_bfloat16><<<g1, kT3, 0, c.stream>>>(Q);
-      if (c.phases & 2) seq_sample_kernel<__nv_bfloat16><<<g2, kT3, 0, c.stream>>>(Q);
+      if (c.phases & 2) launch_pdl(seq_sample_kernel<__nv_bfloat16>, g2, dim3(kT3), 0, c.stream, Q);
     }
     *rc = int(cudaGetLastError());
     return true;
