@@ -23,9 +23,9 @@ constexpr int kPT = kT3 + 64;                    // 256 workers + one producer w
 #define DUODEC_PAIR_STAGES 2
 #endif
 constexpr int kPStages = DUODEC_PAIR_STAGES;     // 8 KB stages per half
-constexpr int kColD = 8;                         // list-column depth per worker thread (shared memory)
-constexpr int kPairCap = kColD * kT3;            // = the kCap of list_select: 2048
-constexpr int kOvfHalf = kT3;                    // overflow-list entries per row (shared memory)
+constexpr int kPairCap = 2048;                   // kCap of the block's list_select over one row's (compacted) list
+constexpr int kWarpCap = 320;                    // list entries per worker warp (shared memory): 4 x 320 per row
+constexpr int kHalfCap = kHW * kWarpCap;         // 1280
 
 struct __align__(16) HalfRow {
   double target;
@@ -41,8 +41,8 @@ struct __align__(16) PairSync {
   float2 hred[2][kHW];
   HalfRow half[2];
   int nlist;
-  int novf[2];  // overflow-list entries of the two rows
-  int pad;
+  int pad[3];
+  int wcnt[2][kHW];  // list entries of each worker warp
 };
 
 // Scratch of one half's own select (half_select below): the level histogram in native 32-bit
@@ -63,7 +63,7 @@ struct __align__(16) HalfScratch {
 };
 
 constexpr size_t pair_smem_bytes() {
-  return size_t(2) * kPStages * kStageBytes + size_t(kHB) * kT3 * 4 + size_t(kPairCap + 2 * kOvfHalf) * sizeof(ListEntry) +
+  return size_t(2) * kPStages * kStageBytes + size_t(kHB) * kT3 * 4 + size_t(2) * kHalfCap * sizeof(ListEntry) +
          sizeof(Scratch3) + sizeof(PairSync) + 2 * sizeof(HalfScratch) + 128;
 }
 
@@ -124,6 +124,13 @@ __device__ __forceinline__ void barh(int h) {  // named barrier of one half (imm
   }
 #endif
 
+// hm |= bit when xa <= x < xb: two compares into one predicate and a predicated OR
+__device__ __forceinline__ void hit_or(unsigned& hm, float x, float xa, float xb, unsigned bit) {
+  asm("{\n\t.reg .pred p;\n\tsetp.ge.f32 p, %1, %2;\n\tsetp.lt.and.f32 p, %1, %3, p;\n\t@p or.b32 %0, %0, %4;\n\t}"
+      : "+r"(hm)
+      : "f"(x), "f"(xa), "f"(xb), "r"(bit));
+}
+
 // smallest float x whose histogram bucket (hist_bits of x*log2e - m0) is >= bits; false if the search
 // does not settle (the caller then takes the general search)
 __device__ __forceinline__ bool bucket_edge(int bits, float m0, float* edge) {
@@ -140,26 +147,27 @@ __device__ __forceinline__ bool bucket_edge(int bits, float m0, float* edge) {
 // pair are finished side by side.  Same exact arithmetic and the same answer as list_select_body
 // (split_kernels.cuh): 38-bit fixed-point masses, a level of 128 value buckets over the entries'
 // value range, suffix scan, all-pairs order of the <= 128 entries of the crossing bucket.  The
-// entries are this thread's list column (col[j * 256], j < mycnt) and its share of the half's
-// overflow list.  Returns false when the row needs the tie bisection: the caller then runs
-// list_select_body with the whole block.
-__device__ __forceinline__ bool half_select(const ListEntry* col, int mycnt, const ListEntry* ovf, int novf, int h,
-                                            int ht, float GB, float Zrow, double target, float m0, HalfScratch* hs,
-                                            RowRecord& rec, int* ncand_out) {
-  constexpr int kPer = kColD + kOvfHalf / kHT;
+// row's entries sit in the half's list hl[4][320], one region per worker warp with wn[w] entries;
+// thread ht looks at the slots j * 128 + ht.  Returns false when the row needs the tie bisection:
+// the caller then runs list_select_body with the whole block.
+__device__ __forceinline__ bool half_select(const ListEntry* hl, const int* wn, int h, int ht, float GB, float Zrow,
+                                            double target, float m0, HalfScratch* hs, RowRecord& rec,
+                                            int* ncand_out) {
+  constexpr int kPer = kHalfCap / kHT;  // list slots of a thread: slot j * 128 + ht belongs to warp slot / 320
   constexpr unsigned long long kNone = 0xffffffffffffffffull;
   const int lane = ht & 31, hw = ht >> 5;
   const int ez = int(__float_as_uint(Zrow) >> 23) - 126;               // Z = f * 2^ez, f in [0.5, 1)
   const float S = __uint_as_float(unsigned(127 + 38 - ez) << 23);      // 2^(38 - ez)
   const unsigned long long tgt = (unsigned long long)(target * double(S));  // floor
   unsigned long long GBf = (unsigned long long)(double(GB) * double(S));    // floor: GBf <= tgt
-  auto entry = [&](int j) { return j < kColD ? &col[j * kT3] : &ovf[(j - kColD) * kHT + ht]; };
+  auto entry = [&](int j) { return &hl[j * kHT + ht]; };
   auto fx = [&](float x) { return __float2ull_rn(row_exp(x, m0) * S); };  // fixed-point mass of an entry
   float cx[kPer];
   float emx = -INFINITY, engmn = -INFINITY;
 #pragma unroll
   for (int j = 0; j < kPer; ++j) {
-    const bool have = j < kColD ? j < mycnt : (j - kColD) * kHT + ht < novf;
+    const int slot = j * kHT + ht, w = slot / kWarpCap;
+    const bool have = slot - w * kWarpCap < wn[w];
     float x = -INFINITY;
     if (have) {
       x = ld_list_x(entry(j));
@@ -326,10 +334,9 @@ __device__ __forceinline__ bool half_select(const ListEntry* col, int mycnt, con
 }
 
 // The whole block's select of one row (rows half_select hands back: ties).  Out of line: rare.
-__device__ __noinline__ void joint_select(const ListEntry* slist, int mine, float GB, float Z, double target, float m0,
-                                          Scratch3* sc, int& phase, RowRecord& rec, int* stats, const ListEntry* ovf,
-                                          int novf) {
-  list_select_body<kPairCap>(slist, 0, mine, 0.0f, 0.0f, GB, Z, target, m0, sc, phase, rec, stats, ovf, novf);
+__device__ __noinline__ void joint_select(const ListEntry* list, int nlist, float GB, float Z, double target, float m0,
+                                          Scratch3* sc, int& phase, RowRecord& rec, int* stats) {
+  list_select_body<kPairCap>(list, nlist, -1, 0.0f, 0.0f, GB, Z, target, m0, sc, phase, rec, stats);
 }
 
 // General search of one row by the 256 workers (rare): exact row maximum first, then the windowed
@@ -355,9 +362,8 @@ template <class TIn>
 __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant__ SplitParams P) {
   extern __shared__ __align__(128) unsigned char smem[];
   float* hist_all = reinterpret_cast<float*>(smem + size_t(2) * kPStages * kStageBytes);
-  ListEntry* slist = reinterpret_cast<ListEntry*>(hist_all + kHB * kT3);  // [kColD][256] columns, then 2 x overflow
-  ListEntry* sovf = slist + kPairCap;
-  Scratch3* sc = reinterpret_cast<Scratch3*>(sovf + 2 * kOvfHalf);
+  ListEntry* slist = reinterpret_cast<ListEntry*>(hist_all + kHB * kT3);  // [2 rows][4 warps][kWarpCap] entries
+  Scratch3* sc = reinterpret_cast<Scratch3*>(slist + 2 * kHalfCap);
   PairSync* ps = reinterpret_cast<PairSync*>(sc + 1);
   HalfScratch* hsc = reinterpret_cast<HalfScratch*>(ps + 1);
 
@@ -376,7 +382,6 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
       }
     mbar_fence_init();
     ps->nlist = 0;
-    ps->novf[0] = ps->novf[1] = 0;
   }
   __syncthreads();
   // nothing above touches global memory; inputs, hints and the workspace are ordered from here on
@@ -421,8 +426,6 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
   float* hp = hist + ht;
   const int bits0 = __float_as_int(kHTmin + kHMagic);
   ListEntry* list = P.lists + (long long)blockIdx.x * kListCap;
-  ListEntry* col = slist + tid;  // this thread's column (shared memory): entry j at slist[j * 256 + tid]
-  ListEntry* ovf_base = sovf;    // entries beyond a full column: the half's overflow list
   int phase = 0;
   unsigned seq = 0;
 #pragma unroll
@@ -448,7 +451,7 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
     const uint4 hint = __ldg(reinterpret_cast<const uint4*>(&P.hints[jb.is_target]));
     const float m0 = int(hint.w) != 0 ? __uint_as_float(hint.x) : 0.0f;
 
-    int mycnt = 0, state = 0;
+    int state = 0;
     float Z = 0.0f, mxl = m0, GB = 0.0f;
     double target = 0.0;
     if (have && !nucleus) {
@@ -553,47 +556,67 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
         if (bstar < kHB - 1 && !bucket_edge(bits0 + bstar + 1, m0, &xb)) slow = true;
         if (slow) xa = INFINITY;
       }
-      // a hit goes to this thread's list column, beyond its depth to the half's overflow list
-#define FP_PUT(x, i, hit)                                             \
-  if (hit) {                                                          \
-    if (mycnt < kColD) {                                              \
-      col[mycnt * kT3] = ListEntry{x, i};                             \
-    } else {                                                          \
-      const int pos = atomicAdd(&ps->novf[h], 1);                     \
-      if (pos < kOvfHalf) ovf_base[h * kOvfHalf + pos] = ListEntry{x, i}; \
-    }                                                                 \
-    ++mycnt;                                                          \
-  }
+      // Per stage: the 16-bit hit mask of the thread's entries (two compares and a bit each), a warp
+      // prefix sum of the hit counts, then one short trip per hit that copies the entry from the stage to
+      // the WARP's list region (any slot order will do) - no atomics, addresses in the shared window.
+      const unsigned wl_s = smem_u32(slist + (h * kHW + hw) * kWarpCap);
+      int wcnt = 0;
 #ifndef ABL_NOPASS2
 #pragma unroll 1
       for (int c = 0; c < nchunk; ++c) {
         PAIR_STAGE_BEGIN(c)
 #ifdef ABL_NOPICK
-        if (v4[0].x == 12345.678f) mycnt += i00;
+        if (v4[0].x == 12345.678f) wcnt += i00;
 #else
-        // hit mask of the thread's 16 entries first (two compares and a bit each), then one trip per hit:
-        // the entry is read back from the stage by its position
         unsigned hm = 0;
-        _Pragma("unroll") for (int u = 0; u < 4; ++u) {
-          if (i00 + u * kHT * 4 < V) {
-            hm |= (v4[u].x >= xa && v4[u].x < xb) ? (1u << (4 * u)) : 0u;
-            hm |= (v4[u].y >= xa && v4[u].y < xb) ? (2u << (4 * u)) : 0u;
-            hm |= (v4[u].z >= xa && v4[u].z < xb) ? (4u << (4 * u)) : 0u;
-            hm |= (v4[u].w >= xa && v4[u].w < xb) ? (8u << (4 * u)) : 0u;
+        if (i00 + 3 * kHT * 4 < V) {  // every stage but a row's last one is whole
+          _Pragma("unroll") for (int u = 0; u < 4; ++u) {
+            hit_or(hm, v4[u].x, xa, xb, 1u << (4 * u)), hit_or(hm, v4[u].y, xa, xb, 2u << (4 * u));
+            hit_or(hm, v4[u].z, xa, xb, 4u << (4 * u)), hit_or(hm, v4[u].w, xa, xb, 8u << (4 * u));
+          }
+        } else {
+          _Pragma("unroll") for (int u = 0; u < 4; ++u) {
+            if (i00 + u * kHT * 4 < V) {
+              hit_or(hm, v4[u].x, xa, xb, 1u << (4 * u)), hit_or(hm, v4[u].y, xa, xb, 2u << (4 * u));
+              hit_or(hm, v4[u].z, xa, xb, 4u << (4 * u)), hit_or(hm, v4[u].w, xa, xb, 8u << (4 * u));
+            }
           }
         }
-        while (hm) {
-          const int k = __ffs(hm) - 1;
-          hm &= hm - 1;
-          const int off = ((k >> 2) * kHT + ht) * 4 + (k & 3);
-          float x = to_f32(reinterpret_cast<const TIn*>(st)[off]);
-          if (temp != 1.0f) x = __fdiv_rn(x, temp);
-          FP_PUT(x, (c) * kStageElems + off, true)
+        if (__any_sync(0xffffffffu, hm != 0u)) {
+          const int nh = __popc(hm);
+          int inc = nh;
+          _Pragma("unroll") for (int d = 1; d < 32; d <<= 1) {
+            const int o = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= d) inc += o;
+          }
+          int pos = wcnt + inc - nh;
+          wcnt += __shfl_sync(0xffffffffu, inc, 31);
+          const unsigned st_s = smem_u32(st);
+          while (hm) {
+            const int k = __ffs(hm) - 1;
+            hm &= hm - 1;
+            const int off = ((k >> 2) * kHT + ht) * 4 + (k & 3);
+            float x;
+            if (kElt == 4) {
+              asm volatile("ld.shared.f32 %0, [%1];" : "=f"(x) : "r"(st_s + unsigned(off) * 4u));
+            } else {
+              unsigned short raw;
+              asm volatile("ld.shared.u16 %0, [%1];" : "=h"(raw) : "r"(st_s + unsigned(off) * 2u));
+              x = __uint_as_float(unsigned(raw) << 16);
+            }
+            if (temp != 1.0f) x = __fdiv_rn(x, temp);
+            if (pos < kWarpCap)
+              asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(wl_s + unsigned(pos) * 8u), "r"(__float_as_int(x)),
+                           "r"(c * kStageElems + off)
+                           : "memory");
+            ++pos;
+          }
         }
 #endif
         PAIR_STAGE_END()
       }
 #endif
+      if (lane == 0) ps->wcnt[h][hw] = wcnt;
       state = slow ? 3 : (bstar > 0 ? 2 : 4);
 #if defined(ABL_NOPASS2) || defined(ABL_NOSELECT) || defined(ABL_NOPICK)
       state = 4;
@@ -604,13 +627,15 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
     rec.m0 = m0, rec.Z = Z, rec.xstar = -INFINITY, rec.istar = 0x7fffffff;
     rec.sel = 0.0f, rec.mxl = mxl, rec.dens = 0.0f;
     if (state == 2) {
-      barh(h);  // the half's list columns and its overflow count are complete
-      const int novf = ps->novf[h];
-      if (novf > kOvfHalf) {
-        state = 3;  // more overflow than the list holds: general search below
+      barh(h);  // the half's four warp lists and their counts are complete
+      bool fits = true;
+#pragma unroll
+      for (int w = 0; w < kHW; ++w) fits = fits && ps->wcnt[h][w] <= kWarpCap;
+      if (!fits) {
+        state = 3;  // more entries than the list holds: general search below
       } else {
         int ncand = 0;
-        const bool ok = half_select(col, mycnt, sovf + h * kOvfHalf, novf, h, ht, GB, Z, target, m0, hsc + h, rec, &ncand);
+        const bool ok = half_select(slist + h * kHalfCap, ps->wcnt[h], h, ht, GB, Z, target, m0, hsc + h, rec, &ncand);
         if (!ok) state = 5;  // ties: the whole block's bisection below
         if (P.stats && ht == 0) {
           atomicAdd(&P.stats[0], 1);
@@ -642,9 +667,22 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
       RowRecord r2;
       r2.m0 = hr.m0, r2.Z = hr.Z, r2.xstar = -INFINITY, r2.istar = 0x7fffffff;
       r2.sel = 0.0f, r2.mxl = hr.mxl, r2.dens = 0.0f;
-      const int mine = (h == hh) ? mycnt : 0;
-      joint_select(slist, mine, hr.GB, hr.Z, hr.target, hr.m0, sc, phase, r2, P.stats, sovf + hh * kOvfHalf,
-                   ps->novf[hh]);
+      // the four warp regions become one list, then the block's select in its linear-list mode
+      ListEntry* hl = slist + hh * kHalfCap;
+      int total = ps->wcnt[hh][0];
+#pragma unroll 1
+      for (int w = 1; w < kHW; ++w) {
+        const int n = ps->wcnt[hh][w];
+        ListEntry t0 = ListEntry{0.0f, 0}, t1 = t0;
+        if (tid < n) t0 = hl[w * kWarpCap + tid];
+        if (tid + kT3 < n) t1 = hl[w * kWarpCap + tid + kT3];
+        bar3();
+        if (tid < n) hl[total + tid] = t0;
+        if (tid + kT3 < n) hl[total + tid + kT3] = t1;
+        bar3();
+        total += n;
+      }
+      joint_select(hl, total, hr.GB, hr.Z, hr.target, hr.m0, sc, phase, r2, P.stats);
       if (tid == hh * kHT) {
         if (tok >= 0 && tok < V) {
           const float e = kept(r2, xtok, int(tok)) ? row_exp(xtok, r2.m0) : 0.0f;
@@ -671,7 +709,6 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
         store_record(&P.records[2 * pr + hh], rec);
       }
     }
-    if (tid == 0) ps->novf[0] = ps->novf[1] = 0;
     bar3();  // lists, scratch and the half records are free for the next pair
   }
 }
