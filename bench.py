@@ -311,7 +311,7 @@ def run_ours(args):
         "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
         "traffic": traffic, "kernel": "pair::row_pair_kernel<float>", "alg_bytes_per_launch": alg_bytes,
         "us_per_launch": scan_us, "peak_source": peak_src, "frac_of_8TBps_nominal": achieved / 8000.0,
-        "step_us": us_launch, "step_kernels": ["pair::row_pair_kernel<float>", "seq_sample_kernel<float>"],
+        "step_us": us_launch, "step_kernels": ["pair::row_pair_kernel<float>", "seq_sample_tma_kernel<float>"],
         "step_frac": alg_bytes / (us_launch * 1e-6) / 1e9 / peak,
     }
 

@@ -387,6 +387,7 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
   // nothing above touches global memory; inputs, hints and the workspace are ordered from here on
   grid_dep_wait();
   grid_dep_launch();
+  if (tid == 0) STAMP(P.stats, 8, true);
 
   if (tid >= kT3) {
     // ---- producers: lane 0 of warp 8 feeds half 0, lane 0 of warp 9 feeds half 1
@@ -509,6 +510,7 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
         PAIR_STAGE_END()
       }
       barh(h);
+      if (ht == 0) STAMP(P.stats, 9);
       // bucket sums: warp w of the half owns buckets 8w .. 8w+7 (fixed order: deterministic)
 #pragma unroll
       for (int q = 0; q < kHB / kHW; ++q) {
@@ -617,6 +619,7 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
       }
 #endif
       if (lane == 0) ps->wcnt[h][hw] = wcnt;
+      if (ht == 0) STAMP(P.stats, 10);
       state = slow ? 3 : (bstar > 0 ? 2 : 4);
 #if defined(ABL_NOPASS2) || defined(ABL_NOSELECT) || defined(ABL_NOPICK)
       state = 4;
@@ -657,6 +660,7 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
         store_record(&P.records[2 * pr + h], rec);
       }
     }
+    if (ht == 0) STAMP(P.stats, 11);
     bar3();  // ---- the halves join: rows that need the whole block (rare) are finished one after the other
 
     const int st[2] = {ps->half[0].state, ps->half[1].state};

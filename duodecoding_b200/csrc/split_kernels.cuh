@@ -43,6 +43,21 @@ struct RowPartial {
 __device__ __forceinline__ void grid_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void grid_dep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
+#ifdef DUODEC_TIMELINE
+// tuning build: global-timer stamps (ns, low 31 bits) into the stats buffer; slot k keeps the maximum,
+// "first" slots keep 0x7fffffff - t so that the maximum is the earliest
+__device__ __forceinline__ void stamp(int* stats, int k, bool first = false) {
+  if (!stats) return;
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  const int v = int(t & 0x7fffffffull);
+  atomicMax(&stats[k], first ? 0x7fffffff - v : v);
+}
+#define STAMP(stats, k, ...) stamp(stats, k, ##__VA_ARGS__)
+#else
+#define STAMP(stats, k, ...)
+#endif
+
 struct ListEntry {
   float x;
   int idx;
@@ -721,10 +736,12 @@ __global__ void __launch_bounds__(kT3, 4) seq_sample_kernel(const __grid_constan
     const int i0 = s0 + u * 4 * kT3 + 4 * tid;
     if (i0 < V && b < P.B) nv4[u] = __ldg(reinterpret_cast<const float4*>(nz + i0));
   }
+  if (tid == 0) STAMP(P.stats, 12, true);
   float rj = 0.0f;  // the acceptance draw of position tid: an input as well
   if (b < P.B && tid < gamma) rj = __ldg(&P.r[(long long)b * P.r_sb + tid]);
   grid_dep_wait();
   grid_dep_launch();
+  if (tid == 0) STAMP(P.stats, 13);
 
   if (b == P.B) {  // the extra block row: block 0 of it aggregates the next launch's prediction, off the critical path
     if (slice != 0) return;
@@ -787,6 +804,7 @@ __global__ void __launch_bounds__(kT3, 4) seq_sample_kernel(const __grid_constan
   int n = 0;
   while (n < gamma && sc.seq_acc[n] != 0) ++n;
   const bool bonus = (n == gamma);
+  if (tid == 0) STAMP(P.stats, 14);
   const RowRecord rp = srec[bonus ? 2 * gamma : 2 * n + 1];
   const RowRecord rq = bonus ? rp : srec[2 * n];
   const TIn* prow = split_row<TIn>(P, RowJob{b, n, 1});
@@ -837,6 +855,7 @@ __global__ void __launch_bounds__(kT3, 4) seq_sample_kernel(const __grid_constan
   }
   if ((tid & 31) == 0) wmass[tid >> 5] = mass, wkey[tid >> 5] = pk, wbd[tid >> 5] = pb;
   bar3();
+  if (tid == 0) STAMP(P.stats, 15);
   if (tid == 0) {
     for (int w = 1; w < kW3; ++w) {
       mass += wmass[w];
@@ -862,6 +881,7 @@ __global__ void __launch_bounds__(kT3, 4) seq_sample_kernel(const __grid_constan
       P.seq_bd[b] = 0ull;
       P.seq_arrive[b] = 0;
     }
+    STAMP(P.stats, 23);
   }
 }
 

@@ -7,6 +7,7 @@
 #include "ring_kernel.cuh"
 #include "resident_kernel.cuh"
 #include "pair_kernel.cuh"
+#include "sample_kernel.cuh"
 #include "stream_launch.h"
 
 namespace duodec {
@@ -146,17 +147,22 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
       const int npairs = int((rows + 1) / 2);
       const int grid = npairs < 2 * sms ? npairs : 2 * sms;  // two blocks per SM, two rows per block
       cudaError_t e;
+      const size_t smem2 = sample_smem_bytes();
       if (c.dtype == DUODEC_F32) {
         e = ensure_stream_smem(reinterpret_cast<const void*>(pair::row_pair_kernel<float>), smem);
+        if (e == cudaSuccess) e = ensure_stream_smem(reinterpret_cast<const void*>(seq_sample_tma_kernel<float>), smem2);
         if (e == cudaSuccess) {
           if (c.phases & 1) launch_pdl(pair::row_pair_kernel<float>, dim3(grid), dim3(pair::kPT), smem, c.stream, Q);
-          if (c.phases & 2) launch_pdl(seq_sample_kernel<float>, g2, dim3(kT3), 0, c.stream, Q);
+          if (c.phases & 2) launch_pdl(seq_sample_tma_kernel<float>, g2, dim3(kT3), smem2, c.stream, Q);
         }
       } else {
         e = ensure_stream_smem(reinterpret_cast<const void*>(pair::row_pair_kernel<__nv_bfloat16>), smem);
+        if (e == cudaSuccess)
+          e = ensure_stream_smem(reinterpret_cast<const void*>(seq_sample_tma_kernel<__nv_bfloat16>), smem2);
         if (e == cudaSuccess) {
-          if (c.phases & 1) launch_pdl(pair::row_pair_kernel<__nv_bfloat16>, dim3(grid), dim3(pair::kPT), smem, c.stream, Q);
-          if (c.phases & 2) launch_pdl(seq_sample_kernel<__nv_bfloat16>, g2, dim3(kT3), 0, c.stream, Q);
+          if (c.phases & 1)
+            launch_pdl(pair::row_pair_kernel<__nv_bfloat16>, dim3(grid), dim3(pair::kPT), smem, c.stream, Q);
+          if (c.phases & 2) launch_pdl(seq_sample_tma_kernel<__nv_bfloat16>, g2, dim3(kT3), smem2, c.stream, Q);
         }
       }
       *rc = int(e != cudaSuccess ? e : cudaGetLastError());
