@@ -2,6 +2,7 @@
 // validates arguments, picks the team size and launches; no allocation, no
 // synchronisation.
 #include <atomic>
+#include <cstdint>
 #include <mutex>
 #include <utility>
 #include <vector>
@@ -161,7 +162,7 @@ size_t duodec_verify_workspace_bytes(int B, int gamma) {
   if (B <= 0 || gamma < 0) return 0;
   // [B] int counters (8 bytes each) + [B, gamma+1] int64 position tokens + 2 row-kind hints
   // + [B, 2*gamma+1] row records
-  return size_t(B) * 8 + size_t(B) * size_t(gamma + 1) * 8 + stream_workspace_bytes(B, gamma);
+  return ((size_t(B) * 8 + size_t(B) * size_t(gamma + 1) * 8 + 15) & ~size_t(15)) + stream_workspace_bytes(B, gamma);
 }
 
 int duodec_verify_fused(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss, int64_t t_sb,
@@ -179,6 +180,7 @@ int duodec_verify_fused(const void* draft, const void* target, int dtype, int64_
   if (!(temperature >= 0.0f) || !(draft_temperature >= 0.0f)) return DUODEC_EINVAL;
   if ((temperature == 0.0f) != (draft_temperature == 0.0f)) return DUODEC_EINVAL;  // greedy on both or neither
   if (workspace_bytes < duodec_verify_workspace_bytes(B, gamma)) return DUODEC_EWORKSPACE;
+  if (reinterpret_cast<uintptr_t>(workspace) & 15u) return DUODEC_EINVAL;  // records are read with 128-bit loads
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (g_stream_path.load() != 0) {
     // fast path: persistent row-stream kernel (stream_launch.cu); falls through when the call does not qualify

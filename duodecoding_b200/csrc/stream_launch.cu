@@ -118,7 +118,10 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
     Q.accepted_len = reinterpret_cast<long long*>(c.accepted_len);
     Q.token = reinterpret_cast<long long*>(c.token);
     Q.all_accepted = c.all_accepted;
-    char* w = reinterpret_cast<char*>(c.workspace) + size_t(c.B) * 8 + size_t(c.B) * size_t(c.gamma + 1) * 8;
+    // behind the general kernel's [B] counters and [B, gamma+1] tokens, rounded up: hints and records
+    // are read with 128-bit loads (B * (gamma + 2) odd would leave them 8-byte aligned)
+    const size_t head = (size_t(c.B) * 8 + size_t(c.B) * size_t(c.gamma + 1) * 8 + 15) & ~size_t(15);
+    char* w = reinterpret_cast<char*>(c.workspace) + head;
     Q.hints = reinterpret_cast<StreamHint*>(w);
     Q.hints_new = Q.hints + 2;
     w += 4 * sizeof(StreamHint);

@@ -89,7 +89,7 @@ int duodec_norm_logits(const void* logits, int in_dtype, int64_t in_row_stride, 
  * outputs
  *   accept_mask [B,gamma] uint8, sel_target_p / sel_draft_p [B,gamma] float32,
  *   accepted_len [B] int64, token [B] int64, all_accepted [B] uint8.
- * workspace: duodec_verify_workspace_bytes(B,gamma) bytes, zero-filled ONCE by
+ * workspace: duodec_verify_workspace_bytes(B,gamma) bytes, 16-byte aligned, zero-filled ONCE by
  *   the caller before first use (the kernel restores it to zero). */
 size_t duodec_verify_workspace_bytes(int B, int gamma);
 

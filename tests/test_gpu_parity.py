@@ -280,6 +280,57 @@ def test_verify_fused_qwen_vocab_bf16(ops, dev):
     _check_verify(got, want)
 
 
+@pytest.mark.parametrize("stream", [5, 4, 3, 1, 0])
+def test_verify_fused_odd_batch_odd_gamma(ops, dev, stream):
+    # B * (gamma + 2) odd: the workspace sections behind the token block start 8 bytes off a
+    # 16-byte boundary unless the launcher rounds up; also an odd row count (one half of the last
+    # row pair has no row)
+    dl, tl, toks, r, noise = _make_case(35, 3, 3, 6000, 0.7, 1.0, 0, 0.9)
+    want = oracle.fused_verify(dl, tl, toks, r, noise, 1.0, 0, 0.9)
+    ops.set_stream_path(stream)
+    try:
+        got = ops.verify_fused(dl.to(dev), tl.to(dev), toks.to(dev), r.to(dev), noise.to(dev), 1.0, 0, 0.9)
+    finally:
+        ops.set_stream_path(True)
+    _check_verify(got, want, NUCLEUS_RTOL)
+
+
+@pytest.mark.parametrize("stream", [5, 3])
+@pytest.mark.parametrize("dtype,V,T,p", [(torch.bfloat16, 151936, 1.0, 0.9), (torch.float32, 128256, 0.7, 0.95)])
+def test_verify_fused_large_vocab_top_p(ops, dev, stream, dtype, V, T, p):
+    # 75 / 63 ring stages per row, a ragged last stage and (T != 1) the IEEE division on the fast paths
+    dl, tl, toks, r, noise = _make_case(31, 3, 3, V, 0.5, T, 0, p, dtype=dtype)
+    want = oracle.fused_verify(dl.float(), tl.float(), toks, r, noise, T, 0, p)
+    ops.set_stream_path(stream)
+    try:
+        got = ops.verify_fused(dl.to(dev), tl.to(dev), toks.to(dev), r.to(dev), noise.to(dev), T, 0, p)
+    finally:
+        ops.set_stream_path(True)
+    _check_verify(got, want, NUCLEUS_RTOL if dtype == torch.float32 else 1e-2)
+
+
+@pytest.mark.parametrize("stream", [5, 3, 0])
+def test_verify_fused_flat_rows_overflow_the_lists(ops, dev, stream):
+    # nearly flat rows: the boundary bucket holds most of the vocabulary, far more than the
+    # shared-memory lists take, so every row goes through the general search
+    g = torch.Generator().manual_seed(33)
+    B, gamma, V = 4, 3, 32000
+    tl = torch.randn(B, gamma + 1, V, generator=g) * 0.05
+    dl = tl[:, :gamma] + 0.02 * torch.randn(B, gamma, V, generator=g)
+    q = oracle.norm_logits(dl, 1.0, 0, 0.9)
+    toks = torch.stack(
+        [oracle.sample(q[:, j], torch.empty(B, V).exponential_(1, generator=g))[:, 0] for j in range(gamma)], 1
+    )
+    r, noise = torch.rand(B, gamma, generator=g), torch.empty(B, V).exponential_(1, generator=g)
+    want = oracle.fused_verify(dl, tl, toks, r, noise, 1.0, 0, 0.9)
+    ops.set_stream_path(stream)
+    try:
+        got = ops.verify_fused(dl.to(dev), tl.to(dev), toks.to(dev), r.to(dev), noise.to(dev), 1.0, 0, 0.9)
+    finally:
+        ops.set_stream_path(True)
+    _check_verify(got, want, NUCLEUS_RTOL)
+
+
 def test_verify_fused_unequal_vocab(ops, dev):
     # draft vocabulary smaller than the target's: gathers and the residual use the common prefix
     dl, tl, toks, r, noise = _make_case(24, 4, 3, 1200, 0.8, 1.0, 0, 0.0, Vd=1000)
