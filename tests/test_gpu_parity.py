@@ -280,6 +280,34 @@ def test_verify_fused_qwen_vocab_bf16(ops, dev):
     _check_verify(got, want)
 
 
+@pytest.mark.parametrize("stream", [5, 0])
+@pytest.mark.parametrize(
+    "B,gamma,V,T,p,dtype",
+    [
+        (1, 1, 1000, 1.0, 0.9, torch.float32),
+        (1, 5, 4096, 0.5, 0.8, torch.float32),
+        (2, 7, 8200, 1.0, 0.95, torch.float32),
+        (5, 1, 32000, 2.0, 0.9, torch.float32),
+        (7, 2, 1504, 1.3, 0.99, torch.float32),
+        (9, 5, 1000, 1.0, 1.0, torch.float32),
+        (2, 3, 1008, 1.0, 0.5, torch.bfloat16),
+        (3, 2, 2056, 0.8, 0.3, torch.bfloat16),
+        (4, 8, 520, 1.0, 0.05, torch.float32),
+    ],
+)
+def test_verify_fused_shape_sweep(ops, dev, stream, B, gamma, V, T, p, dtype):
+    # small and ragged shapes: one-row batches, long and short drafts, a last ring stage of a few
+    # entries, top_p from "almost nothing" to 1.0, temperatures on both sides of 1
+    dl, tl, toks, r, noise = _make_case(100 + B * 17 + gamma, B, gamma, V, 0.6, T, 0, p, dtype=dtype)
+    want = oracle.fused_verify(dl.float(), tl.float(), toks, r, noise, T, 0, p)
+    ops.set_stream_path(stream)
+    try:
+        got = ops.verify_fused(dl.to(dev), tl.to(dev), toks.to(dev), r.to(dev), noise.to(dev), T, 0, p)
+    finally:
+        ops.set_stream_path(True)
+    _check_verify(got, want, NUCLEUS_RTOL if dtype == torch.float32 else 1e-2)
+
+
 @pytest.mark.parametrize("stream", [5, 4, 3, 1, 0])
 def test_verify_fused_odd_batch_odd_gamma(ops, dev, stream):
     # B * (gamma + 2) odd: the workspace sections behind the token block start 8 bytes off a
