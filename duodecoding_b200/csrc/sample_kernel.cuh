@@ -44,10 +44,12 @@ __global__ void __launch_bounds__(kT3, 4) seq_sample_tma_kernel(const __grid_con
       bulk_g2s(s_noise, P.noise + (long long)b * P.noise_sb + s0, unsigned(ne) * 4u, &mb[0]);
     }
   }
+  if (tid == 0) STAMP(P.stats, 12, true);
   float rj = 0.0f;  // the acceptance draw of position tid: an input as well
   if (b < P.B && tid < gamma) rj = __ldg(&P.r[(long long)b * P.r_sb + tid]);
   grid_dep_wait();
   grid_dep_launch();
+  if (tid == 0) STAMP(P.stats, 13);
 
   if (b == P.B) {  // the extra block row: block 0 of it aggregates the next launch's prediction, off the critical path
     if (slice != 0) return;
@@ -121,8 +123,10 @@ __global__ void __launch_bounds__(kT3, 4) seq_sample_tma_kernel(const __grid_con
     bulk_g2s(s_p, prow + s0, unsigned(ne) * unsigned(kElt), &mb[1]);
     if (!bonus) bulk_g2s(s_q, split_row<TIn>(P, RowJob{b, n, 0}) + s0, unsigned(ne) * unsigned(kElt), &mb[1]);
   }
+  if (tid == 0) STAMP(P.stats, 14);
   mbar_wait(&mb[0], 0u);
   mbar_wait(&mb[1], 0u);
+  if (tid == 0) STAMP(P.stats, 24);
 
   float mass = 0.0f, bkey = -1.0f, bdv = -INFINITY;
   int bidx = 0x7fffffff, bdi = 0x7fffffff;
@@ -142,21 +146,29 @@ __global__ void __launch_bounds__(kT3, 4) seq_sample_tma_kernel(const __grid_con
         xq.z = __fdiv_rn(xq.z, P.d_temp), xq.w = __fdiv_rn(xq.w, P.d_temp);
       }
       float4 nv = *reinterpret_cast<const float4*>(s_noise + size_t(l0) * 4);
+      // branch-free per entry: both exponentials are always taken, the keep rules are predicates.
+      // A thread meets its indices in increasing order, so strict ">" keeps the lowest index of a tie.
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         const float x = f4c(xp, k);
-        float d = kept(rp, x, i0 + k) ? row_exp(x, rp.m0) * invZp : 0.0f;
+        const int i = i0 + k;
+        const bool kp = (x > rp.xstar) | ((x == rp.xstar) & (i <= rp.istar));
+        const float pe = row_exp(x, rp.m0) * invZp;
+        float d = kp ? pe : 0.0f;
         if (!bonus) {
           const float y = f4c(xq, k);
-          d -= kept(rq, y, i0 + k) ? row_exp(y, rq.m0) * invZq : 0.0f;
+          const bool kq = (y > rq.xstar) | ((y == rq.xstar) & (i <= rq.istar));
+          const float qe = row_exp(y, rq.m0) * invZq;
+          d -= kq ? qe : 0.0f;
         }
-        if (d > 0.0f) {
-          mass += d;
-          const float key = __fdividef(d, f4c(nv, k));
-          if (key > bkey || (key == bkey && i0 + k < bidx)) bkey = key, bidx = i0 + k;
-        }
-        const float dz = (d == d && fabsf(d) != INFINITY) ? d : 0.0f;
-        if (dz > bdv || (dz == bdv && i0 + k < bdi)) bdv = dz, bdi = i0 + k;
+        const bool pos = d > 0.0f;
+        mass += pos ? d : 0.0f;
+        const float key = pos ? __fdividef(d, f4c(nv, k)) : -1.0f;
+        const bool bk = key > bkey;
+        bkey = bk ? key : bkey, bidx = bk ? i : bidx;
+        const float dz = (fabsf(d) < INFINITY) ? d : 0.0f;  // NaN and +-inf count as 0
+        const bool bd = dz > bdv;
+        bdv = bd ? dz : bdv, bdi = bd ? i : bdi;
       }
     }
   }

@@ -16,12 +16,11 @@ ops.set_stats_buffer(stats)
 for it in range(4):
     stats.zero_()
     out = ops.verify_fused(*sets[it % 4], bench.TEMP, bench.TOP_K, bench.TOP_P, out=out)
-    out = ops.verify_fused(*sets[(it + 1) % 4], bench.TEMP, bench.TOP_K, bench.TOP_P, out=out)
     torch.cuda.synchronize()
     s = stats.tolist()
     t0 = 0x7fffffff - s[8]
     names = {9: "last pass-1 end", 10: "last pass-2 end", 11: "last row closed", 13: "last sample block past the wait",
-             14: "last n known", 15: "last slice reduced", 23: "last sample block end"}
+             14: "last n known (row copies issued)", 24: "last row slices landed", 15: "last slice reduced", 23: "last sample block end"}
     print("launch pair", it, "| first sample block resident at %.1f us" % ((0x7fffffff - s[12] - t0) / 1e3))
     for k, nm in names.items():
         print("   %-34s %.1f us" % (nm, (s[k] - t0) / 1e3))
