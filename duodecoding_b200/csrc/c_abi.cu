@@ -20,7 +20,7 @@ namespace {
 
 constexpr size_t kMaxDynSmem = 232448;  // 227 KB opt-in limit per block on sm_100
 std::atomic<int> g_team_override{0};
-std::atomic<int> g_stream_path{5};
+std::atomic<int> g_stream_path{6};
 std::atomic<int> g_phase_mask{3};
 std::atomic<int*> g_stats{nullptr};
 

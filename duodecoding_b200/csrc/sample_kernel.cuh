@@ -15,6 +15,87 @@ constexpr size_t sample_smem_bytes() { return size_t(3) * kSlice3 * 4; }
 static_assert(sizeof(Scratch3) + (2 * 64 + 1) * sizeof(RowRecord) <= size_t(2) * kSlice3 * 2,
               "scratch + records must fit under the row slices (bf16 rows)");
 
+// Token of one sequence from the kept-entry list of its target row p_n (compact mode of the sample
+// kernel; whole block, 256 threads).  Same per-entry arithmetic as the sliced loop below, so the winner
+// is the same entry: d = p_i - q_i (or p_i for the bonus draw), key = d / noise_i over d > 0, lowest
+// index on ties.  Entries outside the list have p_i = 0, hence d <= 0: they matter only when the
+// residual has no mass at all, and then the first arg-max of p - q over the WHOLE row is taken with
+// plain loads (src/utils.py:787-810 zero-mass fallback; essentially never with a rejected draft).
+template <class TIn>
+__device__ __noinline__ long long compact_token(const SplitParams& P, int b, int n, bool bonus, const RowRecord& rp,
+                                                const RowRecord& rq, float invZp, float invZq,
+                                                unsigned long long* wkey, float* wmass) {
+  const int tid = threadIdx.x, gamma = P.gamma, V = P.V;
+  const int ncomp = rp.pad - 1;
+  const ListEntry* L = P.lists + (long long)(b * (gamma + 1) + n) * kListCap;
+  const TIn* qrow = split_row<TIn>(P, RowJob{b, bonus ? 0 : n, 0});
+  const float* nz = P.noise + (long long)b * P.noise_sb;
+  float mass = 0.0f;
+  unsigned long long pk = 0ull;
+  for (int e = tid; e < ncomp; e += kT3) {
+    const int2 raw = __ldcg(reinterpret_cast<const int2*>(L + e));
+    const float x = __int_as_float(raw.x);
+    const int i = raw.y;
+    float d = row_exp(x, rp.m0) * invZp;
+    if (!bonus) {
+      const float y = scale_logit(to_f32(__ldcg(qrow + i)), P.d_temp);
+      const bool kq = (y > rq.xstar) | ((y == rq.xstar) & (i <= rq.istar));
+      const float qe = row_exp(y, rq.m0) * invZq;
+      d -= kq ? qe : 0.0f;
+    }
+    if (d > 0.0f) {
+      mass += d;
+      const float key = __fdividef(d, __ldg(nz + i));
+      const unsigned long long k2 =
+          ((unsigned long long)__float_as_uint(key) << 32) | (unsigned long long)(0xffffffffu - unsigned(i));
+      if (key >= 0.0f && k2 > pk) pk = k2;  // (a NaN key never wins, as in the sliced loop)
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    mass += __shfl_xor_sync(0xffffffffu, mass, o);
+    const unsigned long long ok = __shfl_xor_sync(0xffffffffu, pk, o);
+    pk = ok > pk ? ok : pk;
+  }
+  if ((tid & 31) == 0) wmass[tid >> 5] = mass, wkey[tid >> 5] = pk;
+  bar3();
+  mass = 0.0f, pk = 0ull;
+#pragma unroll
+  for (int w = 0; w < kW3; ++w) {
+    mass += wmass[w];
+    pk = wkey[w] > pk ? wkey[w] : pk;
+  }
+  if (mass > 0.0f && pk != 0ull) return (long long)(0xffffffffu - unsigned(pk & 0xffffffffull));
+  // ---- zero-mass fallback: first arg-max of p - q over the whole row (NaN and +-inf count as 0)
+  bar3();
+  const TIn* prow = split_row<TIn>(P, RowJob{b, n, 1});
+  unsigned long long pb = 0ull;
+  for (int i = tid; i < V; i += kT3) {
+    const float x = scale_logit(to_f32(__ldcg(prow + i)), P.t_temp);
+    const bool kp = (x > rp.xstar) | ((x == rp.xstar) & (i <= rp.istar));
+    float d = kp ? row_exp(x, rp.m0) * invZp : 0.0f;
+    if (!bonus) {
+      const float y = scale_logit(to_f32(__ldcg(qrow + i)), P.d_temp);
+      const bool kq = (y > rq.xstar) | ((y == rq.xstar) & (i <= rq.istar));
+      d -= kq ? row_exp(y, rq.m0) * invZq : 0.0f;
+    }
+    const float dz = (fabsf(d) < INFINITY) ? d : 0.0f;
+    const unsigned long long k2 = ((unsigned long long)okey(dz) << 32) | (unsigned long long)(0xffffffffu - unsigned(i));
+    pb = k2 > pb ? k2 : pb;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const unsigned long long ob = __shfl_xor_sync(0xffffffffu, pb, o);
+    pb = ob > pb ? ob : pb;
+  }
+  if ((tid & 31) == 0) wkey[tid >> 5] = pb;
+  bar3();
+  pb = 0ull;
+#pragma unroll
+  for (int w = 0; w < kW3; ++w) pb = wkey[w] > pb ? wkey[w] : pb;
+  return pb == 0ull ? 0 : (long long)(0xffffffffu - unsigned(pb & 0xffffffffull));
+}
+
 template <class TIn>
 __global__ void __launch_bounds__(kT3, 4) seq_sample_tma_kernel(const __grid_constant__ SplitParams P) {
   extern __shared__ __align__(128) unsigned char sm3[];
@@ -38,7 +119,7 @@ __global__ void __launch_bounds__(kT3, 4) seq_sample_tma_kernel(const __grid_con
     mbar_init(&mb[0], 1);
     mbar_init(&mb[1], 1);
     mbar_fence_init();
-    if (b < P.B) {
+    if (b < P.B && !P.compact_hint) {
       // the noise does not depend on the scan kernel (the caller wrote it before the scan kernel was launched)
       mbar_expect_tx(&mb[0], unsigned(ne) * 4u);
       bulk_g2s(s_noise, P.noise + (long long)b * P.noise_sb + s0, unsigned(ne) * 4u, &mb[0]);
@@ -114,6 +195,19 @@ __global__ void __launch_bounds__(kT3, 4) seq_sample_tma_kernel(const __grid_con
   const RowRecord rp = srec[bonus ? 2 * gamma : 2 * n + 1];
   const RowRecord rq = bonus ? rp : srec[2 * n];
   const float invZp = __frcp_rn(rp.Z), invZq = __frcp_rn(rq.Z);
+  if (P.compact_hint && rp.pad > 0) {
+    // ---- compact mode: the scan kernel listed the kept entries of p_n (the only entries where
+    // max(0, p - q), or p itself for the bonus draw, is not zero); one block draws the token from them
+    if (slice != 0) return;  // (no copy of this block is in flight: the noise prefetch is off under compact_hint)
+    const long long tok = compact_token<TIn>(P, b, n, bonus, rp, rq, invZp, invZq, wkey, wmass);
+    if (tid == 0) {
+      P.accepted_len[b] = n;
+      P.token[b] = tok;
+      P.all_accepted[b] = (unsigned char)(n == gamma);
+      STAMP(P.stats, 23);
+    }
+    return;
+  }
   // scratch and records are in registers everywhere: their shared memory becomes the row slices
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic accesses above, async writes below
   bar3();
@@ -122,6 +216,10 @@ __global__ void __launch_bounds__(kT3, 4) seq_sample_tma_kernel(const __grid_con
     mbar_expect_tx(&mb[1], unsigned(ne) * unsigned(kElt) * (bonus ? 1u : 2u));
     bulk_g2s(s_p, prow + s0, unsigned(ne) * unsigned(kElt), &mb[1]);
     if (!bonus) bulk_g2s(s_q, split_row<TIn>(P, RowJob{b, n, 0}) + s0, unsigned(ne) * unsigned(kElt), &mb[1]);
+    if (P.compact_hint) {  // a sequence without list under the hint (rare): the noise slice is fetched only now
+      mbar_expect_tx(&mb[0], unsigned(ne) * 4u);
+      bulk_g2s(s_noise, P.noise + (long long)b * P.noise_sb + s0, unsigned(ne) * 4u, &mb[0]);
+    }
   }
   if (tid == 0) STAMP(P.stats, 14);
   mbar_wait(&mb[0], 0u);

@@ -97,6 +97,8 @@ struct SplitParams {
   float* seq_mass;              // [B]
   int* seq_arrive;              // [B]
   int* stats;
+  int cap_rank;      // row-capture kernel: rank (0..31) of the sorted group maxima that gives the capture cut
+  int compact_hint;  // sample kernel: target rows are expected to come with a kept-entry list (no noise prefetch)
 };
 
 struct __align__(16) Scratch3 {

@@ -48,7 +48,7 @@ struct RowRecord {  // 32 bytes per row job, written once, read by the block tha
   float sel;    // probability of the drafted token of this position
   float mxl;    // row maximum * log2(e)            } statistics the next launch's
   float dens;   // list entries per unit of logit    } prediction is built from
-  int pad;
+  int pad = 0;  // row-capture kernel: 1 + number of kept entries in the row's workspace list (0: no list)
 };
 
 struct StreamHint {  // per row kind, lives in the workspace, survives across launches
@@ -128,12 +128,13 @@ __device__ __forceinline__ RowRecord load_record(const RowRecord* p) {
   r.sel = __uint_as_float(b4.x);
   r.mxl = __uint_as_float(b4.y);
   r.dens = __uint_as_float(b4.z);
+  r.pad = int(b4.w);
   return r;
 }
 __device__ __forceinline__ void store_record(RowRecord* p, const RowRecord& r) {
   uint4* dst = reinterpret_cast<uint4*>(p);
   dst[0] = make_uint4(__float_as_uint(r.m0), __float_as_uint(r.Z), __float_as_uint(r.xstar), unsigned(r.istar));
-  dst[1] = make_uint4(__float_as_uint(r.sel), __float_as_uint(r.mxl), __float_as_uint(r.dens), 0u);
+  dst[1] = make_uint4(__float_as_uint(r.sel), __float_as_uint(r.mxl), __float_as_uint(r.dens), unsigned(r.pad));
 }
 
 struct MassBest {

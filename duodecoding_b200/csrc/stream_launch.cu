@@ -7,6 +7,7 @@
 #include "ring_kernel.cuh"
 #include "resident_kernel.cuh"
 #include "pair_kernel.cuh"
+#include "capture_kernel.cuh"
 #include "sample_kernel.cuh"
 #include "stream_launch.h"
 
@@ -68,12 +69,13 @@ cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t s
 
 }  // namespace
 
+constexpr int kMaxGrid = 320;   // blocks of a persistent scan kernel (two per SM): one scratch list each
 constexpr int kMaxSlices = 32;  // row_scan slices the workspace is sized for (V <= 262144)
 
 size_t stream_workspace_bytes(int B, int gamma) {
   const size_t rows = size_t(B) * size_t(2 * gamma + 1);
   return 4 * sizeof(StreamHint) + rows * sizeof(RowRecord) + rows * kMaxSlices * sizeof(RowPartial) + rows * 8 +
-         size_t(B) * 24 + (rows + 2) * size_t(kListCap) * sizeof(ListEntry);
+         size_t(B) * 24 + (rows + 2 + kMaxGrid) * size_t(kListCap) * sizeof(ListEntry);
 }
 
 bool stream_try_launch(const StreamCall& c, int* rc) {
@@ -87,10 +89,12 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
   if (!ok) return false;
   const size_t rows = size_t(c.B) * size_t(2 * c.gamma + 1);
   const bool resident = c.path == 4 && c.B <= 65535;
-  const bool pairp = c.path == 5 && c.B <= 65535;
+  const bool capture = c.path == 6 && c.B <= 65535 && c.Vt >= cap::kMinV &&
+                       cap::cap_smem_bytes((c.Vt + kStageElems - 1) / kStageElems) <= 232448;
+  const bool pairp = (c.path == 5 || (c.path == 6 && !capture)) && c.B <= 65535;
   const bool ring = (c.path == 3 || (c.path == 1 && c.Vt > kMaxSlices * kSlice)) && c.B <= 65535;
   const bool split = c.path == 1 && c.Vt <= kMaxSlices * kSlice && rows <= 65535 && c.B <= 65535;
-  if (ring || split || resident || pairp) {
+  if (ring || split || resident || pairp || capture) {
     SplitParams Q;
     Q.draft = c.draft;
     Q.target = c.target;
@@ -143,7 +147,47 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
     w += size_t(c.B) * 4;
     Q.lists = reinterpret_cast<ListEntry*>(w);
     Q.stats = c.stats;
+    Q.cap_rank = 0;
+    Q.compact_hint = 0;
     const dim3 g1(unsigned(Q.S), unsigned(rows)), g2(unsigned((c.Vt + kSlice3 - 1) / kSlice3), unsigned(c.B) + 1u);  // + the block row that aggregates the hints
+    if (capture) {
+      const size_t smem = cap::cap_smem_bytes((c.Vt + kStageElems - 1) / kStageElems);
+      const int sms = stream_sm_count();
+      const int per_sm = smem <= 115712 ? 2 : 1;  // two blocks per SM while the bit maps leave room
+      const int npairs = int((rows + 1) / 2);
+      int grid = npairs < per_sm * sms ? npairs : per_sm * sms;
+      if (grid > kMaxGrid) grid = kMaxGrid;
+      // capture cut: the top f of a row by count, f = min(1/12, 2667 / V); a thread's 16 sample entries
+      // all lie below the cut with probability (1 - f)^16, which is the rank among the 32 sorted maxima
+      double f = 2667.0 / double(c.Vt);
+      if (f > 1.0 / 12.0) f = 1.0 / 12.0;
+      double pbelow = 1.0;
+      for (int i = 0; i < 16; ++i) pbelow *= 1.0 - f;
+      int rank = int(32.0 * pbelow);
+      Q.cap_rank = rank < 0 ? 0 : (rank > 31 ? 31 : rank);
+      Q.compact_hint = (c.top_p > 0.0f && c.top_p < 1.0f) ? 1 : 0;
+      const dim3 g2c(unsigned((c.Vt + kSlice3 - 1) / kSlice3), unsigned(c.B));  // no hint row: nothing is predicted
+      cudaError_t e;
+      const size_t smem2 = sample_smem_bytes();
+      if (c.dtype == DUODEC_F32) {
+        e = ensure_stream_smem(reinterpret_cast<const void*>(cap::row_capture_kernel<float>), smem);
+        if (e == cudaSuccess) e = ensure_stream_smem(reinterpret_cast<const void*>(seq_sample_tma_kernel<float>), smem2);
+        if (e == cudaSuccess && (c.phases & 1))
+          e = launch_pdl(cap::row_capture_kernel<float>, dim3(grid), dim3(cap::kPT), smem, c.stream, Q);
+        if (e == cudaSuccess && (c.phases & 2))
+          e = launch_pdl(seq_sample_tma_kernel<float>, g2c, dim3(kT3), smem2, c.stream, Q);
+      } else {
+        e = ensure_stream_smem(reinterpret_cast<const void*>(cap::row_capture_kernel<__nv_bfloat16>), smem);
+        if (e == cudaSuccess)
+          e = ensure_stream_smem(reinterpret_cast<const void*>(seq_sample_tma_kernel<__nv_bfloat16>), smem2);
+        if (e == cudaSuccess && (c.phases & 1))
+          e = launch_pdl(cap::row_capture_kernel<__nv_bfloat16>, dim3(grid), dim3(cap::kPT), smem, c.stream, Q);
+        if (e == cudaSuccess && (c.phases & 2))
+          e = launch_pdl(seq_sample_tma_kernel<__nv_bfloat16>, g2c, dim3(kT3), smem2, c.stream, Q);
+      }
+      *rc = int(e != cudaSuccess ? e : cudaGetLastError());
+      return true;
+    }
     if (pairp) {
       const size_t smem = pair::pair_smem_bytes();
       const int sms = stream_sm_count();
@@ -154,19 +198,17 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
       if (c.dtype == DUODEC_F32) {
         e = ensure_stream_smem(reinterpret_cast<const void*>(pair::row_pair_kernel<float>), smem);
         if (e == cudaSuccess) e = ensure_stream_smem(reinterpret_cast<const void*>(seq_sample_tma_kernel<float>), smem2);
-        if (e == cudaSuccess) {
-          if (c.phases & 1) launch_pdl(pair::row_pair_kernel<float>, dim3(grid), dim3(pair::kPT), smem, c.stream, Q);
-          if (c.phases & 2) launch_pdl(seq_sample_tma_kernel<float>, g2, dim3(kT3), smem2, c.stream, Q);
-        }
+        if (e == cudaSuccess && (c.phases & 1))
+          e = launch_pdl(pair::row_pair_kernel<float>, dim3(grid), dim3(pair::kPT), smem, c.stream, Q);
+        if (e == cudaSuccess && (c.phases & 2)) e = launch_pdl(seq_sample_tma_kernel<float>, g2, dim3(kT3), smem2, c.stream, Q);
       } else {
         e = ensure_stream_smem(reinterpret_cast<const void*>(pair::row_pair_kernel<__nv_bfloat16>), smem);
         if (e == cudaSuccess)
           e = ensure_stream_smem(reinterpret_cast<const void*>(seq_sample_tma_kernel<__nv_bfloat16>), smem2);
-        if (e == cudaSuccess) {
-          if (c.phases & 1)
-            launch_pdl(pair::row_pair_kernel<__nv_bfloat16>, dim3(grid), dim3(pair::kPT), smem, c.stream, Q);
-          if (c.phases & 2) launch_pdl(seq_sample_tma_kernel<__nv_bfloat16>, g2, dim3(kT3), smem2, c.stream, Q);
-        }
+        if (e == cudaSuccess && (c.phases & 1))
+          e = launch_pdl(pair::row_pair_kernel<__nv_bfloat16>, dim3(grid), dim3(pair::kPT), smem, c.stream, Q);
+        if (e == cudaSuccess && (c.phases & 2))
+          e = launch_pdl(seq_sample_tma_kernel<__nv_bfloat16>, g2, dim3(kT3), smem2, c.stream, Q);
       }
       *rc = int(e != cudaSuccess ? e : cudaGetLastError());
       return true;

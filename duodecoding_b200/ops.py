@@ -55,7 +55,7 @@ def set_team_size(team: int) -> None:
     lib.duodec_set_team_size(int(team))
 
 
-FAST_PATH = 5  # row-pair scan kernel + sliced sample kernel
+FAST_PATH = 6  # row-capture scan kernel + sample kernel (compact lists)
 
 
 def set_stream_path(path) -> None:
