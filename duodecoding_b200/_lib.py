@@ -26,12 +26,15 @@ SIGNATURES = {
     "duodec_version": (ctypes.c_char_p, []),
     "duodec_team_size": (c_int, [c_int, c_int]),
     "duodec_set_team_size": (None, [c_int]),
-    "duodec_set_stream_path": (None, [c_int]),
-    "duodec_set_phase_mask": (None, [c_int]),
     "duodec_set_stats_buffer": (None, [c_void_p]),
     "duodec_norm_logits": (
         c_int,
         [c_void_p, c_int, c_i64, c_void_p, c_int, c_i64, c_int, c_int, c_float, c_int, c_float, c_void_p],
+    ),
+    "duodec_norm_logits_batched": (
+        c_int,
+        [c_void_p, c_int, c_i64, c_i64, c_void_p, c_int, c_i64, c_i64, c_int, c_int, c_int, c_float, c_int, c_float,
+         c_void_p],
     ),
     "duodec_verify_workspace_bytes": (c_size_t, [c_int, c_int]),
     "duodec_verify_fused": (
@@ -39,6 +42,7 @@ SIGNATURES = {
         [c_void_p, c_void_p, c_int, c_i64, c_i64, c_i64, c_i64, c_int, c_int, c_int, c_int]  # rows / shapes
         + [c_void_p, c_i64, c_void_p, c_i64, c_void_p, c_i64]  # tokens, r, noise
         + [c_float, c_int, c_float, c_float, c_int, c_float]  # target warp, draft warp
+        + [c_int]  # flags
         + [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]  # outputs
         + [c_void_p, c_size_t, c_void_p],  # workspace, stream
     ),

@@ -20,8 +20,6 @@ namespace {
 
 constexpr size_t kMaxDynSmem = 232448;  // 227 KB opt-in limit per block on sm_100
 std::atomic<int> g_team_override{0};
-std::atomic<int> g_stream_path{6};
-std::atomic<int> g_phase_mask{3};
 std::atomic<int*> g_stats{nullptr};
 
 size_t team_smem_bytes(int V, int rows_resident, int C) {
@@ -114,28 +112,30 @@ int duodec_team_size(int V, int rows_resident) {
 
 void duodec_set_team_size(int team) { g_team_override.store(team); }
 
-void duodec_set_stream_path(int enabled) { g_stream_path.store(enabled); }
-void duodec_set_phase_mask(int mask) { g_phase_mask.store(mask); }
-
 void duodec_set_stats_buffer(int* device_counters) { g_stats.store(device_counters); }
 
-int duodec_norm_logits(const void* logits, int in_dtype, int64_t in_row_stride, void* out, int out_dtype,
-                       int64_t out_row_stride, int rows, int V, float temperature, int top_k, float top_p,
-                       void* stream) {
-  if (rows < 0 || V <= 0) return DUODEC_EINVAL;
-  if (rows == 0) return 0;
+int duodec_norm_logits_batched(const void* logits, int in_dtype, int64_t in_batch_stride, int64_t in_row_stride,
+                               void* out, int out_dtype, int64_t out_batch_stride, int64_t out_row_stride, int batch,
+                               int inner, int V, float temperature, int top_k, float top_p, void* stream) {
+  if (batch < 0 || inner < 0 || V <= 0) return DUODEC_EINVAL;
+  if (batch == 0 || inner == 0) return 0;
+  if (int64_t(batch) * int64_t(inner) > 0x7fffffff / 8) return DUODEC_EINVAL;
   if (!logits || !out) return DUODEC_EINVAL;
   if ((in_dtype != DUODEC_F32 && in_dtype != DUODEC_BF16) || (out_dtype != DUODEC_F32 && out_dtype != DUODEC_BF16))
     return DUODEC_EINVAL;
   if (!(temperature >= 0.0f)) return DUODEC_EINVAL;
+  const int rows = batch * inner;
   const int C = pick_team(V, 1);
   if (C == 0) return DUODEC_ETOOBIG;
   NormParams P;
   P.logits = logits;
   P.in_stride = in_row_stride;
+  P.in_bstride = in_batch_stride;
   P.out = out;
   P.out_stride = out_row_stride;
+  P.out_bstride = out_batch_stride;
   P.rows = rows;
+  P.inner = inner;
   P.V = V;
   P.temperature = temperature;
   P.top_p = top_p;
@@ -158,6 +158,13 @@ int duodec_norm_logits(const void* logits, int in_dtype, int64_t in_row_stride, 
   return int(e);
 }
 
+int duodec_norm_logits(const void* logits, int in_dtype, int64_t in_row_stride, void* out, int out_dtype,
+                       int64_t out_row_stride, int rows, int V, float temperature, int top_k, float top_p,
+                       void* stream) {
+  return duodec_norm_logits_batched(logits, in_dtype, 0, in_row_stride, out, out_dtype, 0, out_row_stride, 1, rows, V,
+                                    temperature, top_k, top_p, stream);
+}
+
 size_t duodec_verify_workspace_bytes(int B, int gamma) {
   if (B <= 0 || gamma < 0) return 0;
   // [B] int counters (8 bytes each) + [B, gamma+1] int64 position tokens + 2 row-kind hints
@@ -169,9 +176,9 @@ int duodec_verify_fused(const void* draft, const void* target, int dtype, int64_
                         int64_t t_ss, int B, int gamma, int Vd, int Vt, const int64_t* tokens, int64_t tok_sb,
                         const float* r, int64_t r_sb, const float* noise, int64_t noise_sb, float temperature,
                         int top_k, float top_p, float draft_temperature, int draft_top_k, float draft_top_p,
-                        uint8_t* accept_mask, float* sel_target_p, float* sel_draft_p, int64_t* accepted_len,
-                        int64_t* token, uint8_t* all_accepted, void* workspace, size_t workspace_bytes,
-                        void* stream) {
+                        int flags, uint8_t* accept_mask, float* sel_target_p, float* sel_draft_p,
+                        int64_t* accepted_len, int64_t* token, uint8_t* all_accepted, void* workspace,
+                        size_t workspace_bytes, void* stream) {
   if (B < 0 || gamma < 0 || Vd <= 0 || Vt <= 0) return DUODEC_EINVAL;
   if (B == 0) return 0;
   if (!target || !noise || !accepted_len || !token || !all_accepted || !workspace) return DUODEC_EINVAL;
@@ -182,7 +189,10 @@ int duodec_verify_fused(const void* draft, const void* target, int dtype, int64_
   if (workspace_bytes < duodec_verify_workspace_bytes(B, gamma)) return DUODEC_EWORKSPACE;
   if (reinterpret_cast<uintptr_t>(workspace) & 15u) return DUODEC_EINVAL;  // records are read with 128-bit loads
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (g_stream_path.load() != 0) {
+  const int path = (flags >> 4) & 15, phases = (flags >> 8) & 3;
+  const bool row0 = (flags & DUODEC_VERIFY_ROW0_RULE) != 0 && B > 1 && gamma > 0;
+  if (path != 0 && path != 1 && path != 5 && path != 6) return DUODEC_EINVAL;
+  if (path != 1) {
     // fast path: persistent row-stream kernel (stream_launch.cu); falls through when the call does not qualify
     StreamCall c;
     c.draft = draft, c.target = target, c.dtype = dtype;
@@ -193,10 +203,13 @@ int duodec_verify_fused(const void* draft, const void* target, int dtype, int64_
     c.draft_temperature = draft_temperature, c.draft_top_k = draft_top_k, c.draft_top_p = draft_top_p;
     c.accept_mask = accept_mask, c.sel_target_p = sel_target_p, c.sel_draft_p = sel_draft_p;
     c.accepted_len = accepted_len, c.token = token, c.all_accepted = all_accepted;
-    c.workspace = workspace, c.stats = g_stats.load(), c.path = g_stream_path.load(), c.phases = g_phase_mask.load(), c.stream = st;
+    c.workspace = workspace, c.stats = g_stats.load(), c.path = path == 0 ? 6 : path, c.phases = phases == 0 ? 3 : phases;
+    c.row0_rule = row0 ? 1 : 0, c.stream = st;
     int rc = 0;
     if (stream_try_launch(c, &rc)) return rc;
   }
+  // the general kernel closes every sequence on its own count: the batch rule needs the fast path
+  if (row0) return DUODEC_EINVAL;
   const int Vmax = Vd > Vt ? Vd : Vt;
   const int C = pick_team(Vmax, 2);
   if (C == 0) return DUODEC_ETOOBIG;

@@ -23,8 +23,9 @@
 //            the sample kernel draws the sequence's token from that list instead of re-reading
 //            three V-sized rows.
 //
-// A row whose nucleus is not inside the captured set (flat rows, more than 44 captured entries in
-// one thread, overflowing exponentials) is finished by the general windowed search through L2
+// A thread whose column is full appends to a small overflow pool of its half (atomic append, rare).
+// A row whose nucleus is not inside the captured set (flat rows, a full overflow pool, overflowing
+// exponentials) is finished by the general windowed search through L2
 // (general_row, pair_kernel.cuh), exactly as before.
 //
 // Reference semantics restated: src/utils.py:650-709 (logits / T, top-p filter, softmax); the
@@ -40,7 +41,8 @@ constexpr int kHT = 128;            // worker threads per half
 constexpr int kHW = kHT / 32;
 constexpr int kPT = kT3 + 64;       // 256 workers + one producer warp per half
 constexpr int kCStages = 2;         // 8 KB stages per half
-constexpr int kSlots = 48;          // list slots per worker thread (the last 4 are slack: the cut is re-armed per float4)
+constexpr int kSlots = 40;          // list slots per worker thread (the last 4 are slack: the column is re-checked per float4)
+constexpr int kOvf = 512;           // entries of a half's overflow pool: what does not fit a thread's column (x, index)
 constexpr int kLB = 16;             // value buckets per select level
 constexpr int kMaxLevels = 5;
 constexpr int kSamplePieces = 8;    // sample stage: 8 pieces of 256 entries
@@ -65,10 +67,13 @@ struct __align__(16) CapScratch {  // one per half
   int cand_i[kHT];
   unsigned long long wgb[kHW];
   int wcnt[kHW];
+  int wpre[kHW];  // inclusive warp totals of the kept-for-sure counts (emission offsets)
   unsigned long long gb_new;
   int ncand, res_ok, res_i, nemit;
   float res_x;
-  int pad[3];
+  int novf;  // entries appended to the overflow pool (may exceed kOvf: then the row takes the general search)
+  int pad[2];
+  ListEntry ovf[kOvf];
 };
 
 __host__ __device__ constexpr size_t cap_bitmap_bytes(int nchunk) { return (size_t(nchunk) * kHT * 2 + 15) & ~size_t(15); }
@@ -110,22 +115,33 @@ __device__ __forceinline__ void cap_one(unsigned& lp, unsigned& hm, float x, flo
       : "memory");
 }
 
-// walks the set bits of a thread's bit map in capture order and turns them into row indices
-struct BitWalk {
-  const unsigned short* bm;
-  int stage;
-  unsigned hm;
-  __device__ __forceinline__ BitWalk(const unsigned short* bm_thread) : bm(bm_thread), stage(-1), hm(0u) {}
-  __device__ __forceinline__ int next(int ht) {  // the caller guarantees that another set bit exists
-    while (hm == 0u) {
-      ++stage;
-      hm = bm[stage * kHT];
-    }
-    const int k = __ffs(hm) - 1;
-    hm &= hm - 1u;
-    return stage * kStageElems + ((k >> 2) * kHT + ht) * 4 + (k & 3);
+// A thread whose column filled up stopped capturing at a float4-group boundary: every group after the one
+// that holds its last captured entry was skipped.  Cold path, after the stream: those groups are read
+// again (plain loads, L2) and their entries above the cut go to the half's overflow pool with their index.
+template <class TIn>
+__device__ __noinline__ void cap_spill_rest(CapScratch* hs, const unsigned short* bmt, const TIn* row, int V,
+                                            int nchunk, float temp, float cut, int ht) {
+  int c = nchunk - 1;
+  unsigned hm = 0u;
+  for (; c >= 0; --c) {
+    hm = bmt[c * kHT];
+    if (hm != 0u) break;
   }
-};
+  int g = c < 0 ? 0 : c * 4 + ((31 - __clz(hm)) >> 2) + 1;  // first skipped group (stage * 4 + u)
+  for (; g < nchunk * 4; ++g) {
+    const int i0 = (g >> 2) * kStageElems + ((g & 3) * kHT + ht) * 4;
+    if (i0 >= V) continue;
+    const float4 v = load4_scaled<TIn>(row + i0, temp);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float x = k == 0 ? v.x : (k == 1 ? v.y : (k == 2 ? v.z : v.w));
+      if (x >= cut) {
+        const int pos = atomicAdd(&hs->novf, 1);
+        if (pos < kOvf) hs->ovf[pos] = ListEntry{x, i0 + k};
+      }
+    }
+  }
+}
 
 __device__ __forceinline__ float warp_sort_asc(float v, int lane) {
 #pragma unroll
@@ -146,97 +162,88 @@ __device__ __forceinline__ int lv_bucket(float A, float sc, float x) {
   return bk < 0 ? 0 : (bk > kLB - 1 ? kLB - 1 : bk);
 }
 
-// Nucleus boundary of one row among the entries its half captured.  lst[j * 128], j < nt, are the
-// thread's entries in capture order, bmt its bit-map column.  A level spreads the entries of the current
-// bracket [mA, mB] over 16 value buckets with per-thread FLOAT histograms (private columns: no atomics)
-// and scans the bucket sums from the top for the bucket in which the kept mass crosses top_p * Z; the
-// next level's loop then takes the EXACT mass above that bucket (38-bit fixed point, as in
-// pair::half_select: sums do not depend on the order of anything), counts the bucket's entries, takes
-// their value range as the new bracket and builds the next histogram in the same trip.  With <= 128
-// entries left the all-pairs finish orders them like the reference's sort and tests the crossing
-// exactly.  Returns false when the row needs the general search (nucleus not inside the captured set,
-// ties beyond the finish, float/exact disagreement at a bucket edge).
-__device__ __forceinline__ bool cap_select(const float* lst, int nt, const unsigned short* bmt, int h, int ht,
-                                           float* hist, float Zrow, double target, float m0, CapSync* cs,
-                                           CapScratch* hs, RowRecord& rec) {
+// index of the thread's j-th captured entry (capture order) from its bit-map column
+__device__ __forceinline__ int cap_index_of(const unsigned short* bmt, int j, int ht) {
+  int stage = 0;
+  unsigned hm = bmt[0];
+  while (__popc(hm) <= j) {
+    j -= __popc(hm);
+    ++stage;
+    hm = bmt[stage * kHT];
+  }
+  const int k = __fns(hm, 0, j + 1);
+  return stage * kStageElems + ((k >> 2) * kHT + ht) * 4 + (k & 3);
+}
+
+// Closes one row on the entries its half captured: nucleus boundary (rec.Z / xstar / istar) and, for a
+// target row, the list of kept entries in the workspace.  The thread's entries are lst[j * 128], j < nt
+// (capture order; bit-map column bmt gives their indices) plus its share of the half's overflow pool
+// (entries ht, ht + 128, ... of hs->ovf, with explicit indices): local entry numbers 0 .. ne-1 < 64.
+//
+//   A  one loop over all entries: per-thread FLOAT histogram (private shared-memory column, no atomics,
+//      fixed summation order: deterministic) of e = 2^(x*log2e - m0) over 16 value buckets of [cut, max].
+//   B  bucket sums, scanned from the top: the bucket b* in which the kept mass crosses top_p * Z and the
+//      mass G above it.
+//   C  one loop over all entries: two 64-bit masks per thread - entries above b* (kept for sure) and
+//      entries in b* (candidates).  From here on only mask bits are visited.
+//   D  while more than 128 candidates remain: 16 sub-buckets of the crossing bucket, histogram over the
+//      candidates only, same scan; candidates above the new crossing bucket join the kept mask.
+//   F  the <= 128 candidates left are ordered exactly like the reference's sort (scaled logit descending,
+//      lowest index first) by an all-pairs rank in 38-bit fixed point (integer sums: exactly one entry
+//      crosses), as in pair::half_select.
+//   E  emission: the kept mask's entries go to the row's list at per-thread offsets (prefix sum of the
+//      counts: no atomics in the loop), the kept candidates behind them.
+// Returns false when the row needs the general search (nucleus not inside the captured set, more equal
+// values than the finish can order, float scan and exact finish disagreeing at a bucket edge).
+__device__ __noinline__ bool cap_close(const float* lst, int nt, const unsigned short* bmt, int novf, int h, int ht,
+                                       float* hist, float cut, float xmax, float Zrow, double target, float m0,
+                                       CapSync* cs, CapScratch* hs, RowRecord& rec, ListEntry* emit, int* nemit_out,
+                                       int* stats) {
   const int lane = ht & 31, hw = ht >> 5;
-  const int ez = int(__float_as_uint(Zrow) >> 23) - 126;               // Z = f * 2^ez, f in [0.5, 1)
-  const float S = __uint_as_float(unsigned(127 + 38 - ez) << 23);      // 2^(38 - ez)
-  const unsigned long long tgt = (unsigned long long)(target * double(S));  // floor
-  auto fx = [&](float x) { return __float2ull_rn(row_exp(x, m0) * S); };
+  const int ne = nt + (novf - ht + kHT - 1) / kHT;
   float* hp = hist + ht;
-
-  // ---- value range of the captured entries
-  float emx = -INFINITY, engmn = -INFINITY;
-  for (int j = 0; j < nt; ++j) {
-    const float x = lst[j * kHT];
-    emx = fmaxf(emx, x), engmn = fmaxf(engmn, -x);
-  }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    emx = fmaxf(emx, __shfl_xor_sync(0xffffffffu, emx, o));
-    engmn = fmaxf(engmn, __shfl_xor_sync(0xffffffffu, engmn, o));
-  }
-  if (lane == 0) cs->mm[h][hw] = make_float2(emx, engmn);
+  auto getx = [&](int j) { return j < nt ? lst[j * kHT] : hs->ovf[(j - nt) * kHT + ht].x; };
+  auto geti = [&](int j) { return j < nt ? cap_index_of(bmt, j, ht) : hs->ovf[(j - nt) * kHT + ht].idx; };
+  if (!(cut > -INFINITY) || !(xmax >= cut) || !(xmax < INFINITY)) return false;
+  float fA = cut, fsc = float(kLB) / (nextafterf(xmax, INFINITY) - cut);
+  if (!(fsc < INFINITY)) return false;
   if (ht == 0) hs->ncand = 0, hs->res_ok = 0;
-  barh(h);
-#pragma unroll
-  for (int w = 0; w < kHW; ++w) emx = fmaxf(emx, cs->mm[h][w].x), engmn = fmaxf(engmn, cs->mm[h][w].y);
-  if (!(emx > -INFINITY) || !(engmn > -INFINITY)) return false;  // nothing captured (or -inf / NaN inside)
-  float mA = -engmn, mB = emx;  // current bracket: the entries with mA <= x <= mB; x > mB is in GBf
-  float fA = mA, fsc = float(kLB) / (nextafterf(mB, INFINITY) - mA);  // this level's bucket function
-  float pA = 0.0f, psc = 0.0f;  // the previous level's bucket function and chosen bucket
-  int pb = 0;
-  unsigned long long GBf = 0ull;  // exact mass above the bracket
-  bool small = false;
 
+  // ---- A: level-0 histogram over all entries
+#pragma unroll
+  for (int b = 0; b < kLB; ++b) hp[b * kHT] = 0.0f;
+#pragma unroll 2
+  for (int j = 0; j < ne; ++j) {
+    const float x = getx(j);
+    hp[lv_bucket(fA, fsc, x) * kHT] += row_exp(x, m0);
+  }
+  unsigned long long keptm = 0ull, candm = 0ull;
+  float G = 0.0f;  // mass above the current crossing bucket (float, fixed order)
+  int total = 0;
 #pragma unroll 1
   for (int level = 0; level < kMaxLevels; ++level) {
-#pragma unroll
-    for (int b = 0; b < kLB; ++b) hp[b * kHT] = 0.0f;
-    unsigned long long gb = 0ull;
-    int cnt = 0;
-    float nmx = -INFINITY, nngmn = -INFINITY;
-    for (int j = 0; j < nt; ++j) {
-      const float x = lst[j * kHT];
-      if (!(x >= mA && x <= mB)) continue;
-      if (level > 0) {
-        const int bp = lv_bucket(pA, psc, x);
-        if (bp > pb) gb += fx(x);
-        if (bp != pb) continue;
-        ++cnt;
-        nmx = fmaxf(nmx, x), nngmn = fmaxf(nngmn, -x);
-      }
-      hp[lv_bucket(fA, fsc, x) * kHT] += row_exp(x, m0);
-    }
     if (level > 0) {
+      // ---- D: histogram of the candidates over the sub-buckets of the crossing bucket, and their number
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        gb += __shfl_xor_sync(0xffffffffu, gb, o);
-        cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
-        nmx = fmaxf(nmx, __shfl_xor_sync(0xffffffffu, nmx, o));
-        nngmn = fmaxf(nngmn, __shfl_xor_sync(0xffffffffu, nngmn, o));
+      for (int b = 0; b < kLB; ++b) hp[b * kHT] = 0.0f;
+      for (unsigned long long m = candm; m; m &= m - 1ull) {
+        const float x = getx(__ffsll((long long)m) - 1);
+        hp[lv_bucket(fA, fsc, x) * kHT] += row_exp(x, m0);
       }
-      if (lane == 0) hs->wgb[hw] = gb, hs->wcnt[hw] = cnt, cs->mm[h][hw] = make_float2(nmx, nngmn);
+      int cnt = __popcll(candm);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+      if (lane == 0) hs->wcnt[hw] = cnt;
     }
-    barh(h);  // histogram columns (and the warp partials) complete
+    barh(h);  // histogram columns (and the candidate counts) complete
+    if (ht == 0) STAMP(stats, level == 0 ? 26 : 28);
     if (level > 0) {
-      gb = 0ull, cnt = 0;
+      total = 0;
 #pragma unroll
-      for (int w = 0; w < kHW; ++w) {
-        gb += hs->wgb[w], cnt += hs->wcnt[w];
-        nmx = fmaxf(nmx, cs->mm[h][w].x), nngmn = fmaxf(nngmn, cs->mm[h][w].y);
-      }
-      GBf += gb;
-      if (cnt <= 0) return false;  // (the scan only chooses non-empty buckets)
-      mA = -nngmn, mB = nmx;
-      if (cnt <= kHT) {
-        small = true;
-        break;
-      }
-      if (mA == mB) return false;  // more equal values than the finish can order
+      for (int w = 0; w < kHW; ++w) total += hs->wcnt[w];
+      if (total <= kHT) break;  // few enough for the all-pairs finish
     }
-    // ---- bucket sums (warp w owns buckets 4w .. 4w+3), then every thread scans them from the top
+    // ---- B: bucket sums (warp w owns buckets 4w .. 4w+3), then every thread scans them from the top
 #pragma unroll
     for (int q = 0; q < kLB / kHW; ++q) {
       const int b = hw * (kLB / kHW) + q;
@@ -248,7 +255,7 @@ __device__ __forceinline__ bool cap_select(const float* lst, int nt, const unsig
       if (lane == 0) cs->hsum[h][b] = s;
     }
     barh(h);
-    float run = float(double(GBf) / double(S));
+    float run = G;
     int bstar = -1;
 #pragma unroll
     for (int b = kLB - 1; b >= 0; --b) {
@@ -256,28 +263,71 @@ __device__ __forceinline__ bool cap_select(const float* lst, int nt, const unsig
       if (bstar < 0 && s > 0.0f && double(run + s) > target) bstar = b;
       if (bstar < 0) run += s;
     }
-    barh(h);  // hsum, the warp partials and the histogram are free again
+    if (ht == 0) STAMP(stats, 27);
     if (bstar < 0) return false;  // the kept mass does not cross inside the captured entries
-    pA = fA, psc = fsc, pb = bstar;
+    G = run;
+    // ---- C: classify - above the crossing bucket: kept for sure; inside it: candidate
+    if (level == 0) {
+#pragma unroll 2
+      for (int j = 0; j < ne; ++j) {
+        const int bk = lv_bucket(fA, fsc, getx(j));
+        keptm |= (unsigned long long)(bk > bstar) << j;
+        candm |= (unsigned long long)(bk == bstar) << j;
+      }
+    } else {
+      for (unsigned long long m = candm; m; m &= m - 1ull) {
+        const int j = __ffsll((long long)m) - 1;
+        const int bk = lv_bucket(fA, fsc, getx(j));
+        if (bk > bstar) keptm |= 1ull << j;
+        if (bk != bstar) candm &= ~(1ull << j);
+      }
+    }
     fA = fmaf(float(bstar), 1.0f / fsc, fA);
     fsc = fsc * float(kLB);
+    // (the next level's barrier orders these reads of hsum / hist before they are overwritten)
   }
-  if (!small) return false;
-  // ---- the bracket's entries, ordered exactly like the reference's sort
-  {
-    BitWalk bw(bmt);
-    for (int j = 0; j < nt; ++j) {
-      const float x = lst[j * kHT];
-      const int idx = bw.next(ht);
-      if (x >= mA && x <= mB) {
-        const int pos = atomicAdd(&hs->ncand, 1);
-        if (pos < kHT) hs->cand_x[pos] = x, hs->cand_f[pos] = fx(x), hs->cand_i[pos] = idx;
-      }
+  if (total > kHT || total <= 0) return false;  // more (equal) values than the finish can order
+  // ---- E (first half): offsets of the kept-for-sure entries in the row's list
+  int off = 0;
+  if (emit != nullptr) {
+    const int c = __popcll(keptm);
+    int inc = c;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int o = __shfl_up_sync(0xffffffffu, inc, d);
+      if (lane >= d) inc += o;
+    }
+    if (lane == 31) hs->wpre[hw] = inc;
+    off = inc - c;
+  }
+  // ---- F: the candidates left, with their indices, in the reference's order
+  const int ez = int(__float_as_uint(Zrow) >> 23) - 126;               // Z = f * 2^ez, f in [0.5, 1)
+  const float S = __uint_as_float(unsigned(127 + 38 - ez) << 23);      // 2^(38 - ez)
+  const unsigned long long tgt = (unsigned long long)(target * double(S));  // floor
+  const unsigned long long GBf = (unsigned long long)(double(G) * double(S));
+  for (unsigned long long m = candm; m; m &= m - 1ull) {
+    const int j = __ffsll((long long)m) - 1;
+    const float x = getx(j);
+    const int pos = atomicAdd(&hs->ncand, 1);
+    if (pos < kHT) {
+      hs->cand_x[pos] = x;
+      hs->cand_f[pos] = __float2ull_rn(row_exp(x, m0) * S);
+      hs->cand_i[pos] = geti(j);
     }
   }
   barh(h);
+  if (ht == 0) STAMP(stats, 29);
   const int n = hs->ncand;
   if (n > kHT || n <= 0) return false;
+  int certain = 0;
+  if (emit != nullptr) {
+#pragma unroll
+    for (int w = 0; w < kHW; ++w) {
+      if (w < hw) off += hs->wpre[w];
+      certain += hs->wpre[w];
+    }
+    if (ht == 0) hs->nemit = certain;
+  }
   int Pn = 16;
   while (Pn < n) Pn <<= 1;
   const int parts = kHT / Pn;  // 1..8 threads share one candidate (same warp)
@@ -295,49 +345,58 @@ __device__ __forceinline__ bool cap_select(const float* lst, int nt, const unsig
   }
   for (int o = parts >> 1; o > 0; o >>= 1) cum += __shfl_xor_sync(0xffffffffu, cum, o);
   const unsigned long long incl = GBf + cum;
-  if (t < n && part == 0 && incl > tgt && incl - fme <= tgt) {
+  const bool mine = t < n && part == 0;
+  if (mine && incl > tgt && incl - fme <= tgt) {
     hs->res_x = xx;
     hs->res_i = ii;
     hs->gb_new = incl;
     hs->res_ok = 1;
   }
-  barh(h);
+  barh(h);  // also: nemit holds the number of kept-for-sure entries
   if (!hs->res_ok) return false;  // the float scan chose a neighbouring bucket (edge case): general search
   rec.Z = float(double(hs->gb_new) / double(S));
   rec.xstar = hs->res_x;
   rec.istar = hs->res_i;
-  return true;
-}
-
-// kept entries of a finished target row -> the row's list in the workspace (any order); returns the count
-__device__ __forceinline__ int cap_emit(const float* lst, int nt, const unsigned short* bmt, int h, int ht,
-                                        const RowRecord& rec, ListEntry* out, CapScratch* hs) {
-  const int lane = ht & 31;
-  if (ht == 0) hs->nemit = 0;
-  barh(h);
-  int ntmax = nt;
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) ntmax = max(ntmax, __shfl_xor_sync(0xffffffffu, ntmax, o));
-  BitWalk bw(bmt);
-  for (int j = 0; j < ntmax; ++j) {
-    float x = 0.0f;
-    int idx = 0;
-    bool keep = false;
-    if (j < nt) {
-      x = lst[j * kHT];
-      idx = bw.next(ht);
-      keep = kept(rec, x, idx);
+  if (emit == nullptr) return true;
+  // ---- E (second half): candidates at or before the crossing entry, then the kept mask's entries
+  {
+    const bool keep = mine && incl - fme <= tgt;
+    const unsigned bal = __ballot_sync(0xffffffffu, keep);
+    if (bal != 0u) {
+      int base = 0;
+      if (lane == 0) base = atomicAdd(&hs->nemit, __popc(bal));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      const int pos = base + __popc(bal & ((1u << lane) - 1u));
+      if (keep && pos < kListCap) emit[pos] = ListEntry{xx, ii};
     }
-    const unsigned m = __ballot_sync(0xffffffffu, keep);
-    if (m == 0u) continue;
-    int base = 0;
-    if (lane == 0) base = atomicAdd(&hs->nemit, __popc(m));
-    base = __shfl_sync(0xffffffffu, base, 0);
-    const int pos = base + __popc(m & ((1u << lane) - 1u));
-    if (keep && pos < kListCap) out[pos] = ListEntry{x, idx};
+  }
+  if (keptm != 0ull) {
+    int j = 0;
+    const int nstage_bits = nt;  // entries 0 .. nt-1 are walked through the bit map, the rest carry their index
+    int stage = -1;
+    unsigned hm = 0u;
+    for (; j < nstage_bits; ++j) {
+      while (hm == 0u) {
+        ++stage;
+        hm = bmt[stage * kHT];
+      }
+      const int k = __ffs(hm) - 1;
+      hm &= hm - 1u;
+      if ((keptm >> j) & 1ull) {
+        if (off < kListCap) emit[off] = ListEntry{lst[j * kHT], stage * kStageElems + ((k >> 2) * kHT + ht) * 4 + (k & 3)};
+        ++off;
+      }
+    }
+    for (; j < ne; ++j) {
+      if ((keptm >> j) & 1ull) {
+        if (off < kListCap) emit[off] = hs->ovf[(j - nt) * kHT + ht];
+        ++off;
+      }
+    }
   }
   barh(h);
-  return hs->nemit;
+  *nemit_out = hs->nemit;
+  return true;
 }
 
 template <class TIn>
@@ -365,6 +424,7 @@ __global__ void __launch_bounds__(kPT, 2) row_capture_kernel(const __grid_consta
       }
     mbar_fence_init();
     cs->nlist = 0;
+    hsc[0].novf = 0, hsc[1].novf = 0;
   }
   __syncthreads();
   // nothing above touches global memory; inputs and the workspace are ordered from here on
@@ -412,6 +472,7 @@ __global__ void __launch_bounds__(kPT, 2) row_capture_kernel(const __grid_consta
   float* hist = hist_all + h * kLB * kHT;
   unsigned short* bmt = reinterpret_cast<unsigned short*>(bm_all + size_t(h) * cap_bitmap_bytes(nchunk)) + ht;
   const unsigned lp0 = smem_u32(lst), lim = lp0 + unsigned(kSlots - 4) * unsigned(kHT * 4);
+  CapScratch* hs = hsc + h;
   ListEntry* glist = P.lists + (long long)(P.B * (gamma + 1) + int(blockIdx.x)) * kListCap;  // the general search's scratch list
   unsigned seq = 0;
 
@@ -433,12 +494,11 @@ __global__ void __launch_bounds__(kPT, 2) row_capture_kernel(const __grid_consta
       if (tok >= 0 && tok < V) xtok = scale_logit(to_f32(__ldcg(row + tok)), temp);
     }
 
-    int state = 0, nt = 0;
-    float Z = 0.0f, m0 = 0.0f;
+    int state = 0, nt = 0, novf = 0;
+    float Z = 0.0f, m0 = 0.0f, cut = INFINITY, xmax = -INFINITY;
     double target = 0.0;
     if (have) {
       // ---- sample stage: exponent offset and capture cut from the row itself
-      float cut = INFINITY;
       {
         CAP_STAGE_BEGIN(-1)
         float m16 = -INFINITY;
@@ -454,9 +514,11 @@ __global__ void __launch_bounds__(kPT, 2) row_capture_kernel(const __grid_consta
 #pragma unroll
         for (int w = 0; w < kHW; ++w) csum += cs->pro[h][w].x, mx = fmaxf(mx, cs->pro[h][w].y);
         cut = csum * (1.0f / kHW);
+        xmax = mx;
         m0 = mx * kLog2e;
       }
       if (!nucleus) cut = INFINITY;
+      // (hs->novf of this half is zero here: set below at the row's end, ordered by the half barriers in between)
       // ---- the stream: sum of exponentials in registers, entries above the cut into the list column
       float z0 = 0.0f, z1 = 0.0f, z2 = 0.0f, z3 = 0.0f;
       unsigned lp = lp0;
@@ -489,19 +551,19 @@ __global__ void __launch_bounds__(kPT, 2) row_capture_kernel(const __grid_consta
       float z = (z0 + z1) + (z2 + z3);
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) z += __shfl_xor_sync(0xffffffffu, z, o);
-      const bool ovf = __any_sync(0xffffffffu, lp >= lim);
-      if (lane == 0) cs->post[h][hw] = make_float2(z, ovf ? 1.0f : 0.0f);
+      if (lp >= lim) cap_spill_rest<TIn>(hs, bmt, row, V, nchunk, temp, cut, ht);
+      if (lane == 0) cs->post[h][hw] = make_float2(z, 0.0f);
       barh(h);  // also: every list column and bit map of the half is complete
       if (ht == 0) STAMP(P.stats, 9);
-      float of = 0.0f;
       z = 0.0f;
 #pragma unroll
-      for (int w = 0; w < kHW; ++w) z += cs->post[h][w].x, of += cs->post[h][w].y;
+      for (int w = 0; w < kHW; ++w) z += cs->post[h][w].x;
       Z = z;
+      novf = hs->novf;
       nt = int((lp - lp0) / unsigned(kHT * 4));
       const bool bad = !(Z < INFINITY) || !(Z > 0.0f);
       if (!nucleus) state = bad ? 3 : (top_p >= 1.0f ? 4 : 1);
-      else state = (bad || of > 0.0f) ? 3 : 2;
+      else state = (bad || novf > kOvf) ? 3 : 2;
       target = double(top_p) * double(Z);
     }
     // ---- each half closes its own row
@@ -509,13 +571,12 @@ __global__ void __launch_bounds__(kPT, 2) row_capture_kernel(const __grid_consta
     rec.m0 = m0, rec.Z = Z, rec.xstar = -INFINITY, rec.istar = 0x7fffffff;
     rec.sel = 0.0f, rec.mxl = m0, rec.dens = 0.0f, rec.pad = 0;
     if (state == 2) {
-      const bool ok = cap_select(lst, nt, bmt, h, ht, hist, Z, target, m0, cs, hsc + h, rec);
+      int nem = 0;
+      ListEntry* el = jb.is_target ? P.lists + (long long)(jb.b * (gamma + 1) + jb.j) * kListCap : nullptr;
+      const bool ok = cap_close(lst, nt, bmt, novf, h, ht, hist, cut, xmax, Z, target, m0, cs, hs, rec, el, &nem, P.stats);
       if (!ok) state = 3;
       if (ht == 0) STAMP(P.stats, 10);
-      if (ok && jb.is_target) {
-        const int ne = cap_emit(lst, nt, bmt, h, ht, rec, P.lists + (long long)(jb.b * (gamma + 1) + jb.j) * kListCap, hsc + h);
-        rec.pad = ne <= kListCap ? ne + 1 : 0;
-      }
+      if (ok && jb.is_target) rec.pad = nem <= kListCap ? nem + 1 : 0;
       if (P.stats && ht == 0) atomicAdd(&P.stats[ok ? 16 : 17], 1);
     }
     if (ht == 0) {
@@ -531,7 +592,10 @@ __global__ void __launch_bounds__(kPT, 2) row_capture_kernel(const __grid_consta
         store_record(&P.records[job], rec);
       }
     }
-    if (ht == 0) STAMP(P.stats, 11);
+    if (ht == 0) {
+      hs->novf = 0;  // every reader of this row's pool is behind a half barrier; the next row's appends are after the join
+      STAMP(P.stats, 11);
+    }
     bar3();  // ---- the halves join: rows that need the general search (rare) are finished one after the other
 
     const int st[2] = {cs->half[0].state, cs->half[1].state};

@@ -8,11 +8,11 @@
 namespace duodec {
 
 struct NormParams {
-  const void* logits;  // [rows, V], vocab stride 1
-  long long in_stride;
-  void* out;  // [rows, V]
-  long long out_stride;
-  int rows, V;
+  const void* logits;  // [batch, inner, V], vocab stride 1; row = b * inner + s
+  long long in_stride, in_bstride;
+  void* out;  // [batch, inner, V]
+  long long out_stride, out_bstride;
+  int rows, inner, V;
   float temperature, top_p;
   int top_k;
   int per, slice_floats;
@@ -35,8 +35,9 @@ __global__ void __launch_bounds__(kThreads, 1) norm_logits_kernel(const __grid_c
     mbar_fence_init();
   }
   __syncthreads();
-  const TIn* row = reinterpret_cast<const TIn*>(P.logits) + rowi * P.in_stride;
-  TOut* out = reinterpret_cast<TOut*>(P.out) + rowi * P.out_stride;
+  const long long rb = rowi / P.inner, rs = rowi - rb * P.inner;
+  const TIn* row = reinterpret_cast<const TIn*>(P.logits) + rb * P.in_bstride + rs * P.in_stride;
+  TOut* out = reinterpret_cast<TOut*>(P.out) + rb * P.out_bstride + rs * P.out_stride;
   const Slice s = team_slice(P.per, P.V, rank);
   const bool greedy = P.temperature == 0.0f;
   const float temp = greedy ? 1.0f : P.temperature;

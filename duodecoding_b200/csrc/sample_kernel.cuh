@@ -32,23 +32,41 @@ __device__ __noinline__ long long compact_token(const SplitParams& P, int b, int
   const float* nz = P.noise + (long long)b * P.noise_sb;
   float mass = 0.0f;
   unsigned long long pk = 0ull;
-  for (int e = tid; e < ncomp; e += kT3) {
-    const int2 raw = __ldcg(reinterpret_cast<const int2*>(L + e));
-    const float x = __int_as_float(raw.x);
-    const int i = raw.y;
-    float d = row_exp(x, rp.m0) * invZp;
-    if (!bonus) {
-      const float y = scale_logit(to_f32(__ldcg(qrow + i)), P.d_temp);
-      const bool kq = (y > rq.xstar) | ((y == rq.xstar) & (i <= rq.istar));
-      const float qe = row_exp(y, rq.m0) * invZq;
-      d -= kq ? qe : 0.0f;
+  // batches of 8 entries per thread: all list loads first, then all gathers, then the arithmetic, so that
+  // a batch costs three memory round trips instead of three per entry
+  for (int e0 = 0; e0 < ncomp; e0 += 8 * kT3) {
+    int2 raw[8];
+    float y[8], nzv[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int e = e0 + u * kT3 + tid;
+      raw[u] = e < ncomp ? __ldcg(reinterpret_cast<const int2*>(L + e)) : make_int2(0, -1);
     }
-    if (d > 0.0f) {
-      mass += d;
-      const float key = __fdividef(d, __ldg(nz + i));
-      const unsigned long long k2 =
-          ((unsigned long long)__float_as_uint(key) << 32) | (unsigned long long)(0xffffffffu - unsigned(i));
-      if (key >= 0.0f && k2 > pk) pk = k2;  // (a NaN key never wins, as in the sliced loop)
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int i = raw[u].y;
+      y[u] = (i >= 0 && !bonus) ? to_f32(__ldcg(qrow + i)) : 0.0f;
+      nzv[u] = i >= 0 ? __ldg(nz + i) : 1.0f;
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int i = raw[u].y;
+      if (i < 0) continue;
+      const float x = __int_as_float(raw[u].x);
+      float d = row_exp(x, rp.m0) * invZp;
+      if (!bonus) {
+        const float ys = scale_logit(y[u], P.d_temp);
+        const bool kq = (ys > rq.xstar) | ((ys == rq.xstar) & (i <= rq.istar));
+        const float qe = row_exp(ys, rq.m0) * invZq;
+        d -= kq ? qe : 0.0f;
+      }
+      if (d > 0.0f) {
+        mass += d;
+        const float key = __fdividef(d, nzv[u]);
+        const unsigned long long k2 =
+            ((unsigned long long)__float_as_uint(key) << 32) | (unsigned long long)(0xffffffffu - unsigned(i));
+        if (key >= 0.0f && k2 > pk) pk = k2;  // (a NaN key never wins, as in the sliced loop)
+      }
     }
   }
 #pragma unroll
@@ -102,6 +120,7 @@ __global__ void __launch_bounds__(kT3, 4) seq_sample_tma_kernel(const __grid_con
   __shared__ unsigned long long wkey[kW3], wbd[kW3];
   __shared__ float wmass[kW3];
   __shared__ unsigned long long mb[2];
+  __shared__ int acc0[64];
   constexpr int kElt = int(sizeof(TIn));
   unsigned char* s_noise = sm3;                                   // [kSlice3] float
   unsigned char* s_p = sm3 + size_t(kSlice3) * 4;                 // [kSlice3] TIn
@@ -188,9 +207,18 @@ __global__ void __launch_bounds__(kT3, 4) seq_sample_tma_kernel(const __grid_con
       P.sel_q[o] = rq.sel;
     }
   }
+  if (P.row0_rule && b != 0 && tid < gamma) {
+    // the reference's batch rule (src/decoding_ops.py:144-147): sequence 0's accepted count positions every sequence
+    const RowRecord q0 = load_record(&P.records[2 * tid]), p0 = load_record(&P.records[2 * tid + 1]);
+    acc0[tid] = __ldg(&P.r[tid]) <= __fdiv_rn(p0.sel, q0.sel);
+  }
   bar3();
   int n = 0;
-  while (n < gamma && sc.seq_acc[n] != 0) ++n;
+  if (P.row0_rule && b != 0) {
+    while (n < gamma && acc0[n] != 0) ++n;
+  } else {
+    while (n < gamma && sc.seq_acc[n] != 0) ++n;
+  }
   const bool bonus = (n == gamma);
   const RowRecord rp = srec[bonus ? 2 * gamma : 2 * n + 1];
   const RowRecord rq = bonus ? rp : srec[2 * n];

@@ -1,22 +1,9 @@
-// Split verification kernels (the default fast path of duodec_verify_fused).
-//
-//   row_scan_kernel   grid (S slices, rows): every block streams ONE 8192-entry slice of one
-//                     logit row with eight independent 128-bit loads per thread in flight,
-//                     and reduces  max, Z = sum 2^(x*log2e - M0), the mass above a predicted
-//                     nucleus window and the window's entries (appended to the row's list in
-//                     global memory).  The block that finishes a row LAST resolves the row:
-//                     nucleus boundary from the list (narrowing on registers + exact all-pairs
-//                     order of the last <= 160 candidates), kept mass Z', probability of the
-//                     drafted token -> a 32-byte record.  A row whose boundary is not inside the
-//                     predicted window (cold start, unusual row) is re-read through L2 by that
-//                     block with a moved window.
-//   seq_sample_kernel grid (S3 slices, B): accept tests r <= p/q from the records, leading run,
-//                     and the ONE token the sequence needs - residual resample at the first
-//                     rejection or the bonus sample - as a sliced arg-max of d_i / noise_i that
-//                     is combined across slices with packed 64-bit atomicMax.
-//
-// HBM traffic: every logit once (row_scan), plus per sequence two rows through L2 and one noise
-// row (seq_sample).  Reference semantics: see stream_kernel.cuh (same record / keep rule).
+// Row-level building blocks shared by the fused-verify fast paths: the parameter block, the list
+// entry, block reductions, and the GENERAL nucleus search of one row by one 256-thread block through
+// L2 (rescan_row -> resolve_row3 -> list_select_body: windowed passes with plain loads, exact 38-bit
+// fixed-point level histogram, all-pairs order of the last candidates, tie bisection).  The scan
+// kernels call it for rows their fast scheme cannot finish (flat rows, large tie groups, exponent
+// offsets far from the row maximum).  Reference semantics: see stream_kernel.cuh.
 #pragma once
 
 #include "stream_kernel.cuh"
@@ -99,6 +86,7 @@ struct SplitParams {
   int* stats;
   int cap_rank;      // row-capture kernel: rank (0..31) of the sorted group maxima that gives the capture cut
   int compact_hint;  // sample kernel: target rows are expected to come with a kept-entry list (no noise prefetch)
+  int row0_rule;     // sample kernel: sequence 0's accepted count positions every sequence (reference batch rule)
 };
 
 struct __align__(16) Scratch3 {
@@ -536,355 +524,6 @@ __device__ __forceinline__ const TIn* split_row(const SplitParams& P, RowJob jb)
   return jb.is_target
              ? reinterpret_cast<const TIn*>(P.target) + (long long)jb.b * P.t_sb + (long long)jb.j * P.t_ss
              : reinterpret_cast<const TIn*>(P.draft) + (long long)jb.b * P.d_sb + (long long)jb.j * P.d_ss;
-}
-
-// ---------------------------------------------------------------------------
-// kernel 1: slice scan + (last block of a row) row resolve
-// ---------------------------------------------------------------------------
-template <class TIn>
-__global__ void __launch_bounds__(kT3, 4) row_scan_kernel(const __grid_constant__ SplitParams P) {
-  __shared__ float col_x[kCol3 * kT3];
-  __shared__ int col_i[kCol3 * kT3];
-  __shared__ float ovf_x[kOvf3];
-  __shared__ int ovf_i[kOvf3];
-  __shared__ Scratch3 sc;
-
-  const int tid = threadIdx.x;
-  const int slice = blockIdx.x, job = blockIdx.y;
-  const int V = P.V, gamma = P.gamma;
-  const RowJob jb = decode_job(job, gamma);
-  const TIn* row = split_row<TIn>(P, jb);
-  const float temp = jb.is_target ? P.t_temp : P.d_temp;
-  const float top_p = jb.is_target ? P.t_top_p : P.d_top_p;
-  const bool nucleus = top_p > 0.0f;
-
-  // prediction of this launch (built by the previous one's seq_sample_kernel): exponent offset, window
-  const uint4 h = __ldg(reinterpret_cast<const uint4*>(&P.hints[jb.is_target]));
-  const bool warm = int(h.w) != 0;
-  float m0 = warm ? __uint_as_float(h.x) : 0.0f;
-  float dens = warm ? __uint_as_float(h.z) : 0.0f;
-  float lo = INFINITY, hi = INFINITY;
-  if (nucleus && warm && dens > 0.0f) {
-    const float hw = __ldg(&P.hints[jb.is_target].hw);
-    lo = __uint_as_float(h.y) - hw, hi = __uint_as_float(h.y) + hw;
-  }
-  if (tid == 0) sc.novf = 0;
-  bar3();
-
-  // ---- this block's slice: eight independent 128-bit loads per thread, then arithmetic
-  const int s0 = slice * kSlice;
-  float4 v[8];
-#pragma unroll
-  for (int u = 0; u < 8; ++u) {
-    const int i0 = s0 + u * 4 * kT3 + 4 * tid;
-    if (i0 < V) v[u] = load4_scaled<TIn>(row + i0, temp);
-  }
-  float mx = -INFINITY, z = 0.0f, ghi = 0.0f, gwin = 0.0f;
-  int cnt = 0;
-#pragma unroll
-  for (int u = 0; u < 8; ++u) {
-    const int i0 = s0 + u * 4 * kT3 + 4 * tid;
-    if (i0 < V) {
-      mx = fmaxf(mx, fmaxf(fmaxf(v[u].x, v[u].y), fmaxf(v[u].z, v[u].w)));
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const float x = f4c(v[u], k);
-        const float e = row_exp(x, m0);
-        z += e;
-        const bool above = x >= hi;
-        if (above) ghi += e;
-        if (x >= lo && !above) {  // rare: a window entry, staged in this thread's column
-          gwin += e;
-          if (cnt < kCol3) {
-            col_x[cnt * kT3 + tid] = x;
-            col_i[cnt * kT3 + tid] = i0 + k;
-          } else {
-            const int pos = atomicAdd(&sc.novf, 1);
-            if (pos < kOvf3) {
-              ovf_x[pos] = x;
-              ovf_i[pos] = i0 + k;
-            }
-          }
-          ++cnt;
-        }
-      }
-    }
-  }
-  int phase = 0;
-  R8 r;
-  r.v[0] = mx, r.v[1] = z, r.v[2] = ghi, r.v[3] = gwin, r.v[4] = float(cnt);
-  r.v[5] = r.v[6] = r.v[7] = 0.0f;
-  r = reduce3(r, &sc, phase);
-  const int ncta = int(r.v[4]);
-
-  // ---- append the staged entries to the row's list: one global atomic per block
-  ListEntry* list = P.lists + (long long)job * kListCap;
-  if (ncta > 0) {
-    const int mine = cnt < kCol3 ? cnt : kCol3;
-    int incl = mine;  // exclusive offset of this thread's column entries among the block's
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-      const int o = __shfl_up_sync(0xffffffffu, incl, d);
-      if ((tid & 31) >= d) incl += o;
-    }
-    if ((tid & 31) == 31) sc.wsum[tid >> 5] = incl;
-    if (tid == 0) {
-      // a block whose staging overflowed marks the list incomplete by over-reserving
-      const int reserve = sc.novf > kOvf3 ? kListCap + 1 : ncta;
-      sc.base = atomicAdd(&P.row_count[job], reserve);
-    }
-    bar3();
-    int off = incl - mine;
-    int colsum = 0;
-#pragma unroll
-    for (int w = 0; w < kW3; ++w) {
-      if (w < (tid >> 5)) off += sc.wsum[w];
-      colsum += sc.wsum[w];
-    }
-    const int base = sc.base;
-    for (int j = 0; j < mine; ++j) {
-      const int pos = base + off + j;
-      if (pos < kListCap) list[pos] = ListEntry{col_x[j * kT3 + tid], col_i[j * kT3 + tid]};
-    }
-    const int nov = sc.novf < kOvf3 ? sc.novf : kOvf3;
-    for (int t = tid; t < nov; t += kT3) {
-      const int pos = base + colsum + t;
-      if (pos < kListCap) list[pos] = ListEntry{ovf_x[t], ovf_i[t]};
-    }
-  }
-  if (tid == 0) {
-    P.partials[(long long)job * P.S + slice] = RowPartial{r.v[0], r.v[1], r.v[2], r.v[3]};
-  }
-  bar3();
-  if (tid == 0) {
-    __threadfence();  // cumulative: the barrier ordered every thread's list writes before it
-    sc.last = (atomicAdd(&P.row_arrive[job], 1) == P.S - 1);
-  }
-  bar3();
-  if (!sc.last) return;
-
-  // ---- this block finished the row: combine the slices and resolve it
-  __threadfence();
-  R8 c;
-  c.v[0] = -INFINITY;
-  c.v[1] = c.v[2] = c.v[3] = c.v[4] = c.v[5] = c.v[6] = c.v[7] = 0.0f;
-  for (int s = tid; s < P.S; s += kT3) {
-    const float4 q = __ldcg(reinterpret_cast<const float4*>(&P.partials[(long long)job * P.S + s]));
-    c.v[0] = fmaxf(c.v[0], q.x), c.v[1] += q.y, c.v[2] += q.z, c.v[3] += q.w;
-  }
-  c = reduce3(c, &sc, phase);
-  Pass3 pr;
-  pr.mx = c.v[0], pr.z = c.v[1], pr.ghi = c.v[2], pr.gwin = c.v[3];
-  pr.n = *reinterpret_cast<volatile int*>(&P.row_count[job]);
-  if (!(fabsf(pr.mx * kLog2e - m0) <= 32.0f) || !(pr.z < INFINITY) || !(pr.z > 0.0f)) {
-    // the predicted offset was far from this row's maximum: redo the pass with the exact one
-    m0 = pr.mx * kLog2e;
-    pr = rescan_row<TIn, kListCap>(row, V, temp, m0, lo, hi, list, &P.row_count[job], &sc, phase);
-  }
-  RowRecord rec;
-  rec.m0 = m0;
-  rec.Z = pr.z;
-  rec.xstar = -INFINITY;
-  rec.istar = 0x7fffffff;
-  rec.sel = 0.0f;
-  rec.mxl = pr.mx * kLog2e;
-  rec.dens = 0.0f;
-  float theta = pr.mx;
-  if (nucleus)
-    resolve_row3<TIn, kListCap>(row, V, temp, top_p, m0, pr, lo, hi, dens, list, &P.row_count[job], &sc, phase, rec, &theta,
-                      &dens, P.stats);
-  if (tid == 0) {
-    if (jb.j < gamma) {
-      const long long tok = P.tokens[(long long)jb.b * P.tok_sb + jb.j];
-      if (tok >= 0 && tok < V) {
-        const float x = scale_logit(to_f32(__ldcg(row + tok)), temp);
-        const float e = kept(rec, x, int(tok)) ? row_exp(x, m0) : 0.0f;
-        rec.sel = __fdiv_rn(e, rec.Z);
-      }
-    }
-    rec.dens = (nucleus && rec.xstar > -INFINITY) ? dens : 0.0f;
-    store_record(&P.records[job], rec);
-    P.row_count[job] = 0;
-    P.row_arrive[job] = 0;
-  }
-}
-
-// ---------------------------------------------------------------------------
-// kernel 2: accept tests, leading run, sliced token draw
-// ---------------------------------------------------------------------------
-struct SampleAcc {
-  float mass;
-  unsigned long long key;  // (bits(d / noise) << 32) | ~index, d > 0
-  unsigned long long bd;   // (okey(p - q) << 32) | ~index      (zero-mass fallback: first argmax of p - q)
-};
-
-template <class TIn>
-__global__ void __launch_bounds__(kT3, 4) seq_sample_kernel(const __grid_constant__ SplitParams P) {
-  __shared__ Scratch3 sc;
-  __shared__ unsigned long long wkey[kW3], wbd[kW3];
-  __shared__ float wmass[kW3];
-  const int tid = threadIdx.x;
-  const int slice = blockIdx.x, b = blockIdx.y;
-  const int gamma = P.gamma, V = P.V;
-  const int base = b * (2 * gamma + 1);
-
-  // the noise slice does not depend on the scan kernel: its loads go out before the grid dependency
-  // resolves (the caller wrote the noise before the scan kernel was launched)
-  const float* nz = P.noise + (long long)b * P.noise_sb;
-  const int s0 = slice * kSlice3;
-  float4 nv4[kSlice3 / (4 * kT3)];
-#pragma unroll
-  for (int u = 0; u < kSlice3 / (4 * kT3); ++u) {
-    const int i0 = s0 + u * 4 * kT3 + 4 * tid;
-    if (i0 < V && b < P.B) nv4[u] = __ldg(reinterpret_cast<const float4*>(nz + i0));
-  }
-  if (tid == 0) STAMP(P.stats, 12, true);
-  float rj = 0.0f;  // the acceptance draw of position tid: an input as well
-  if (b < P.B && tid < gamma) rj = __ldg(&P.r[(long long)b * P.r_sb + tid]);
-  grid_dep_wait();
-  grid_dep_launch();
-  if (tid == 0) STAMP(P.stats, 13);
-
-  if (b == P.B) {  // the extra block row: block 0 of it aggregates the next launch's prediction, off the critical path
-    if (slice != 0) return;
-    // prediction for the next launch, per row kind: mean exponent offset, mean / spread of the
-    // nucleus boundary and mean list density over this launch's rows (fixed order: deterministic)
-    int phase = 0;
-    const int rows = P.B * (2 * gamma + 1);
-    for (int kind = 0; kind < 2; ++kind) {
-      R8 a;
-      a.v[0] = -INFINITY;
-      for (int i = 1; i < 8; ++i) a.v[i] = 0.0f;
-      for (int job = tid; job < rows; job += kT3) {
-        if (decode_job(job, gamma).is_target != kind) continue;
-        const RowRecord rc = load_record(&P.records[job]);
-        a.v[1] += 1.0f;
-        a.v[2] += rc.mxl;
-        if (rc.dens > 0.0f) {
-          a.v[3] += 1.0f;
-          a.v[4] += rc.xstar;
-          a.v[5] += rc.xstar * rc.xstar;
-          a.v[6] += rc.dens;
-        }
-      }
-      a = reduce3(a, &sc, phase);
-      if (tid == 0 && a.v[1] > 0.0f) {
-        StreamHint hn;
-        hn.m0 = a.v[2] / a.v[1];
-        hn.theta = 0.0f, hn.dens = 0.0f, hn.hw = 0.0f;
-        hn.valid = 1;
-        hn.pad[0] = hn.pad[1] = hn.pad[2] = 0;
-        if (a.v[3] > 0.0f) {
-          const float mean = a.v[4] / a.v[3];
-          const float var = fmaxf(a.v[5] / a.v[3] - mean * mean, 0.0f);
-          hn.theta = mean;
-          hn.dens = a.v[6] / a.v[3];
-          // four standard deviations, at least ~200 entries, at most ~1800 entries per side
-          hn.hw = fminf(fminf(fmaxf(4.0f * sqrtf(var), 200.0f / hn.dens), 1800.0f / hn.dens), 8.0f);
-        }
-        P.hints[kind] = hn;
-      }
-    }
-    return;
-  }
-  // every record of the sequence is read ONCE (one L2 round trip) and kept in shared memory
-  __shared__ RowRecord srec[2 * 64 + 1];
-  if (tid <= 2 * gamma) srec[tid] = load_record(&P.records[base + tid]);
-  bar3();
-  if (tid < gamma) {
-    const RowRecord rq = srec[2 * tid], rp = srec[2 * tid + 1];
-    const int accept = rj <= __fdiv_rn(rp.sel, rq.sel);  // raw IEEE division
-    sc.seq_acc[tid] = accept;
-    if (slice == 0) {
-      const long long o = (long long)b * gamma + tid;
-      P.accept_mask[o] = (unsigned char)accept;
-      P.sel_p[o] = rp.sel;
-      P.sel_q[o] = rq.sel;
-    }
-  }
-  bar3();
-  int n = 0;
-  while (n < gamma && sc.seq_acc[n] != 0) ++n;
-  const bool bonus = (n == gamma);
-  if (tid == 0) STAMP(P.stats, 14);
-  const RowRecord rp = srec[bonus ? 2 * gamma : 2 * n + 1];
-  const RowRecord rq = bonus ? rp : srec[2 * n];
-  const TIn* prow = split_row<TIn>(P, RowJob{b, n, 1});
-  const TIn* qrow = bonus ? prow : split_row<TIn>(P, RowJob{b, n, 0});
-  const float invZp = __frcp_rn(rp.Z), invZq = __frcp_rn(rq.Z);
-
-  float mass = 0.0f, bkey = -1.0f, bdv = -INFINITY;
-  int bidx = 0x7fffffff, bdi = 0x7fffffff;
-#pragma unroll
-  for (int u = 0; u < kSlice3 / (4 * kT3); ++u) {
-    const int i0 = s0 + u * 4 * kT3 + 4 * tid;
-    if (i0 < V) {
-      float4 xp = load4_scaled<TIn>(prow + i0, P.t_temp);
-      float4 xq = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (!bonus) xq = load4_scaled<TIn>(qrow + i0, P.d_temp);
-      float4 nv = nv4[u];
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const float x = f4c(xp, k);
-        float d = kept(rp, x, i0 + k) ? row_exp(x, rp.m0) * invZp : 0.0f;
-        if (!bonus) {
-          const float y = f4c(xq, k);
-          d -= kept(rq, y, i0 + k) ? row_exp(y, rq.m0) * invZq : 0.0f;
-        }
-        if (d > 0.0f) {
-          mass += d;
-          const float key = __fdividef(d, f4c(nv, k));
-          if (key > bkey || (key == bkey && i0 + k < bidx)) bkey = key, bidx = i0 + k;
-        }
-        const float dz = (d == d && fabsf(d) != INFINITY) ? d : 0.0f;
-        if (dz > bdv || (dz == bdv && i0 + k < bdi)) bdv = dz, bdi = i0 + k;
-      }
-    }
-  }
-  unsigned long long pk = bidx == 0x7fffffff ? 0ull
-                                            : ((unsigned long long)__float_as_uint(bkey) << 32) |
-                                                  (unsigned long long)(0xffffffffu - unsigned(bidx));
-  unsigned long long pb =
-      bdi == 0x7fffffff ? 0ull
-                        : ((unsigned long long)okey(bdv) << 32) | (unsigned long long)(0xffffffffu - unsigned(bdi));
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    mass += __shfl_xor_sync(0xffffffffu, mass, o);
-    const unsigned long long ok = __shfl_xor_sync(0xffffffffu, pk, o);
-    const unsigned long long ob = __shfl_xor_sync(0xffffffffu, pb, o);
-    pk = ok > pk ? ok : pk;
-    pb = ob > pb ? ob : pb;
-  }
-  if ((tid & 31) == 0) wmass[tid >> 5] = mass, wkey[tid >> 5] = pk, wbd[tid >> 5] = pb;
-  bar3();
-  if (tid == 0) STAMP(P.stats, 15);
-  if (tid == 0) {
-    for (int w = 1; w < kW3; ++w) {
-      mass += wmass[w];
-      pk = wkey[w] > pk ? wkey[w] : pk;
-      pb = wbd[w] > pb ? wbd[w] : pb;
-    }
-    if (mass > 0.0f) atomicAdd(&P.seq_mass[b], mass);
-    if (pk != 0ull) atomicMax(&P.seq_key[b], pk);
-    if (pb != 0ull) atomicMax(&P.seq_bd[b], pb);
-    __threadfence();
-    if (atomicAdd(&P.seq_arrive[b], 1) == int(gridDim.x) - 1) {
-      __threadfence();
-      const float m = atomicAdd(&P.seq_mass[b], 0.0f);
-      const unsigned long long k = atomicMax(&P.seq_key[b], 0ull);
-      const unsigned long long d = atomicMax(&P.seq_bd[b], 0ull);
-      const unsigned long long win = (m > 0.0f && k != 0ull) ? k : d;
-      long long tok = win == 0ull ? 0 : (long long)(0xffffffffu - unsigned(win & 0xffffffffull));
-      P.accepted_len[b] = n;
-      P.token[b] = tok;
-      P.all_accepted[b] = (unsigned char)(n == gamma);
-      P.seq_mass[b] = 0.0f;
-      P.seq_key[b] = 0ull;
-      P.seq_bd[b] = 0ull;
-      P.seq_arrive[b] = 0;
-    }
-    STAMP(P.stats, 23);
-  }
 }
 
 }  // namespace duodec

@@ -1,11 +1,10 @@
-// Launcher of the persistent row-stream verification kernel (see stream_kernel.cuh).
+// Launcher of the fused-verify fast paths: row-capture scan kernel (path 6, default) or row-pair scan
+// kernel (path 5), each followed by the sample kernel under programmatic dependent launch.
 #include <mutex>
 #include <utility>
 #include <vector>
 
 #include "../../include/duodec.h"
-#include "ring_kernel.cuh"
-#include "resident_kernel.cuh"
 #include "pair_kernel.cuh"
 #include "capture_kernel.cuh"
 #include "sample_kernel.cuh"
@@ -14,10 +13,6 @@
 namespace duodec {
 
 namespace {
-
-size_t stream_smem_bytes() {
-  return size_t(kSlots) * kSlotBytes + size_t(kColCap) * kCT * 8 + sizeof(StreamScratch) + 128;
-}
 
 // cudaFuncSetAttribute is per (kernel, device): remember the pairs already set up.
 cudaError_t ensure_stream_smem(const void* kernel, size_t bytes) {
@@ -69,13 +64,15 @@ cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t s
 
 }  // namespace
 
+constexpr size_t kCapSmemMax = 232448;  // the capture kernel's shared memory depends on V: opt in to the limit once
 constexpr int kMaxGrid = 320;   // blocks of a persistent scan kernel (two per SM): one scratch list each
-constexpr int kMaxSlices = 32;  // row_scan slices the workspace is sized for (V <= 262144)
 
+// hints | row records | per-sequence cells of the sliced sample mode | kept-entry lists of the target rows +
+// one scratch list per scan block
 size_t stream_workspace_bytes(int B, int gamma) {
   const size_t rows = size_t(B) * size_t(2 * gamma + 1);
-  return 4 * sizeof(StreamHint) + rows * sizeof(RowRecord) + rows * kMaxSlices * sizeof(RowPartial) + rows * 8 +
-         size_t(B) * 24 + (rows + 2 + kMaxGrid) * size_t(kListCap) * sizeof(ListEntry);
+  return 4 * sizeof(StreamHint) + rows * sizeof(RowRecord) + size_t(B) * 24 +
+         (size_t(B) * size_t(gamma + 1) + kMaxGrid) * size_t(kListCap) * sizeof(ListEntry);
 }
 
 bool stream_try_launch(const StreamCall& c, int* rc) {
@@ -88,13 +85,10 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
                   (size_t(c.d_ss) * elt) % 16 == 0 && al16(c.noise) && (c.noise_sb % 4) == 0;
   if (!ok) return false;
   const size_t rows = size_t(c.B) * size_t(2 * c.gamma + 1);
-  const bool resident = c.path == 4 && c.B <= 65535;
   const bool capture = c.path == 6 && c.B <= 65535 && c.Vt >= cap::kMinV &&
                        cap::cap_smem_bytes((c.Vt + kStageElems - 1) / kStageElems) <= 232448;
   const bool pairp = (c.path == 5 || (c.path == 6 && !capture)) && c.B <= 65535;
-  const bool ring = (c.path == 3 || (c.path == 1 && c.Vt > kMaxSlices * kSlice)) && c.B <= 65535;
-  const bool split = c.path == 1 && c.Vt <= kMaxSlices * kSlice && rows <= 65535 && c.B <= 65535;
-  if (ring || split || resident || pairp || capture) {
+  if (pairp || capture) {
     SplitParams Q;
     Q.draft = c.draft;
     Q.target = c.target;
@@ -105,7 +99,7 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
     Q.B = c.B;
     Q.gamma = c.gamma;
     Q.V = c.Vt;
-    Q.S = (c.Vt + kSlice - 1) / kSlice;
+    Q.S = 0;
     Q.tokens = reinterpret_cast<const long long*>(c.tokens);
     Q.tok_sb = c.tok_sb;
     Q.r = c.r;
@@ -131,12 +125,9 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
     w += 4 * sizeof(StreamHint);
     Q.records = reinterpret_cast<RowRecord*>(w);
     w += rows * sizeof(RowRecord);
-    Q.partials = reinterpret_cast<RowPartial*>(w);
-    w += rows * kMaxSlices * sizeof(RowPartial);
-    Q.row_count = reinterpret_cast<int*>(w);
-    w += rows * 4;
-    Q.row_arrive = reinterpret_cast<int*>(w);
-    w += rows * 4;
+    Q.partials = nullptr;
+    Q.row_count = nullptr;
+    Q.row_arrive = nullptr;
     Q.seq_key = reinterpret_cast<unsigned long long*>(w);
     w += size_t(c.B) * 8;
     Q.seq_bd = reinterpret_cast<unsigned long long*>(w);
@@ -149,7 +140,8 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
     Q.stats = c.stats;
     Q.cap_rank = 0;
     Q.compact_hint = 0;
-    const dim3 g1(unsigned(Q.S), unsigned(rows)), g2(unsigned((c.Vt + kSlice3 - 1) / kSlice3), unsigned(c.B) + 1u);  // + the block row that aggregates the hints
+    Q.row0_rule = c.row0_rule;
+    const dim3 g2(unsigned((c.Vt + kSlice3 - 1) / kSlice3), unsigned(c.B) + 1u);  // + the block row that aggregates the hints
     if (capture) {
       const size_t smem = cap::cap_smem_bytes((c.Vt + kStageElems - 1) / kStageElems);
       const int sms = stream_sm_count();
@@ -157,10 +149,10 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
       const int npairs = int((rows + 1) / 2);
       int grid = npairs < per_sm * sms ? npairs : per_sm * sms;
       if (grid > kMaxGrid) grid = kMaxGrid;
-      // capture cut: the top f of a row by count, f = min(1/12, 2667 / V); a thread's 16 sample entries
+      // capture cut: the top f of a row by count, f = min(1/11, 2667 / V); a thread's 16 sample entries
       // all lie below the cut with probability (1 - f)^16, which is the rank among the 32 sorted maxima
       double f = 2667.0 / double(c.Vt);
-      if (f > 1.0 / 12.0) f = 1.0 / 12.0;
+      if (f > 1.0 / 11.0) f = 1.0 / 11.0;
       double pbelow = 1.0;
       for (int i = 0; i < 16; ++i) pbelow *= 1.0 - f;
       int rank = int(32.0 * pbelow);
@@ -170,14 +162,14 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
       cudaError_t e;
       const size_t smem2 = sample_smem_bytes();
       if (c.dtype == DUODEC_F32) {
-        e = ensure_stream_smem(reinterpret_cast<const void*>(cap::row_capture_kernel<float>), smem);
+        e = ensure_stream_smem(reinterpret_cast<const void*>(cap::row_capture_kernel<float>), kCapSmemMax);
         if (e == cudaSuccess) e = ensure_stream_smem(reinterpret_cast<const void*>(seq_sample_tma_kernel<float>), smem2);
         if (e == cudaSuccess && (c.phases & 1))
           e = launch_pdl(cap::row_capture_kernel<float>, dim3(grid), dim3(cap::kPT), smem, c.stream, Q);
         if (e == cudaSuccess && (c.phases & 2))
           e = launch_pdl(seq_sample_tma_kernel<float>, g2c, dim3(kT3), smem2, c.stream, Q);
       } else {
-        e = ensure_stream_smem(reinterpret_cast<const void*>(cap::row_capture_kernel<__nv_bfloat16>), smem);
+        e = ensure_stream_smem(reinterpret_cast<const void*>(cap::row_capture_kernel<__nv_bfloat16>), kCapSmemMax);
         if (e == cudaSuccess)
           e = ensure_stream_smem(reinterpret_cast<const void*>(seq_sample_tma_kernel<__nv_bfloat16>), smem2);
         if (e == cudaSuccess && (c.phases & 1))
@@ -213,106 +205,8 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
       *rc = int(e != cudaSuccess ? e : cudaGetLastError());
       return true;
     }
-    if (resident) {
-      const size_t smem = resident::ring_smem_bytes();
-      const int sms = stream_sm_count();
-      const int grid = int(rows) < sms ? int(rows) : sms;  // one block per SM
-      cudaError_t e;
-      if (c.dtype == DUODEC_F32) {
-        e = ensure_stream_smem(reinterpret_cast<const void*>(resident::row_resident_kernel<float>), smem);
-        if (e == cudaSuccess) {
-          if (c.phases & 1) resident::row_resident_kernel<float><<<grid, resident::kRT, smem, c.stream>>>(Q);
-          if (c.phases & 2) launch_pdl(seq_sample_kernel<float>, g2, dim3(kT3), 0, c.stream, Q);
-        }
-      } else {
-        e = ensure_stream_smem(reinterpret_cast<const void*>(resident::row_resident_kernel<__nv_bfloat16>), smem);
-        if (e == cudaSuccess) {
-          if (c.phases & 1) resident::row_resident_kernel<__nv_bfloat16><<<grid, resident::kRT, smem, c.stream>>>(Q);
-          if (c.phases & 2) launch_pdl(seq_sample_kernel<__nv_bfloat16>, g2, dim3(kT3), 0, c.stream, Q);
-        }
-      }
-      *rc = int(e != cudaSuccess ? e : cudaGetLastError());
-      return true;
-    }
-    if (ring) {
-      const size_t smem = ring_smem_bytes();
-      const int sms = stream_sm_count();
-      const int grid = int(rows) < 2 * sms ? int(rows) : 2 * sms;  // two blocks per SM
-      cudaError_t e;
-      if (c.dtype == DUODEC_F32) {
-        e = ensure_stream_smem(reinterpret_cast<const void*>(row_ring_kernel<float>), smem);
-        if (e == cudaSuccess) {
-          if (c.phases & 1) row_ring_kernel<float><<<grid, kRT, smem, c.stream>>>(Q);
-          if (c.phases & 2) launch_pdl(seq_sample_kernel<float>, g2, dim3(kT3), 0, c.stream, Q);
-        }
-      } else {
-        e = ensure_stream_smem(reinterpret_cast<const void*>(row_ring_kernel<__nv_bfloat16>), smem);
-        if (e == cudaSuccess) {
-          if (c.phases & 1) row_ring_kernel<__nv_bfloat16><<<grid, kRT, smem, c.stream>>>(Q);
-          if (c.phases & 2) launch_pdl(seq_sample_kernel<__nv_bfloat16>, g2, dim3(kT3), 0, c.stream, Q);
-        }
-      }
-      *rc = int(e != cudaSuccess ? e : cudaGetLastError());
-      return true;
-    }
-    if (c.dtype == DUODEC_F32) {
-      if (c.phases & 1) row_scan_kernel<float><<<g1, kT3, 0, c.stream>>>(Q);
-      if (c.phases & 2) launch_pdl(seq_sample_kernel<float>, g2, dim3(kT3), 0, c.stream, Q);
-    } else {
-      if (c.phases & 1) row_scan_kernel<__nv_bfloat16><<<g1, kT3, 0, c.stream>>>(Q);
-      if (c.phases & 2) launch_pdl(seq_sample_kernel<__nv_bfloat16>, g2, dim3(kT3), 0, c.stream, Q);
-    }
-    *rc = int(cudaGetLastError());
-    return true;
   }
-  StreamParams S;
-  S.draft = c.draft;
-  S.target = c.target;
-  S.d_sb = c.d_sb;
-  S.d_ss = c.d_ss;
-  S.t_sb = c.t_sb;
-  S.t_ss = c.t_ss;
-  S.B = c.B;
-  S.gamma = c.gamma;
-  S.V = c.Vt;
-  S.tokens = reinterpret_cast<const long long*>(c.tokens);
-  S.tok_sb = c.tok_sb;
-  S.r = c.r;
-  S.r_sb = c.r_sb;
-  S.noise = c.noise;
-  S.noise_sb = c.noise_sb;
-  S.t_temp = c.temperature;
-  S.t_top_p = c.top_p;
-  S.d_temp = c.draft_temperature;
-  S.d_top_p = c.draft_top_p;
-  S.accept_mask = c.accept_mask;
-  S.sel_p = c.sel_target_p;
-  S.sel_q = c.sel_draft_p;
-  S.accepted_len = reinterpret_cast<long long*>(c.accepted_len);
-  S.token = reinterpret_cast<long long*>(c.token);
-  S.all_accepted = c.all_accepted;
-  char* w = reinterpret_cast<char*>(c.workspace);
-  S.counters = reinterpret_cast<int*>(w);
-  w += size_t(c.B) * 8;
-  w += size_t(c.B) * size_t(c.gamma + 1) * 8;  // (the general kernel's position tokens)
-  S.hints = reinterpret_cast<StreamHint*>(w);
-  w += 4 * sizeof(StreamHint);  // (this launch's and the next launch's predictions of the split kernels)
-  S.records = reinterpret_cast<RowRecord*>(w);
-  S.stats = c.stats;
-  const size_t smem = stream_smem_bytes();
-  const int njobs = c.B * (2 * c.gamma + 1);
-  const int sms = stream_sm_count();
-  const int grid = njobs < 2 * sms ? njobs : 2 * sms;
-  cudaError_t e;
-  if (c.dtype == DUODEC_F32) {
-    e = ensure_stream_smem(reinterpret_cast<const void*>(verify_stream_kernel<float>), smem);
-    if (e == cudaSuccess) verify_stream_kernel<float><<<grid, kST, smem, c.stream>>>(S);
-  } else {
-    e = ensure_stream_smem(reinterpret_cast<const void*>(verify_stream_kernel<__nv_bfloat16>), smem);
-    if (e == cudaSuccess) verify_stream_kernel<__nv_bfloat16><<<grid, kST, smem, c.stream>>>(S);
-  }
-  *rc = int(e != cudaSuccess ? e : cudaGetLastError());
-  return true;
+  return false;
 }
 
 }  // namespace duodec

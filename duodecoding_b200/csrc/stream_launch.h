@@ -35,7 +35,8 @@ struct StreamCall {  // the arguments of duodec_verify_fused, verbatim
   void* workspace;
   int* stats;
   int phases;  // bit 0: scan kernel, bit 1: sample kernel (3 = both; measurement hook)
-  int path;  // 1: split kernels (row_scan + seq_sample), 2: persistent row-stream kernel
+  int path;  // 6: row-capture scan kernel (default), 5: row-pair scan kernel
+  int row0_rule;  // sequence 0's accepted count positions every sequence
   cudaStream_t stream;
 };
 

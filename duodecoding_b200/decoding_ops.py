@@ -8,6 +8,17 @@ keep working like they do on the reference.
 
 ``KVCacheModel`` below means anything with the reference's cache surface: ``prob_history``,
 ``vocab_size``, ``device`` and ``rollback(end_pos)`` (src/model_gpu.py).
+
+Fused route.  When both caches are :class:`duodecoding_b200.model_gpu.KVCacheModel` objects (they
+keep LOGIT rows), no ``draft_probs_override`` is given and nobody has patched this module's
+``sample`` / ``max_fn`` / ``sample_reject_token`` / ``sample_accept_token``, then
+``resolve_stage_verification`` and the ``verify_draft_sequence`` -> ``finalize_verification`` pair
+run ONE ``duodec_verify_fused`` call on the logits rows (softmax + filter of the gamma draft rows and
+gamma+1 target rows, accept test, leading run, residual / bonus draw) instead of materialising
+probability rows and walking them with four operators.  The reference's batch rule is kept: the
+accepted count of sequence 0 positions every sequence (``row0_rule``).  Anything else - overrides,
+top-k transfer compression, patched samplers, comm accounting that needs the draft rows, plain
+tensors as histories - takes the probability-space operators below, exactly as before.
 """
 
 from __future__ import annotations
@@ -104,6 +115,50 @@ def _unpatched() -> bool:
     return g["sample"] is _ORIG_SAMPLE and g["max_fn"] is _ORIG_MAX_FN
 
 
+def _fused_ready(draft_cache, target_cache, draft_probs_override) -> bool:
+    """Both caches keep logit rows the fused kernel can read, and nothing asks for the probability flow."""
+    g = globals()
+    if draft_probs_override is not None or not _unpatched():
+        return False
+    if g["sample_reject_token"] is not _ORIG_REJECT or g["sample_accept_token"] is not _ORIG_ACCEPT:
+        return False
+    if not (hasattr(draft_cache, "logits_rows") and hasattr(target_cache, "logits_rows")):
+        return False
+    if draft_cache.vocab_size != target_cache.vocab_size:
+        return False
+    dT, tT = float(draft_cache._temperature), float(target_cache._temperature)
+    return (dT == 0.0) == (tT == 0.0)
+
+
+def _fused_verify(draft_cache, target_cache, x: torch.Tensor, prefix_len: int, gamma: int,
+                  r: Optional[torch.Tensor] = None, noise: Optional[torch.Tensor] = None):
+    """One duodec_verify_fused call over the logit rows [P-1, P-1+g') of the draft and [P-1, P-1+g'] of the
+    target.  Returns (accepted_count, n, token [B,1], g') or None when the rows are not there (then the
+    caller takes the probability-space flow)."""
+    lo = prefix_len - 1
+    q_len, p_len = draft_cache._current_seq_len, target_cache._current_seq_len
+    steps = min(prefix_len + gamma - 1, q_len, p_len) - lo
+    if gamma <= 0 or steps <= 0 or p_len != lo + steps + 1 or x.shape[1] < prefix_len + steps:
+        return None  # the bonus row must be the target's newest row (reference: prob_history[:, -1])
+    dl, tl = draft_cache.logits_rows(lo, lo + steps), target_cache.logits_rows(lo, lo + steps + 1)
+    if dl is None or tl is None or not dl.is_cuda or dl.device != tl.device or dl.dtype != tl.dtype:
+        return None
+    if dl.shape[-1] != tl.shape[-1] or dl.shape[0] != tl.shape[0]:
+        return None
+    B, V, dev = dl.shape[0], dl.shape[-1], dl.device
+    tokens = x[:, prefix_len:prefix_len + steps].to(dev)
+    if r is None:
+        r = torch.rand((B, steps), device=dev)
+    if noise is None:
+        noise = torch.empty((B, V), dtype=torch.float32, device=dev).exponential_(1.0)
+    out = ops.verify_fused(dl, tl, tokens, r, noise, float(target_cache._temperature),
+                           int(target_cache._top_k or 0), float(target_cache._top_p or 0.0),
+                           float(draft_cache._temperature), int(draft_cache._top_k or 0),
+                           float(draft_cache._top_p or 0.0), row0_rule=True)
+    accepted = int(out["accepted_len"][0].item())  # the one device->host read of the step (reference: .item())
+    return accepted, int(prefix_len + accepted - 1), out["token"].unsqueeze(1), steps
+
+
 def sample_reject_token(target_probs: torch.Tensor, draft_probs: torch.Tensor,
                         output_device: Optional[torch.device] = None) -> torch.Tensor:
     """src/decoding_ops.py:190-206: sample(max_fn(p - q)) -> [B, 1] int64.  One fused kernel
@@ -128,6 +183,9 @@ def sample_accept_token(target_next_probs: torch.Tensor,
     return token
 
 
+_ORIG_REJECT, _ORIG_ACCEPT = sample_reject_token, sample_accept_token
+
+
 def verify_draft_sequence_result(draft_model_cache, target_model_cache, x: torch.Tensor, prefix_len: int, gamma: int,
                                  *, draft_probs_override: Optional[torch.Tensor] = None,
                                  r: Optional[torch.Tensor] = None) -> Tuple[VerificationInputs, AcceptanceResult]:
@@ -136,6 +194,9 @@ def verify_draft_sequence_result(draft_model_cache, target_model_cache, x: torch
                                      x=x, prefix_len=prefix_len, gamma=gamma,
                                      draft_probs_override=draft_probs_override)
     return vi, compute_acceptance_result(vi, r=r)
+
+
+_ORIG_VDSR = verify_draft_sequence_result
 
 
 def verify_draft_sequence(draft_model_cache, target_model_cache, x: torch.Tensor, prefix_len: int, gamma: int,
@@ -147,9 +208,24 @@ def verify_draft_sequence(draft_model_cache, target_model_cache, x: torch.Tensor
     drives it: ``transfer(tokens, q(tokens), link)`` before the test in "batch_before" mode,
     ``send_reject_message(link)`` after a rejection, one ``transfer(token, q_row, link)`` per
     transmitted position in "serial" mode."""
+    needs_rows = comm_simulator is not None and transfer_mode in ("batch_before", "serial")
+    if not needs_rows and _fused_ready(draft_model_cache, target_model_cache, draft_probs_override):
+        fv = _fused_verify(draft_model_cache, target_model_cache, x, prefix_len, gamma)
+        if fv is not None:
+            accepted, n, token, steps = fv
+            if accepted < steps and send_reject_message and comm_simulator:
+                comm_simulator.send_reject_message(comm_link)
+            if decoding_metrics is not None:
+                decoding_metrics["draft_generated_tokens"] += gamma
+                decoding_metrics["draft_accepted_tokens"] += int(n - prefix_len + 1)
+            if steps == gamma:  # finalize_verification(n) picks the token up instead of drawing again
+                target_model_cache._fused_token = (n, prefix_len, gamma, token)
+            return accepted, n
     vi = prepare_verification_inputs(draft_model_cache=draft_model_cache, target_model_cache=target_model_cache,
                                      x=x, prefix_len=prefix_len, gamma=gamma,
                                      draft_probs_override=draft_probs_override)
+    if vi.actual_gamma <= 0:  # src/decoding_ops.py: nothing to verify, no traffic, no metrics
+        return 0, prefix_len - 1
     if transfer_mode == "batch_before" and comm_simulator is not None:
         comm_simulator.transfer(vi.draft_tokens,
                                 torch.gather(vi.draft_probs_batch, 2, vi.draft_token_indices).squeeze(-1), comm_link)
@@ -173,6 +249,16 @@ def resolve_stage_verification(proposer_cache, verifier_cache, x: torch.Tensor, 
                                draft_probs_override: Optional[torch.Tensor] = None
                                ) -> Tuple[int, int, torch.Tensor, bool]:
     """src/decoding_ops.py:353-397: verify -> plan -> resample (vocab-limited) or bonus -> rollback."""
+    if globals()["verify_draft_sequence_result"] is _ORIG_VDSR and _fused_ready(proposer_cache, verifier_cache,
+                                                                                draft_probs_override):
+        fv = _fused_verify(proposer_cache, verifier_cache, x, prefix_len, gamma)
+        if fv is not None:
+            accepted, n, token, steps = fv
+            plan = build_rollback_plan(prefix_len, steps, n)
+            apply_rollback(proposer_cache, verifier_cache, plan)
+            if output_device is not None and token.device != output_device:
+                token = token.to(output_device)
+            return accepted, n, token, plan.all_accepted
     vocab_limit = min(proposer_cache.vocab_size, verifier_cache.vocab_size)
     vi, res = verify_draft_sequence_result(draft_model_cache=proposer_cache, target_model_cache=verifier_cache, x=x,
                                            prefix_len=prefix_len, gamma=gamma,
@@ -195,6 +281,13 @@ def finalize_verification(approx_model_cache, target_model_cache, x: torch.Tenso
     bonus at row -1, rollback the target cache, return cat(x[:, :n+1], t)."""
     prefix = x[:, :n + 1]
     plan = build_rollback_plan(prefix_len, gamma, n)
+    pend = getattr(target_model_cache, "_fused_token", None)
+    if pend is not None and draft_probs_override is None and pend[:3] == (n, prefix_len, gamma) and \
+            _fused_ready(approx_model_cache, target_model_cache, None):
+        target_model_cache._fused_token = None  # the token verify_draft_sequence drew with this very n
+        approx_model_cache.rollback(plan.draft_end_pos)
+        target_model_cache.rollback(plan.target_end_pos_accept if plan.all_accepted else plan.target_end_pos_reject)
+        return torch.cat((prefix, pend[3].to(prefix.device)), dim=1)
     approx_model_cache.rollback(plan.draft_end_pos)
     q_hist = draft_probs_override if draft_probs_override is not None else approx_model_cache.prob_history
     p_hist = target_model_cache.prob_history

@@ -7,6 +7,7 @@ CPU tensors - there is no fallback path.
 
 from __future__ import annotations
 
+from collections import OrderedDict
 from typing import Dict, Optional, Tuple
 
 import torch
@@ -15,7 +16,10 @@ from . import _lib
 from ._lib import BF16, F32, check, lib
 
 _DTYPES = {torch.float32: F32, torch.bfloat16: BF16}
-_WORKSPACES: Dict[Tuple[int, int, int], torch.Tensor] = {}
+# verify workspaces: one per (device, stream, B, gamma) - a workspace holds the records of ONE launch in
+# flight, so launches on different streams must not share it; least recently used entries are dropped
+_WORKSPACES: "OrderedDict[Tuple[int, int, int, int], torch.Tensor]" = OrderedDict()
+_WORKSPACE_LIMIT_BYTES = 1 << 30
 
 
 def _need_cuda(*tensors: torch.Tensor) -> None:
@@ -55,21 +59,27 @@ def set_team_size(team: int) -> None:
     lib.duodec_set_team_size(int(team))
 
 
-FAST_PATH = 6  # row-capture scan kernel + sample kernel (compact lists)
+FAST_PATH = 6  # row-capture scan kernel + sample kernel (compact kept-entry lists)
+_PATH = 0       # DUODEC_VERIFY_PATH: 0 automatic, 1 general team kernel, 5 row-pair kernel, 6 row capture
+_PHASES = 0     # DUODEC_VERIFY_PHASES: 0 / 3 both kernels, 1 scan only, 2 sample only
+ROW0_RULE = 1   # DUODEC_VERIFY_ROW0_RULE
 
 
 def set_stream_path(path) -> None:
-    """Test hook: device path of verify_fused.  True: the default fast path (5, row-pair scan kernel);
-    False / 0: the general team kernel; 1: sliced scan kernel; 2: first-generation persistent kernel;
-    3: row-ring scan kernel; 4: resident-row scan kernel (experimental)."""
+    """Test hook: device path of the following verify_fused calls.  True: automatic (the row-capture fast
+    path when the call qualifies); False / 0: the general team kernel; 5: row-pair scan kernel; 6: row
+    capture.  The choice travels in the call's ``flags`` argument - the library keeps no path state."""
+    global _PATH
     if isinstance(path, bool):
-        path = FAST_PATH if path else 0
-    lib.duodec_set_stream_path(int(path))
+        _PATH = 0 if path else 1
+    else:
+        _PATH = 1 if int(path) == 0 else int(path)
 
 
 def set_phase_mask(mask: int) -> None:
     """Measurement hook: 1 = scan kernel only, 2 = sample kernel only, 3 = both (default)."""
-    lib.duodec_set_phase_mask(int(mask))
+    global _PHASES
+    _PHASES = int(mask) & 3
 
 
 def set_stats_buffer(buf: Optional[torch.Tensor]) -> None:
@@ -94,15 +104,31 @@ def norm_logits(
 ) -> torch.Tensor:
     """softmax(top_k_top_p_filter(logits / T)), or the argmax one-hot at T == 0."""
     _need_cuda(logits, out)
-    x = _rows(logits)
-    rows, V = x.shape
+    V = logits.shape[-1]
     if out is None:
         if out_dtype is None:
             out_dtype = torch.float32 if temperature == 0 else logits.dtype
         out = torch.empty(logits.shape, dtype=out_dtype, device=logits.device)
+    if logits.dim() == 3 and out.dim() == 3 and logits.stride(-1) == 1 and out.stride(-1) == 1 and \
+            logits.shape == out.shape:
+        # [B, S, V] views with their own batch / row strides (history buffers): one launch, no copy
+        Bn, Sn = logits.shape[0], logits.shape[1]
+        if Bn and Sn:
+            with torch.cuda.device(logits.device):
+                check(
+                    lib.duodec_norm_logits_batched(
+                        logits.data_ptr(), _code(logits), logits.stride(0), logits.stride(1), out.data_ptr(),
+                        _code(out), out.stride(0), out.stride(1), Bn, Sn, V, float(temperature), int(top_k),
+                        float(top_p), _stream(),
+                    ),
+                    "duodec_norm_logits_batched",
+                )
+        return out
+    x = _rows(logits)
+    rows = x.shape[0]
     o = out.reshape(-1, V) if out.dim() != 2 else out
-    if o.numel() and o.stride(-1) != 1:
-        raise ValueError("out must have unit stride along the vocabulary")
+    if o.numel() and (o.stride(-1) != 1 or o.data_ptr() != out.data_ptr()):
+        raise ValueError("out must have unit stride along the vocabulary and rows that flatten without a copy")
     if rows:
         with torch.cuda.device(logits.device):
             check(
@@ -116,12 +142,21 @@ def norm_logits(
 
 
 def _workspace(device: torch.device, B: int, gamma: int) -> torch.Tensor:
-    key = (device.index if device.index is not None else torch.cuda.current_device(), B, gamma)
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    stream = torch.cuda.current_stream(device)
+    key = (idx, stream.cuda_stream, B, gamma)
     ws = _WORKSPACES.get(key)
-    if ws is None:
-        nbytes = int(lib.duodec_verify_workspace_bytes(B, gamma))
-        ws = torch.zeros(nbytes, dtype=torch.uint8, device=device)
-        _WORKSPACES[key] = ws
+    if ws is not None:
+        _WORKSPACES.move_to_end(key)
+        return ws
+    nbytes = int(lib.duodec_verify_workspace_bytes(B, gamma))
+    with torch.cuda.stream(stream):
+        ws = torch.zeros(nbytes, dtype=torch.uint8, device=device)  # zero-filled on the stream that will use it
+    _WORKSPACES[key] = ws
+    total = sum(int(t.numel()) for t in _WORKSPACES.values())
+    while total > _WORKSPACE_LIMIT_BYTES and len(_WORKSPACES) > 1:
+        _, old = _WORKSPACES.popitem(last=False)
+        total -= int(old.numel())
     return ws
 
 
@@ -138,8 +173,10 @@ def verify_fused(
     draft_top_k: Optional[int] = None,
     draft_top_p: Optional[float] = None,
     out: Optional[Dict[str, torch.Tensor]] = None,
+    row0_rule: bool = False,
 ) -> Dict[str, torch.Tensor]:
-    """One fused verification step on logits for every sequence of the batch."""
+    """One fused verification step on logits for every sequence of the batch.  ``row0_rule``: the
+    reference's batch rule - sequence 0's accepted count positions every sequence (fast paths only)."""
     _need_cuda(draft_logits, target_logits, tokens, r, noise)
     B, gamma = tokens.shape
     dev = target_logits.device
@@ -178,6 +215,7 @@ def verify_fused(
                 tokens.data_ptr(), tokens.stride(0) if gamma else 0, r.data_ptr(), r.stride(0) if gamma else 0,
                 noise.data_ptr(), noise.stride(0),
                 float(temperature), int(top_k), float(top_p), float(dT), int(dk), float(dp),
+                (ROW0_RULE if row0_rule else 0) | ((_PATH & 15) << 4) | ((_PHASES & 3) << 8),
                 out["accept_mask"].data_ptr(), out["selected_target_p"].data_ptr(),
                 out["selected_draft_p"].data_ptr(), out["accepted_len"].data_ptr(), out["token"].data_ptr(),
                 out["all_accepted"].data_ptr(), ws.data_ptr(), ws.numel(), _stream(),

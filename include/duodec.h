@@ -16,7 +16,12 @@
  *   - dtype codes: DUODEC_F32 = 0, DUODEC_BF16 = 1;
  *   - return value: 0 on success, a negative DUODEC_E* code for a rejected
  *     argument, or a positive cudaError_t from the launch;
- *   - re-entrant: no global state besides one-time kernel attribute setup.
+ *   - re-entrant: a call depends on its arguments only.  Process-global state is limited to one-time
+ *     kernel attribute setup and the two tuning / test hooks duodec_set_team_size and
+ *     duodec_set_stats_buffer below (not meant for concurrent use).
+ *   - a verify workspace holds the records and per-sequence cells of ONE launch in flight: do not
+ *     share it between launches that may overlap (different streams or threads); launches on one
+ *     stream may reuse it.
  */
 #ifndef DUODEC_H_
 #define DUODEC_H_
@@ -46,20 +51,8 @@ int duodec_team_size(int V, int rows_resident);
 /* Override the team-size heuristic (0 = automatic).  Tuning / test hook. */
 void duodec_set_team_size(int team);
 
-/* Device path of duodec_verify_fused for calls that qualify (equal vocabularies, 16-byte
- * aligned rows, no top-k, T > 0): 5 (default) row-pair scan kernel + sliced sample kernel,
- * 3 row-ring scan kernel, 4 resident-row scan kernel, 1 sliced scan kernel, 2 first-generation
- * persistent kernel;
- * 0 forces the general team kernel, which every other call takes anyway (test hook). */
-void duodec_set_stream_path(int enabled);
-
-/* Measurement hook for the fast paths: bit 0 launches the scan kernel, bit 1 the sample kernel
- * (default 3 = both).  bench.py uses 1 to time the dominant kernel alone for the roofline. */
-void duodec_set_phase_mask(int mask);
-
-/* Tuning hook: device int[32] that the row-stream kernel increments (0..15: rows by number of
- * nucleus search passes, 16: rows finished by the candidate ordering, 17: rows finished by the
- * bisection path, 18: candidates ordered).  NULL (default) disables it. */
+/* Tuning hook: device int[32] that the scan kernels increment (16: rows finished by the fast select,
+ * 17: rows handed to the general search, 19: general searches run).  NULL (default) disables it. */
 void duodec_set_stats_buffer(int* device_counters);
 
 /* ---- logits -> probabilities --------------------------------------------
@@ -71,6 +64,11 @@ void duodec_set_stats_buffer(int* device_counters);
 int duodec_norm_logits(const void* logits, int in_dtype, int64_t in_row_stride, void* out, int out_dtype,
                        int64_t out_row_stride, int rows, int V, float temperature, int top_k, float top_p,
                        void* stream);
+/* The same over [batch, inner, V] views with two row strides each: what KVCacheModel's history
+ * buffers are ([B, max_len, V] rows [start, start+S), src/model_gpu.py:186-203) - one launch. */
+int duodec_norm_logits_batched(const void* logits, int in_dtype, int64_t in_batch_stride, int64_t in_row_stride,
+                               void* out, int out_dtype, int64_t out_batch_stride, int64_t out_row_stride, int batch,
+                               int inner, int V, float temperature, int top_k, float top_p, void* stream);
 
 /* ---- fused verification on logits -----------------------------------------
  * One call = norm_logits on the gamma draft rows and gamma+1 target rows
@@ -89,17 +87,29 @@ int duodec_norm_logits(const void* logits, int in_dtype, int64_t in_row_stride, 
  * outputs
  *   accept_mask [B,gamma] uint8, sel_target_p / sel_draft_p [B,gamma] float32,
  *   accepted_len [B] int64, token [B] int64, all_accepted [B] uint8.
+ * flags: DUODEC_VERIFY_ROW0_RULE - the reference's batch rule (src/decoding_ops.py:144-147): the
+ *   accepted count of sequence 0 positions EVERY sequence (accepted_len[b] = accepted_len[0], every
+ *   token drawn at that position); without it every sequence is verified on its own count.  Only
+ *   the fast paths implement it (equal vocabularies, no top-k, T > 0, 16-byte aligned rows):
+ *   DUODEC_EINVAL otherwise when B > 1.
+ *   DUODEC_VERIFY_PATH(p) - test hook: 0 automatic (row-capture scan kernel when the call qualifies,
+ *   else the general team kernel), 1 general team kernel, 5 row-pair scan kernel, 6 row capture.
+ *   DUODEC_VERIFY_PHASES(m) - measurement hook: 1 scan kernel only, 2 sample kernel only, 0 / 3 both.
  * workspace: duodec_verify_workspace_bytes(B,gamma) bytes, 16-byte aligned, zero-filled ONCE by
- *   the caller before first use (the kernel restores it to zero). */
+ *   the caller before first use (the kernels restore what they need to zero).  One launch in flight
+ *   per workspace. */
+#define DUODEC_VERIFY_ROW0_RULE 1
+#define DUODEC_VERIFY_PATH(p) (((p) & 15) << 4)
+#define DUODEC_VERIFY_PHASES(m) (((m) & 3) << 8)
 size_t duodec_verify_workspace_bytes(int B, int gamma);
 
 int duodec_verify_fused(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss, int64_t t_sb,
                         int64_t t_ss, int B, int gamma, int Vd, int Vt, const int64_t* tokens, int64_t tok_sb,
                         const float* r, int64_t r_sb, const float* noise, int64_t noise_sb, float temperature,
                         int top_k, float top_p, float draft_temperature, int draft_top_k, float draft_top_p,
-                        uint8_t* accept_mask, float* sel_target_p, float* sel_draft_p, int64_t* accepted_len,
-                        int64_t* token, uint8_t* all_accepted, void* workspace, size_t workspace_bytes,
-                        void* stream);
+                        int flags, uint8_t* accept_mask, float* sel_target_p, float* sel_draft_p,
+                        int64_t* accepted_len, int64_t* token, uint8_t* all_accepted, void* workspace,
+                        size_t workspace_bytes, void* stream);
 
 /* ---- probability-space operators -----------------------------------------
  * Accept test on stored probability histories; replaces the tensor part of
