@@ -203,7 +203,7 @@ int duodec_verify_fused(const void* draft, const void* target, int dtype, int64_
     c.draft_temperature = draft_temperature, c.draft_top_k = draft_top_k, c.draft_top_p = draft_top_p;
     c.accept_mask = accept_mask, c.sel_target_p = sel_target_p, c.sel_draft_p = sel_draft_p;
     c.accepted_len = accepted_len, c.token = token, c.all_accepted = all_accepted;
-    c.workspace = workspace, c.stats = g_stats.load(), c.path = path == 0 ? 6 : path, c.phases = phases == 0 ? 3 : phases;
+    c.workspace = workspace, c.stats = g_stats.load(), c.path = path == 0 ? 5 : path, c.phases = phases == 0 ? 3 : phases;
     c.row0_rule = row0 ? 1 : 0, c.stream = st;
     int rc = 0;
     if (stream_try_launch(c, &rc)) return rc;

@@ -19,9 +19,9 @@
 //            top_p * Z; the mass above it and the <= 128 entries inside it are then handled in exact
 //            38-bit fixed-point arithmetic and ordered like the reference's sort (scaled logit
 //            descending, lowest index first) - same arithmetic and answer as the row-pair kernel.
-//   emit     a target row also writes its kept entries (x, index) to the row's list in the workspace:
-//            the sample kernel draws the sequence's token from that list instead of re-reading
-//            three V-sized rows.
+//   dump     a target row also leaves its list columns and bit map in the workspace (two TMA bulk
+//            stores issued by one thread while the select runs): the sample kernel draws the sequence's
+//            token from the kept entries of that dump instead of re-reading three V-sized rows.
 //
 // A thread whose column is full appends to a small overflow pool of its half (atomic append, rare).
 // A row whose nucleus is not inside the captured set (flat rows, a full overflow pool, overflowing
@@ -42,7 +42,13 @@ constexpr int kHW = kHT / 32;
 constexpr int kPT = kT3 + 64;       // 256 workers + one producer warp per half
 constexpr int kCStages = 2;         // 8 KB stages per half
 constexpr int kSlots = 40;          // list slots per worker thread (the last 4 are slack: the column is re-checked per float4)
-constexpr int kOvf = 512;           // entries of a half's overflow pool: what does not fit a thread's column (x, index)
+constexpr int kOvf = 192;           // entries of a half's overflow pool: what does not fit a thread's column (x, index)
+// Dump of a closed target row in its 32 KB workspace slot (read by the sample kernel): the list columns
+// [kSlots][128] float, the bit map [nchunk][128] u16, the pool (count, entries).
+constexpr int kDumpBitmap = kSlots * kHT * 4;          // 20480
+constexpr int kDumpPool = 30720;                       // int count, then entries at +16
+constexpr int kDumpMaxChunks = (kDumpPool - kDumpBitmap) / (kHT * 2);  // 40 stages: V <= 81920
+static_assert(kDumpPool + 16 + kOvf * 8 <= kListCap * 8, "dump must fit the row's workspace slot");
 constexpr int kLB = 16;             // value buckets per select level
 constexpr int kMaxLevels = 5;
 constexpr int kSamplePieces = 8;    // sample stage: 8 pieces of 256 entries
@@ -67,7 +73,6 @@ struct __align__(16) CapScratch {  // one per half
   int cand_i[kHT];
   unsigned long long wgb[kHW];
   int wcnt[kHW];
-  int wpre[kHW];  // inclusive warp totals of the kept-for-sure counts (emission offsets)
   unsigned long long gb_new;
   int ncand, res_ok, res_i, nemit;
   float res_x;
@@ -104,6 +109,14 @@ __device__ __forceinline__ void barh(int h) { pair::barh(h); }
   __syncwarp();                                                                               \
   if (lane == 0) mbar_arrive(&cs->empty[h][slot]);                                            \
   ++seq;
+
+// TMA bulk store shared -> global (SASS UBLKCP), bulk-group completion
+__device__ __forceinline__ void bulk_s2g(void* dst, const void* src, unsigned bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(src)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
 // x >= ce: append x to the thread's list column, advance the column pointer, mark the entry's bit
 __device__ __forceinline__ void cap_one(unsigned& lp, unsigned& hm, float x, float ce, unsigned bit) {
@@ -184,21 +197,18 @@ __device__ __forceinline__ int cap_index_of(const unsigned short* bmt, int j, in
 //      fixed summation order: deterministic) of e = 2^(x*log2e - m0) over 16 value buckets of [cut, max].
 //   B  bucket sums, scanned from the top: the bucket b* in which the kept mass crosses top_p * Z and the
 //      mass G above it.
-//   C  one loop over all entries: two 64-bit masks per thread - entries above b* (kept for sure) and
-//      entries in b* (candidates).  From here on only mask bits are visited.
+//   C  one loop over all entries: a 64-bit mask per thread of the entries in b* (candidates).  From here
+//      on only mask bits are visited.
 //   D  while more than 128 candidates remain: 16 sub-buckets of the crossing bucket, histogram over the
-//      candidates only, same scan; candidates above the new crossing bucket join the kept mask.
+//      candidates only, same scan.
 //   F  the <= 128 candidates left are ordered exactly like the reference's sort (scaled logit descending,
 //      lowest index first) by an all-pairs rank in 38-bit fixed point (integer sums: exactly one entry
 //      crosses), as in pair::half_select.
-//   E  emission: the kept mask's entries go to the row's list at per-thread offsets (prefix sum of the
-//      counts: no atomics in the loop), the kept candidates behind them.
 // Returns false when the row needs the general search (nucleus not inside the captured set, more equal
 // values than the finish can order, float scan and exact finish disagreeing at a bucket edge).
 __device__ __noinline__ bool cap_close(const float* lst, int nt, const unsigned short* bmt, int novf, int h, int ht,
                                        float* hist, float cut, float xmax, float Zrow, double target, float m0,
-                                       CapSync* cs, CapScratch* hs, RowRecord& rec, ListEntry* emit, int* nemit_out,
-                                       int* stats) {
+                                       CapSync* cs, CapScratch* hs, RowRecord& rec, int* stats) {
   const int lane = ht & 31, hw = ht >> 5;
   const int ne = nt + (novf - ht + kHT - 1) / kHT;
   float* hp = hist + ht;
@@ -217,7 +227,7 @@ __device__ __noinline__ bool cap_close(const float* lst, int nt, const unsigned 
     const float x = getx(j);
     hp[lv_bucket(fA, fsc, x) * kHT] += row_exp(x, m0);
   }
-  unsigned long long keptm = 0ull, candm = 0ull;
+  unsigned long long candm = 0ull;
   float G = 0.0f;  // mass above the current crossing bucket (float, fixed order)
   int total = 0;
 #pragma unroll 1
@@ -270,16 +280,12 @@ __device__ __noinline__ bool cap_close(const float* lst, int nt, const unsigned 
     if (level == 0) {
 #pragma unroll 2
       for (int j = 0; j < ne; ++j) {
-        const int bk = lv_bucket(fA, fsc, getx(j));
-        keptm |= (unsigned long long)(bk > bstar) << j;
-        candm |= (unsigned long long)(bk == bstar) << j;
+        candm |= (unsigned long long)(lv_bucket(fA, fsc, getx(j)) == bstar) << j;
       }
     } else {
       for (unsigned long long m = candm; m; m &= m - 1ull) {
         const int j = __ffsll((long long)m) - 1;
-        const int bk = lv_bucket(fA, fsc, getx(j));
-        if (bk > bstar) keptm |= 1ull << j;
-        if (bk != bstar) candm &= ~(1ull << j);
+        if (lv_bucket(fA, fsc, getx(j)) != bstar) candm &= ~(1ull << j);
       }
     }
     fA = fmaf(float(bstar), 1.0f / fsc, fA);
@@ -287,19 +293,6 @@ __device__ __noinline__ bool cap_close(const float* lst, int nt, const unsigned 
     // (the next level's barrier orders these reads of hsum / hist before they are overwritten)
   }
   if (total > kHT || total <= 0) return false;  // more (equal) values than the finish can order
-  // ---- E (first half): offsets of the kept-for-sure entries in the row's list
-  int off = 0;
-  if (emit != nullptr) {
-    const int c = __popcll(keptm);
-    int inc = c;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-      const int o = __shfl_up_sync(0xffffffffu, inc, d);
-      if (lane >= d) inc += o;
-    }
-    if (lane == 31) hs->wpre[hw] = inc;
-    off = inc - c;
-  }
   // ---- F: the candidates left, with their indices, in the reference's order
   const int ez = int(__float_as_uint(Zrow) >> 23) - 126;               // Z = f * 2^ez, f in [0.5, 1)
   const float S = __uint_as_float(unsigned(127 + 38 - ez) << 23);      // 2^(38 - ez)
@@ -319,15 +312,6 @@ __device__ __noinline__ bool cap_close(const float* lst, int nt, const unsigned 
   if (ht == 0) STAMP(stats, 29);
   const int n = hs->ncand;
   if (n > kHT || n <= 0) return false;
-  int certain = 0;
-  if (emit != nullptr) {
-#pragma unroll
-    for (int w = 0; w < kHW; ++w) {
-      if (w < hw) off += hs->wpre[w];
-      certain += hs->wpre[w];
-    }
-    if (ht == 0) hs->nemit = certain;
-  }
   int Pn = 16;
   while (Pn < n) Pn <<= 1;
   const int parts = kHT / Pn;  // 1..8 threads share one candidate (same warp)
@@ -352,50 +336,11 @@ __device__ __noinline__ bool cap_close(const float* lst, int nt, const unsigned 
     hs->gb_new = incl;
     hs->res_ok = 1;
   }
-  barh(h);  // also: nemit holds the number of kept-for-sure entries
+  barh(h);
   if (!hs->res_ok) return false;  // the float scan chose a neighbouring bucket (edge case): general search
   rec.Z = float(double(hs->gb_new) / double(S));
   rec.xstar = hs->res_x;
   rec.istar = hs->res_i;
-  if (emit == nullptr) return true;
-  // ---- E (second half): candidates at or before the crossing entry, then the kept mask's entries
-  {
-    const bool keep = mine && incl - fme <= tgt;
-    const unsigned bal = __ballot_sync(0xffffffffu, keep);
-    if (bal != 0u) {
-      int base = 0;
-      if (lane == 0) base = atomicAdd(&hs->nemit, __popc(bal));
-      base = __shfl_sync(0xffffffffu, base, 0);
-      const int pos = base + __popc(bal & ((1u << lane) - 1u));
-      if (keep && pos < kListCap) emit[pos] = ListEntry{xx, ii};
-    }
-  }
-  if (keptm != 0ull) {
-    int j = 0;
-    const int nstage_bits = nt;  // entries 0 .. nt-1 are walked through the bit map, the rest carry their index
-    int stage = -1;
-    unsigned hm = 0u;
-    for (; j < nstage_bits; ++j) {
-      while (hm == 0u) {
-        ++stage;
-        hm = bmt[stage * kHT];
-      }
-      const int k = __ffs(hm) - 1;
-      hm &= hm - 1u;
-      if ((keptm >> j) & 1ull) {
-        if (off < kListCap) emit[off] = ListEntry{lst[j * kHT], stage * kStageElems + ((k >> 2) * kHT + ht) * 4 + (k & 3)};
-        ++off;
-      }
-    }
-    for (; j < ne; ++j) {
-      if ((keptm >> j) & 1ull) {
-        if (off < kListCap) emit[off] = hs->ovf[(j - nt) * kHT + ht];
-        ++off;
-      }
-    }
-  }
-  barh(h);
-  *nemit_out = hs->nemit;
   return true;
 }
 
@@ -495,6 +440,7 @@ __global__ void __launch_bounds__(kPT, 2) row_capture_kernel(const __grid_consta
     }
 
     int state = 0, nt = 0, novf = 0;
+    bool dumped = false;
     float Z = 0.0f, m0 = 0.0f, cut = INFINITY, xmax = -INFINITY;
     double target = 0.0;
     if (have) {
@@ -553,7 +499,17 @@ __global__ void __launch_bounds__(kPT, 2) row_capture_kernel(const __grid_consta
       for (int o = 16; o > 0; o >>= 1) z += __shfl_xor_sync(0xffffffffu, z, o);
       if (lp >= lim) cap_spill_rest<TIn>(hs, bmt, row, V, nchunk, temp, cut, ht);
       if (lane == 0) cs->post[h][hw] = make_float2(z, 0.0f);
+      const bool dump = nucleus && jb.is_target && nchunk <= kDumpMaxChunks;
+      if (dump) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // list / bit-map writes -> the async proxy
       barh(h);  // also: every list column and bit map of the half is complete
+      if (dump && ht == 0) {
+        // the row's capture state goes to its workspace slot while the select runs (nobody writes it until the row closes)
+        unsigned char* slot = reinterpret_cast<unsigned char*>(P.lists + (long long)(jb.b * (gamma + 1) + jb.j) * kListCap);
+        bulk_s2g(slot, lists + h * kSlots * kHT, unsigned(kSlots * kHT * 4));
+        bulk_s2g(slot + kDumpBitmap, bm_all + size_t(h) * cap_bitmap_bytes(nchunk), unsigned(cap_bitmap_bytes(nchunk)));
+        bulk_commit();
+      }
+      dumped = dump;
       if (ht == 0) STAMP(P.stats, 9);
       z = 0.0f;
 #pragma unroll
@@ -571,12 +527,16 @@ __global__ void __launch_bounds__(kPT, 2) row_capture_kernel(const __grid_consta
     rec.m0 = m0, rec.Z = Z, rec.xstar = -INFINITY, rec.istar = 0x7fffffff;
     rec.sel = 0.0f, rec.mxl = m0, rec.dens = 0.0f, rec.pad = 0;
     if (state == 2) {
-      int nem = 0;
-      ListEntry* el = jb.is_target ? P.lists + (long long)(jb.b * (gamma + 1) + jb.j) * kListCap : nullptr;
-      const bool ok = cap_close(lst, nt, bmt, novf, h, ht, hist, cut, xmax, Z, target, m0, cs, hs, rec, el, &nem, P.stats);
+      const bool ok = cap_close(lst, nt, bmt, novf, h, ht, hist, cut, xmax, Z, target, m0, cs, hs, rec, P.stats);
       if (!ok) state = 3;
       if (ht == 0) STAMP(P.stats, 10);
-      if (ok && jb.is_target) rec.pad = nem <= kListCap ? nem + 1 : 0;
+      if (ok && dumped) {
+        // the overflow pool (rare) follows with plain stores; the record's flag tells the sample kernel to use the dump
+        unsigned char* slot = reinterpret_cast<unsigned char*>(P.lists + (long long)(jb.b * (gamma + 1) + jb.j) * kListCap);
+        ListEntry* gp = reinterpret_cast<ListEntry*>(slot + kDumpPool + 16);
+        for (int o = ht; o < novf; o += kHT) gp[o] = hs->ovf[o];
+        rec.pad = 1 + novf;
+      }
       if (P.stats && ht == 0) atomicAdd(&P.stats[ok ? 16 : 17], 1);
     }
     if (ht == 0) {
@@ -593,6 +553,7 @@ __global__ void __launch_bounds__(kPT, 2) row_capture_kernel(const __grid_consta
       }
     }
     if (ht == 0) {
+      if (dumped) bulk_wait_all();  // the bulk stores are complete: the columns may be overwritten, the dump is in memory
       hs->novf = 0;  // every reader of this row's pool is behind a half barrier; the next row's appends are after the join
       STAMP(P.stats, 11);
     }

@@ -41,8 +41,11 @@ __device__ __forceinline__ void stamp(int* stats, int k, bool first = false) {
   atomicMax(&stats[k], first ? 0x7fffffff - v : v);
 }
 #define STAMP(stats, k, ...) stamp(stats, k, ##__VA_ARGS__)
+// cycle stamps relative to t0 (same SM): slot k keeps the maximum
+#define CSTAMP(stats, k, t0) do { if (stats) atomicMax(&(stats)[k], int(clock64() - (t0))); } while (0)
 #else
 #define STAMP(stats, k, ...)
+#define CSTAMP(stats, k, t0)
 #endif
 
 struct ListEntry {
@@ -85,6 +88,7 @@ struct SplitParams {
   int* seq_arrive;              // [B]
   int* stats;
   int cap_rank;      // row-capture kernel: rank (0..31) of the sorted group maxima that gives the capture cut
+  int cap_slots;     // row-capture kernel: list slots per worker thread (layout of a row's dump)
   int compact_hint;  // sample kernel: target rows are expected to come with a kept-entry list (no noise prefetch)
   int row0_rule;     // sample kernel: sequence 0's accepted count positions every sequence (reference batch rule)
 };

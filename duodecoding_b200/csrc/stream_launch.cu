@@ -71,7 +71,7 @@ constexpr int kMaxGrid = 320;   // blocks of a persistent scan kernel (two per S
 // one scratch list per scan block
 size_t stream_workspace_bytes(int B, int gamma) {
   const size_t rows = size_t(B) * size_t(2 * gamma + 1);
-  return 4 * sizeof(StreamHint) + rows * sizeof(RowRecord) + size_t(B) * 24 +
+  return 4 * sizeof(StreamHint) + rows * sizeof(RowRecord) + size_t(B) * 24 + 128 +
          (size_t(B) * size_t(gamma + 1) + kMaxGrid) * size_t(kListCap) * sizeof(ListEntry);
 }
 
@@ -136,9 +136,11 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
     w += size_t(c.B) * 4;
     Q.seq_arrive = reinterpret_cast<int*>(w);
     w += size_t(c.B) * 4;
+    w = reinterpret_cast<char*>((reinterpret_cast<uintptr_t>(w) + 127) & ~uintptr_t(127));  // TMA bulk stores land here
     Q.lists = reinterpret_cast<ListEntry*>(w);
     Q.stats = c.stats;
     Q.cap_rank = 0;
+    Q.cap_slots = cap::kSlots;
     Q.compact_hint = 0;
     Q.row0_rule = c.row0_rule;
     const dim3 g2(unsigned((c.Vt + kSlice3 - 1) / kSlice3), unsigned(c.B) + 1u);  // + the block row that aggregates the hints
@@ -157,7 +159,7 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
       for (int i = 0; i < 16; ++i) pbelow *= 1.0 - f;
       int rank = int(32.0 * pbelow);
       Q.cap_rank = rank < 0 ? 0 : (rank > 31 ? 31 : rank);
-      Q.compact_hint = (c.top_p > 0.0f && c.top_p < 1.0f) ? 1 : 0;
+      Q.compact_hint = (c.top_p > 0.0f && c.top_p < 1.0f && (c.Vt + kStageElems - 1) / kStageElems <= cap::kDumpMaxChunks) ? 1 : 0;
       const dim3 g2c(unsigned((c.Vt + kSlice3 - 1) / kSlice3), unsigned(c.B));  // no hint row: nothing is predicted
       cudaError_t e;
       const size_t smem2 = sample_smem_bytes();

@@ -59,7 +59,7 @@ def set_team_size(team: int) -> None:
     lib.duodec_set_team_size(int(team))
 
 
-FAST_PATH = 6  # row-capture scan kernel + sample kernel (compact kept-entry lists)
+FAST_PATH = 5  # row-pair scan kernel + sliced sample kernel (6: row-capture kernel, experimental)
 _PATH = 0       # DUODEC_VERIFY_PATH: 0 automatic, 1 general team kernel, 5 row-pair kernel, 6 row capture
 _PHASES = 0     # DUODEC_VERIFY_PHASES: 0 / 3 both kernels, 1 scan only, 2 sample only
 ROW0_RULE = 1   # DUODEC_VERIFY_ROW0_RULE

@@ -92,8 +92,9 @@ int duodec_norm_logits_batched(const void* logits, int in_dtype, int64_t in_batc
  *   token drawn at that position); without it every sequence is verified on its own count.  Only
  *   the fast paths implement it (equal vocabularies, no top-k, T > 0, 16-byte aligned rows):
  *   DUODEC_EINVAL otherwise when B > 1.
- *   DUODEC_VERIFY_PATH(p) - test hook: 0 automatic (row-capture scan kernel when the call qualifies,
- *   else the general team kernel), 1 general team kernel, 5 row-pair scan kernel, 6 row capture.
+ *   DUODEC_VERIFY_PATH(p) - test hook: 0 automatic (row-pair scan kernel when the call qualifies,
+ *   else the general team kernel), 1 general team kernel, 5 row-pair scan kernel, 6 row-capture scan
+ *   kernel (single pass, experimental).
  *   DUODEC_VERIFY_PHASES(m) - measurement hook: 1 scan kernel only, 2 sample kernel only, 0 / 3 both.
  * workspace: duodec_verify_workspace_bytes(B,gamma) bytes, 16-byte aligned, zero-filled ONCE by
  *   the caller before first use (the kernels restore what they need to zero).  One launch in flight

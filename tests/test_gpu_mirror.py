@@ -129,9 +129,12 @@ def test_kvcache_model_rollback(mods, dev):  # test/test_model_gpu_rollback.py
     assert tuple(x.shape) == (1, 7) and cache.current_length == 6 and cache._current_seq_len == 6
     cache.rollback(7)  # must not extend past the real cache length
     assert cache.current_length == 6 and cache._current_seq_len == 6 and cache.prob_history.shape[1] == 6
-    assert cache.seq_lens.tolist() == [6] and len(cache) == 6
+    kv = cache._past_key_values
+    assert isinstance(kv, mg.InPlaceKVCache) and kv.seq_lens.tolist() == [6] and len(cache) == 6
+    ptrs = [layer._kbuf.data_ptr() for layer in kv.layers]
     cache.rollback(4)
-    assert cache.current_length == 4 and cache.prob_history.shape[1] == 4 and cache.seq_lens.tolist() == [4]
+    assert cache.current_length == 4 and cache.prob_history.shape[1] == 4 and kv.seq_lens.tolist() == [4]
+    assert [layer._kbuf.data_ptr() for layer in kv.layers] == ptrs  # a length write: no K/V byte moved
     # contents after rollback + re-forward == a fresh forward of the truncated prefix (unpinned upstream)
     again = cache._forward_with_kvcache(x[:, :6])
     fresh = mg.KVCacheModel(model, temperature=0, top_k=0, top_p=0)
@@ -157,15 +160,239 @@ def test_kvcache_history_rows_match_oracle_and_rebuilt_generation(mods, dev):
     assert float(cache._prob_buffer[0, 2, :10].abs().sum()) == 0.0
 
 
-def test_static_kv_cache_crop_is_a_length_write(mods, dev):
+def test_inplace_kv_cache_ragged_crop_clamps_device_lengths(mods, dev):
     mg = mods[2]
-    kv = mg.StaticKVCache(num_layers=2, batch=3, heads=2, max_len=16, head_dim=4, dtype=torch.float32, device=dev)
+    kv = mg.InPlaceKVCache()
     for layer in range(2):
-        kv.append(layer, torch.ones(3, 2, 5, 4, device=dev), torch.ones(3, 2, 5, 4, device=dev))
-    ptr = kv.keys[0].data_ptr()
+        kv.update(torch.ones(3, 2, 5, 4, device=dev), torch.ones(3, 2, 5, 4, device=dev), layer)
+    ptr = kv.layers[0]._kbuf.data_ptr()
     assert kv.get_seq_length() == 5 and kv.seq_lens.tolist() == [5, 5, 5]
     kv.crop(3)
-    assert kv.get_seq_length() == 3 and kv.seq_lens.tolist() == [3, 3, 3] and kv.keys[0].data_ptr() == ptr
+    assert kv.get_seq_length() == 3 and kv.seq_lens.tolist() == [3, 3, 3] and kv.layers[0]._kbuf.data_ptr() == ptr
     assert [k.shape[2] for k, _ in kv] == [3, 3]
-    kv.crop(torch.tensor([1, 9, 2], device=dev))  # ragged per-sequence lengths
+    kv.crop(torch.tensor([1, 9, 2], device=dev))  # ragged per-sequence lengths (cache_seqlens of attention kernels)
     assert kv.seq_lens.tolist() == [1, 3, 2]
+
+
+# ------------------------------------------------------------------ lazy histories, window, fused routes
+class _NoModel:
+    """What KVCacheModel's constructor needs from a model, for tests that load logit rows by hand."""
+
+    class _Emb:
+        def __init__(self, V, dev):
+            self.weight = torch.zeros(V, 1, device=dev)
+
+    class _Cfg:
+        def __init__(self, V):
+            self.vocab_size = V
+
+    def __init__(self, V, dev):
+        self.config, self._emb = self._Cfg(V), self._Emb(V, dev)
+
+    def get_input_embeddings(self):
+        return self._emb
+
+    def parameters(self):
+        return iter([self._emb.weight])
+
+
+class _Len:
+    """Stand-in transformer cache: a length with crop / get_seq_length (src/model_gpu.py:23-26)."""
+
+    def __init__(self, n):
+        self.n, self.crops = n, []
+
+    def crop(self, end):
+        self.crops.append(end)
+        self.n = min(self.n, end)
+
+    def get_seq_length(self, layer_idx=0):
+        return self.n
+
+
+def _loaded_cache(mg, logits, T, k, p, **kw):
+    """A KVCacheModel whose history holds the given [B, L, V] logit rows."""
+    cache = mg.KVCacheModel(_NoModel(logits.shape[-1], logits.device), temperature=T, top_k=k, top_p=p, **kw)
+    cache._store_rows(logits, 0)
+    cache._past_key_values = _Len(logits.shape[1])
+    return cache
+
+
+def test_probabilities_are_lazy_and_one_launch(mods, dev):
+    mg = mods[2]
+    g = torch.Generator().manual_seed(5)
+    x = (torch.randn(3, 9, 700, generator=g) * 3).to(dev)
+    cache = _loaded_cache(mg, x, 0.8, 0, 0.9)
+    assert cache._prob_buffer is None  # nothing V-sized was normalised by the store
+    assert cache.logits_rows(4, 9).data_ptr() == cache._logits_buffer[:, 4:9].data_ptr()
+    want = oracle.norm_logits(x.cpu(), 0.8, 0, 0.9)
+    torch.testing.assert_close(cache.prob_history.cpu(), want, rtol=1e-4, atol=1e-7)
+    cache.prob_history[:, 2, :10] = 0.0  # callers write into the history (src/engine.py:948-954)
+    assert float(cache._prob_buffer[0, 2, :10].abs().sum()) == 0.0
+    cache._store_rows(x[:, :2], 9)  # two more rows: only they are normalised on the next read
+    assert float(cache.prob_history[0, 2, :10].abs().sum()) == 0.0 and cache.prob_history.shape[1] == 11
+    cache.rollback(7)
+    assert cache.prob_history.shape[1] == 7 and cache._past_key_values.crops == [7]
+
+
+def test_history_window_keeps_memory_flat_and_serves_recent_rows(mods, dev):
+    mg = mods[2]
+    g = torch.Generator().manual_seed(6)
+    V, W = 512, 4
+    x = (torch.randn(2, 23, V, generator=g) * 2).to(dev)
+    cache = _loaded_cache(mg, x[:, :5], 1.0, 0, 0.0, history_window=W)
+    for t in range(5, 23):
+        cache._store_rows(x[:, t:t + 1], t)
+        cache._past_key_values.n = t + 1
+    assert cache._logits_buffer.shape[1] == 2 * W and cache._current_seq_len == 23
+    hist = cache.prob_history
+    assert tuple(hist.shape) == (2, 23, V)
+    want = oracle.norm_logits(x[:, 20:23].cpu(), 1.0, 0, 0.0)
+    torch.testing.assert_close(hist[:, 20:23, :].cpu(), want, rtol=1e-4, atol=1e-7)
+    torch.testing.assert_close(hist[:, -1, :V].cpu(), want[:, -1], rtol=1e-4, atol=1e-7)
+    torch.testing.assert_close(cache.logits_history[:, 21, :].cpu(), x[:, 21].cpu())
+    hist[:, 22, :7] = 0.0
+    assert float(cache.prob_history[:, 22, :7].abs().sum()) == 0.0
+    with pytest.raises(IndexError):
+        _ = hist[:, 3, :]
+    # B=256, V=151936 (config 5) stays under 2 GB with a window: 256 * 2W * V * 2 bytes
+    big = mg.KVCacheModel(_NoModel(151936, dev), history_window=8)
+    big._ensure_buffer_size(256, 1, dev, torch.bfloat16)
+    assert big._logits_buffer.numel() * 2 < 2 * 1024 ** 3 and big._prob_buffer is None
+
+
+def _fused_case(seed, B, P, gamma, V, sigma, dtype=torch.float32):
+    g = torch.Generator().manual_seed(seed)
+    tl = torch.randn(B, P + gamma, V, generator=g) * 3
+    dl = tl[:, :P + gamma - 1] + sigma * torch.randn(B, P + gamma - 1, V, generator=g)
+    tl, dl = tl.to(dtype), dl.to(dtype)
+    q = oracle.norm_logits(dl[:, P - 1:].float(), 1.0, 0, 0.9)
+    toks = torch.stack([oracle.sample(q[:, j], torch.empty(B, V).exponential_(1, generator=g))[:, 0]
+                        for j in range(gamma)], 1)
+    x = torch.cat((torch.randint(0, V, (B, P), generator=g), toks), 1)
+    r = torch.rand(B, gamma, generator=g)
+    noise = torch.empty(B, V).exponential_(1, generator=g)
+    return dl, tl, x, r, noise
+
+
+def _row0_expectation(dl, tl, x, r, noise, P, gamma):
+    """The reference's flow on the CPU oracle: sequence 0's accepted count positions every sequence."""
+    q = oracle.norm_logits(dl[:, P - 1:P - 1 + gamma].float(), 1.0, 0, 0.9)
+    p = oracle.norm_logits(tl[:, P - 1:P + gamma].float(), 1.0, 0, 0.9)
+    acc = oracle.compute_acceptance(q, p[:, :gamma], x[:, P:P + gamma], P, r)
+    a = acc["accepted_count"]
+    tok = oracle.sample_accept_token(p[:, gamma], noise) if a == gamma else \
+        oracle.sample_reject_token(p[:, a], q[:, a], noise)
+    return a, P + a - 1, tok
+
+
+@pytest.mark.parametrize("B,V,dtype", [(1, 4096, torch.float32), (5, 32000, torch.float32), (3, 8192, torch.bfloat16)])
+def test_fused_routes_match_the_reference_flow(mods, dev, B, V, dtype):
+    """resolve_stage_verification and verify_draft_sequence -> finalize_verification on KVCacheModel caches run
+    one fused kernel on the logit rows; results equal the reference flow (batch rule included) on the oracle."""
+    from unittest.mock import patch
+    dops, mg = mods[0], mods[2]
+    P, gamma = 6, 4
+    for seed, sigma in [(41, 0.4), (42, 1.5), (43, 0.0)]:
+        dl, tl, x, r, noise = _fused_case(seed, B, P, gamma, V, sigma, dtype)
+        a, n, tok = _row0_expectation(dl, tl, x, r, noise, P, gamma)
+        for route in ("resolve", "engine"):
+            dc = _loaded_cache(mg, dl.to(dev), 1.0, 0, 0.9)
+            tc = _loaded_cache(mg, tl.to(dev), 1.0, 0, 0.9)
+            with patch.object(torch, "rand", lambda *s, **kw: r.to(dev)), \
+                    patch.object(torch.Tensor, "exponential_", lambda self, *a_, **kw: self.copy_(noise.to(dev))):
+                if route == "resolve":
+                    got = dops.resolve_stage_verification(dc, tc, x.to(dev), P, gamma, output_device=dev)
+                    ga, gn, gt, gall = got
+                else:
+                    ga, gn = dops.verify_draft_sequence(dc, tc, x.to(dev), P, gamma, transfer_mode="none",
+                                                        send_reject_message=False)
+                    assert tc._fused_token is not None
+                    out = dops.finalize_verification(dc, tc, x.to(dev), P, gamma, gn)
+                    assert tuple(out.shape) == (B, gn + 2) and torch.equal(out[:, :gn + 1].cpu(), x[:, :gn + 1])
+                    gt, gall = out[:, -1:], gn >= P + gamma - 1
+            assert dc._prob_buffer is None and tc._prob_buffer is None  # no probability row was materialised
+            assert isinstance(ga, int) and isinstance(gn, int) and (ga, gn) == (a, n) and gall == (a == gamma)
+            assert torch.equal(gt.cpu().reshape(-1), tok.reshape(-1)), (route, seed)
+            assert dc._past_key_values.crops == [n + 1] and tc._past_key_values.crops == [n + 2 if a == gamma else n + 1]
+
+
+def test_fused_route_steps_aside_for_overrides_and_patched_samplers(mods, dev):
+    from unittest.mock import patch
+    dops, mg = mods[0], mods[2]
+    P, gamma, V = 5, 3, 4096
+    dl, tl, x, r, noise = _fused_case(44, 1, P, gamma, V, 0.8)
+    dc, tc = _loaded_cache(mg, dl.to(dev), 1.0, 0, 0.9), _loaded_cache(mg, tl.to(dev), 1.0, 0, 0.9)
+    with patch("duodecoding_b200.decoding_ops.sample", lambda probs, *a, **k: torch.full((probs.shape[0], 1), 7, device=dev)):
+        _, _, t, _ = dops.resolve_stage_verification(dc, tc, x.to(dev), P, gamma, output_device=dev)
+    assert t.tolist() == [[7]] and tc._prob_buffer is not None  # the mocked sampler saw probability rows
+    dc, tc = _loaded_cache(mg, dl.to(dev), 1.0, 0, 0.9), _loaded_cache(mg, tl.to(dev), 1.0, 0, 0.9)
+    override = dc.prob_history.clone()
+    dops.resolve_stage_verification(dc, tc, x.to(dev), P, gamma, output_device=dev, draft_probs_override=override)
+    assert tc._prob_buffer is not None
+
+
+def test_golden_resolve_and_finalize_replayed_on_the_gpu(golden, mods, dev):
+    """The reference-generated resolve/* and finalize/* fixtures through the GPU mirrors (probability-space
+    operators on plain history tensors), bit-exact."""
+    from unittest.mock import patch
+    import duodecoding_b200.ops as ops
+    dops = mods[0]
+    Pm, Qm = torch.from_numpy(golden["finalize/P"]).to(dev), torch.from_numpy(golden["finalize/Q"]).to(dev)
+    x = torch.from_numpy(golden["finalize/x"]).to(dev)
+    noise = torch.from_numpy(golden["finalize/noise"]).to(dev)
+    V = Pm.shape[-1]
+    with patch.object(ops, "draw_noise", lambda rows, v, d, generator=None: noise[:rows, :v]):
+        for name in ("reject", "accept"):
+            P_, g_, n_ = (int(v) for v in golden[f"finalize/{name}/args"])
+            a, t = Cache(Qm.clone(), V), Cache(Pm.clone(), V)
+            y = dops.finalize_verification(a, t, x, P_, g_, n_)
+            assert torch.equal(y.cpu(), torch.from_numpy(golden[f"finalize/{name}/out"]))
+            assert a.rollback_calls + t.rollback_calls == golden[f"finalize/{name}/rollbacks"].tolist()
+        for name in ("mixed", "all"):
+            rr = torch.from_numpy(golden[f"resolve/{name}/r"]).to(dev)
+            a, t = Cache(Qm.clone(), V), Cache(Pm.clone(), V)
+            with patch.object(torch, "rand", lambda *s, **kw: rr.clone()):
+                ac, n, tk, alla = dops.resolve_stage_verification(a, t, x, 8, 4, output_device=dev)
+            assert [ac, n, int(tk), int(alla)] == golden[f"resolve/{name}/result"].tolist()
+            assert a.rollback_calls + t.rollback_calls == golden[f"resolve/{name}/rollbacks"].tolist()
+
+
+class _Comm:
+    def __init__(self):
+        self.calls = []
+
+    def transfer(self, *args):
+        self.calls.append(("transfer",) + tuple(a.shape if isinstance(a, torch.Tensor) else a for a in args))
+
+    def send_reject_message(self, link):
+        self.calls.append(("reject", link))
+
+
+def test_verify_draft_sequence_comm_accounting_and_empty_history(mods, dev):  # src/decoding_ops.py:223-328
+    from unittest.mock import patch
+    dops = mods[0]
+    g = torch.Generator().manual_seed(9)
+    B, L, V, P, gamma = 1, 10, 300, 5, 4
+    q = torch.softmax(torch.randn(B, L, V, generator=g), -1).to(dev)
+    p = torch.softmax(torch.randn(B, L, V, generator=g), -1).to(dev)
+    x = torch.randint(0, V, (B, P + gamma), generator=g).to(dev)
+    r = torch.rand(B, gamma, generator=g)
+    want = oracle.compute_acceptance(q[:, P - 1:P - 1 + gamma].cpu(), p[:, P - 1:P - 1 + gamma].cpu(),
+                                     x[:, P:P + gamma].cpu(), P, r)
+    for mode in ("none", "serial", "batch_before"):
+        comm, metrics = _Comm(), {"draft_generated_tokens": 0, "draft_accepted_tokens": 0}
+        with patch.object(torch, "rand", lambda *s, **kw: r.to(dev)):
+            ac, n = dops.verify_draft_sequence(Cache(q, V), Cache(p, V), x, P, gamma, comm_simulator=comm,
+                                               comm_link="edge_cloud", transfer_mode=mode, decoding_metrics=metrics)
+        assert (ac, n) == (want["accepted_count"], want["n"])
+        assert metrics == {"draft_generated_tokens": gamma, "draft_accepted_tokens": n - P + 1}
+        rejected = ac < gamma
+        kinds = [c[0] for c in comm.calls]
+        assert kinds.count("reject") == (1 if rejected else 0)
+        assert kinds.count("transfer") == {"none": 0, "batch_before": 1, "serial": ac + (1 if rejected else 0)}[mode]
+    # nothing to verify: early return, no traffic, no metrics (reference: `if actual_gamma <= 0: return 0, prefix_len - 1`)
+    comm, metrics = _Comm(), {"draft_generated_tokens": 0, "draft_accepted_tokens": 0}
+    ac, n = dops.verify_draft_sequence(Cache(q[:, :4], V), Cache(p, V), x, P, gamma, comm_simulator=comm,
+                                       transfer_mode="batch_before", decoding_metrics=metrics)
+    assert (ac, n) == (0, P - 1) and comm.calls == [] and metrics["draft_generated_tokens"] == 0
