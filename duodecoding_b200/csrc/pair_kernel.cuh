@@ -159,7 +159,9 @@ __device__ __forceinline__ bool half_select(const ListEntry* hl, const int* wn, 
   const int ez = int(__float_as_uint(Zrow) >> 23) - 126;               // Z = f * 2^ez, f in [0.5, 1)
   const float S = __uint_as_float(unsigned(127 + 38 - ez) << 23);      // 2^(38 - ez)
   const unsigned long long tgt = (unsigned long long)(target * double(S));  // floor
-  unsigned long long GBf = (unsigned long long)(double(GB) * double(S));    // floor: GBf <= tgt
+  unsigned long long GBf = (unsigned long long)(double(GB) * double(S));
+  if (GBf > tgt) GBf = tgt;  // GB is an fp32 scan difference: it may land a few ulps above the target; the top
+                             // non-empty bucket is then the crossing one and its largest entry the boundary
   auto entry = [&](int j) { return &hl[j * kHT + ht]; };
   auto fx = [&](float x) { return __float2ull_rn(row_exp(x, m0) * S); };  // fixed-point mass of an entry
   float cx[kPer];
@@ -546,7 +548,9 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
         if (crossed) {
           const int l = __ffs(crossed) - 1;
           bstar = kHB - 1 - l;
-          GB = __shfl_sync(0xffffffffu, incl - hb, l);
+          // mass above the crossing bucket = the previous lane's inclusive sum (not incl - hb, which is rounded twice)
+          const float prev = __shfl_up_sync(0xffffffffu, incl, 1);
+          GB = l == 0 ? 0.0f : __shfl_sync(0xffffffffu, prev, l);
         }
         if (bstar <= 0) slow = true;  // the lower end bucket is unbounded below
       }

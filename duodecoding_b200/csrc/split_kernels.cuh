@@ -228,7 +228,8 @@ __device__ __forceinline__ void list_select_body(const ListEntry* list, int nlis
   const int ez = int(__float_as_uint(pr.z) >> 23) - 126;               // Z = f * 2^ez, f in [0.5, 1)
   const float S = __uint_as_float(unsigned(127 + 38 - ez) << 23);      // 2^(38 - ez)
   const unsigned long long tgt = (unsigned long long)(target * double(S));  // floor
-  unsigned long long GBf = (unsigned long long)(double(GB) * double(S));    // floor: GBf <= tgt
+  unsigned long long GBf = (unsigned long long)(double(GB) * double(S));
+  if (GBf > tgt) GBf = tgt;  // (a float GB a few ulps above the target: the top non-empty bucket is the crossing one)
   // entry j of this thread sits at list[j * 256 + tid]; it exists if j < mycnt (per-thread columns,
   // mycnt >= 0) or j * 256 + tid < nlist (one shared list, mycnt < 0)
   float cx[kPer];

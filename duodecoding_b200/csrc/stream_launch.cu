@@ -7,6 +7,7 @@
 #include "../../include/duodec.h"
 #include "pair_kernel.cuh"
 #include "capture_kernel.cuh"
+#include "greedy_kernels.cuh"
 #include "sample_kernel.cuh"
 #include "stream_launch.h"
 
@@ -78,6 +79,34 @@ size_t stream_workspace_bytes(int B, int gamma) {
 bool stream_try_launch(const StreamCall& c, int* rc) {
   const size_t elt = c.dtype == DUODEC_F32 ? 4 : 2;
   auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+  const size_t nrows = size_t(c.B) * size_t(2 * c.gamma + 1);
+  const bool rows_ok = c.Vd == c.Vt && (size_t(c.Vt) * elt) % 16 == 0 && al16(c.target) && (c.gamma == 0 || al16(c.draft)) &&
+                       (size_t(c.t_sb) * elt) % 16 == 0 && (size_t(c.t_ss) * elt) % 16 == 0 &&
+                       (size_t(c.d_sb) * elt) % 16 == 0 && (size_t(c.d_ss) * elt) % 16 == 0;
+  if (c.temperature == 0.0f && c.draft_temperature == 0.0f && rows_ok && nrows <= 65535 && c.path != 1) {
+    // greedy verification: one arg-max pass over the rows, then one thread per sequence (greedy_kernels.cuh)
+    greedy::GreedyParams G;
+    G.draft = c.draft, G.target = c.target;
+    G.d_sb = c.d_sb, G.d_ss = c.d_ss, G.t_sb = c.t_sb, G.t_ss = c.t_ss;
+    G.B = c.B, G.gamma = c.gamma, G.V = c.Vt, G.row0_rule = c.row0_rule;
+    G.tokens = reinterpret_cast<const long long*>(c.tokens), G.tok_sb = c.tok_sb;
+    G.r = c.r, G.r_sb = c.r_sb;
+    G.accept_mask = c.accept_mask, G.sel_p = c.sel_target_p, G.sel_q = c.sel_draft_p;
+    G.accepted_len = reinterpret_cast<long long*>(c.accepted_len), G.token = reinterpret_cast<long long*>(c.token);
+    G.all_accepted = c.all_accepted;
+    const size_t head = (size_t(c.B) * 8 + size_t(c.B) * size_t(c.gamma + 1) * 8 + 15) & ~size_t(15);
+    G.cells = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(c.workspace) + head + 4 * sizeof(StreamHint));
+    cudaError_t e = cudaMemsetAsync(G.cells, 0, nrows * 8, c.stream);  // (the record area: 32 bytes per row)
+    const dim3 grid(unsigned((c.Vt + greedy::kGSlice - 1) / greedy::kGSlice), unsigned(nrows));
+    if (e == cudaSuccess) {
+      if (c.dtype == DUODEC_F32) greedy::greedy_argmax_kernel<float><<<grid, greedy::kGT, 0, c.stream>>>(G);
+      else greedy::greedy_argmax_kernel<__nv_bfloat16><<<grid, greedy::kGT, 0, c.stream>>>(G);
+      greedy::greedy_close_kernel<<<(c.B + 127) / 128, 128, 0, c.stream>>>(G);
+      e = cudaGetLastError();
+    }
+    *rc = int(e);
+    return true;
+  }
   const bool ok = c.Vd == c.Vt && c.gamma <= 64 && c.temperature > 0.0f && c.draft_temperature > 0.0f &&
                   c.top_k <= 0 && c.draft_top_k <= 0 && (size_t(c.Vt) * elt) % 16 == 0 && al16(c.target) &&
                   (c.gamma == 0 || al16(c.draft)) && (size_t(c.t_sb) * elt) % 16 == 0 &&
