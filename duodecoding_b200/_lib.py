@@ -62,20 +62,26 @@ SIGNATURES = {
     "duodec_shard_stats": (
         c_int,
         [c_void_p, c_void_p, c_int, c_i64, c_i64, c_i64, c_i64, c_int, c_int, c_int, c_int, c_void_p, c_i64]
-        + [c_float, c_float, c_void_p, c_void_p],
+        + [c_float, c_float, c_void_p, c_void_p, c_void_p],
     ),
     "duodec_shard_accept": (
         c_int,
         [c_void_p, c_int, c_int, c_int, c_void_p, c_i64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
-         c_void_p],
+         c_void_p, c_void_p],
     ),
     "duodec_shard_sample": (
         c_int,
         [c_void_p, c_void_p, c_int, c_i64, c_i64, c_i64, c_i64, c_int, c_int, c_int, c_int, c_float, c_float]
-        + [c_void_p, c_void_p, c_i64, c_int, c_void_p, c_void_p],
+        + [c_void_p, c_void_p, c_i64, c_int, c_void_p, c_void_p, c_void_p],
     ),
-    "duodec_shard_finish": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "duodec_shard_finish": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
 }
+
+
+class ShardXchg(ctypes.Structure):
+    """duodec_shard_xchg (include/duodec.h): the fused peer-memory exchange of the sharded step."""
+
+    _fields_ = [("peers", c_void_p), ("rank", c_int), ("world", c_int), ("off_stats", c_i64), ("off_partial", c_i64)]
 
 
 class DuodecError(RuntimeError):

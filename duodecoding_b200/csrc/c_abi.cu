@@ -383,63 +383,82 @@ static bool shard_rows_ok(const void* draft, const void* target, int dtype, int 
          (dtype == DUODEC_F32 || dtype == DUODEC_BF16);
 }
 
+static bool xchg_ok(const duodec_shard_xchg* x) {
+  return x == nullptr || (x->peers != nullptr && x->world >= 1 && x->world <= 32 && x->rank >= 0 && x->rank < x->world &&
+                          x->off_stats >= 1024 && x->off_partial >= 1024 && x->off_stats % 16 == 0 &&
+                          x->off_partial % 8 == 0);
+}
+static ShardXchg xchg_of(const duodec_shard_xchg* x) {
+  if (x == nullptr) return ShardXchg{nullptr, 0, 1, 0, 0};
+  return ShardXchg{x->peers, x->rank, x->world, x->off_stats, x->off_partial};
+}
+
 int duodec_shard_stats(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss, int64_t t_sb,
                        int64_t t_ss, int B, int gamma, int Vs, int v_begin, const int64_t* tokens, int64_t tok_sb,
-                       float temperature, float draft_temperature, float* stats, void* stream) {
+                       float temperature, float draft_temperature, float* stats, const duodec_shard_xchg* xchg,
+                       void* stream) {
   if (!shard_rows_ok(draft, target, dtype, B, gamma, Vs) || temperature <= 0.0f || draft_temperature <= 0.0f)
     return DUODEC_EINVAL;
   if (B == 0) return 0;
-  if (!stats || (gamma > 0 && !tokens)) return DUODEC_EINVAL;
+  if (!xchg_ok(xchg) || (!stats && !xchg) || (gamma > 0 && !tokens)) return DUODEC_EINVAL;
+  const ShardXchg X = xchg_of(xchg);
   const ShardRows S{draft, target, d_sb, d_ss, t_sb, t_ss, B, gamma, Vs, v_begin, temperature, draft_temperature};
   const int rows = B * (2 * gamma + 1);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (dtype == DUODEC_F32)
     shard_stats_kernel<float><<<rows, kThreads, 0, st>>>(S, reinterpret_cast<const long long*>(tokens), tok_sb,
-                                                         reinterpret_cast<float4*>(stats));
+                                                         reinterpret_cast<float4*>(stats), X);
   else
     shard_stats_kernel<__nv_bfloat16><<<rows, kThreads, 0, st>>>(S, reinterpret_cast<const long long*>(tokens), tok_sb,
-                                                                 reinterpret_cast<float4*>(stats));
+                                                                 reinterpret_cast<float4*>(stats), X);
   return int(cudaGetLastError());
 }
 
 int duodec_shard_accept(const float* gathered_stats, int world, int B, int gamma, const float* r, int64_t r_sb,
                         uint8_t* accept_mask, float* sel_target_p, float* sel_draft_p, int64_t* accepted_len,
-                        uint8_t* all_accepted, void* plan, void* stream) {
+                        uint8_t* all_accepted, void* plan, const duodec_shard_xchg* xchg, void* stream) {
   if (world <= 0 || B < 0 || gamma < 0 || gamma > 32) return DUODEC_EINVAL;
   if (B == 0) return 0;
-  if (!gathered_stats || !accepted_len || !all_accepted || !plan ||
+  if (!xchg_ok(xchg) || (xchg && xchg->world != world)) return DUODEC_EINVAL;
+  if ((!gathered_stats && !xchg) || !accepted_len || !all_accepted || !plan ||
       (gamma > 0 && (!r || !accept_mask || !sel_target_p || !sel_draft_p)))
     return DUODEC_EINVAL;
   shard_accept_kernel<<<B, 32, 0, static_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<const float4*>(gathered_stats), world, B, gamma, r, r_sb, accept_mask, sel_target_p,
-      sel_draft_p, reinterpret_cast<long long*>(accepted_len), all_accepted, static_cast<ShardPlan*>(plan));
+      sel_draft_p, reinterpret_cast<long long*>(accepted_len), all_accepted, static_cast<ShardPlan*>(plan),
+      xchg_of(xchg));
   return int(cudaGetLastError());
 }
 
 int duodec_shard_sample(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss, int64_t t_sb,
                         int64_t t_ss, int B, int gamma, int Vs, int v_begin, float temperature,
                         float draft_temperature, const void* plan, const float* noise, int64_t noise_sb,
-                        int nslice, void* partial, void* stream) {
+                        int nslice, void* partial, const duodec_shard_xchg* xchg, void* stream) {
   if (!shard_rows_ok(draft, target, dtype, B, gamma, Vs)) return DUODEC_EINVAL;
   if (B == 0) return 0;
-  if (!plan || !noise || !partial || nslice <= 0 || nslice > 65535 || B > 65535) return DUODEC_EINVAL;
+  if (!xchg_ok(xchg) || !plan || !noise || (!partial && !xchg) || nslice <= 0 || nslice > 65535 || B > 65535)
+    return DUODEC_EINVAL;
+  const ShardXchg X = xchg_of(xchg);
   const ShardRows S{draft, target, d_sb, d_ss, t_sb, t_ss, B, gamma, Vs, v_begin, temperature, draft_temperature};
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (dtype == DUODEC_F32)
-    shard_sample_kernel<float><<<dim3(unsigned(nslice), unsigned(B)), kThreads, 0, st>>>(S, static_cast<const ShardPlan*>(plan), noise, noise_sb,
-                                                       static_cast<ShardPartial*>(partial));
+    shard_sample_kernel<float><<<dim3(unsigned(nslice), unsigned(B)), kThreads, 0, st>>>(
+        S, static_cast<const ShardPlan*>(plan), noise, noise_sb, static_cast<ShardPartial*>(partial), X);
   else
-    shard_sample_kernel<__nv_bfloat16><<<dim3(unsigned(nslice), unsigned(B)), kThreads, 0, st>>>(S, static_cast<const ShardPlan*>(plan), noise,
-                                                               noise_sb, static_cast<ShardPartial*>(partial));
+    shard_sample_kernel<__nv_bfloat16><<<dim3(unsigned(nslice), unsigned(B)), kThreads, 0, st>>>(
+        S, static_cast<const ShardPlan*>(plan), noise, noise_sb, static_cast<ShardPartial*>(partial), X);
   return int(cudaGetLastError());
 }
 
-int duodec_shard_finish(const void* gathered_partials, int world, int B, int nslice, int64_t* token, void* stream) {
+int duodec_shard_finish(const void* gathered_partials, int world, int B, int nslice, int64_t* token,
+                        const duodec_shard_xchg* xchg, void* stream) {
   if (world <= 0 || B < 0 || nslice <= 0) return DUODEC_EINVAL;
   if (B == 0) return 0;
-  if (!gathered_partials || !token) return DUODEC_EINVAL;
-  shard_finish_kernel<<<(B + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const ShardPartial*>(gathered_partials), world, B, nslice, reinterpret_cast<long long*>(token));
+  if (!xchg_ok(xchg) || (xchg && xchg->world != world) || (!gathered_partials && !xchg) || !token) return DUODEC_EINVAL;
+  const int blocks = xchg ? 1 : (B + 127) / 128;  // the fused exchange closes the step in one block
+  shard_finish_kernel<<<blocks, xchg ? 256 : 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const ShardPartial*>(gathered_partials), world, B, nslice, reinterpret_cast<long long*>(token),
+      xchg_of(xchg));
   return int(cudaGetLastError());
 }
 

@@ -16,6 +16,12 @@
 // Rows are identified like in the fused path: job = b * (2*gamma+1) + k (draft j, target j, ..., bonus).
 // Reference semantics: src/utils.py:686-709 (softmax of logits / T), src/decoding_ops.py:127-147,
 // :190-220, src/utils.py:727-748, :787-810.  No top-k / top-p on this path (C5 runs without filter).
+//
+// Fused exchange (ShardXchg): with peer-mapped symmetric buffers (NVLink / NVSwitch P2P) the two exchanges
+// happen INSIDE the kernels - shard_stats / shard_sample store their 16- / 24-byte results straight into every
+// peer's gather buffer; the block that finishes last publishes the rank's step number to a flag in every
+// peer (st.release.sys); shard_accept / shard_finish spin on their own flags (ld.acquire.sys) and read the
+// gathered data locally.  No NCCL call, no extra launch; a step is four kernels in one CUDA graph.
 #pragma once
 
 #include "common.cuh"
@@ -61,6 +67,50 @@ __device__ __forceinline__ float ex2f(float t) {
 }
 constexpr float kShardLog2e = 1.4426950408889634f;
 
+// ---- fused exchange over peer-mapped memory --------------------------------------------------------
+// Every rank owns one symmetric buffer: a 1 KB header (flags of exchange 1 at +0, of exchange 2 at +256, one u32
+// per rank; block counters at +512 / +516; the step number at +520), then the gather areas.
+constexpr int kXFlags1 = 0, kXFlags2 = 256, kXCnt1 = 512, kXCnt2 = 516, kXStep = 520;
+struct ShardXchg {
+  void* const* peers;  // device array of `world` base pointers (own base at [rank]); nullptr: no fused exchange
+  int rank, world;
+  long long off_stats, off_partial;  // byte offsets of gstats [world][rows] float4 / gpartial [world][B * nslice]
+};
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// thread 0 of every block, after its stores into the peers: the last block of the grid publishes the step
+__device__ __forceinline__ void xchg_publish(const ShardXchg& X, int flags_off, int cnt_off, unsigned nblocks) {
+  __threadfence_system();
+  unsigned char* self = static_cast<unsigned char*>(X.peers[X.rank]);
+  unsigned* cnt = reinterpret_cast<unsigned*>(self + cnt_off);
+  if (atomicAdd(cnt, 1u) == nblocks - 1u) {
+    *cnt = 0u;  // (every block of this grid has counted: ready for the next step)
+    __threadfence_system();
+    const unsigned epoch = *reinterpret_cast<volatile unsigned*>(self + kXStep) + 1u;
+    for (int g = 0; g < X.world; ++g)
+      st_release_sys(reinterpret_cast<unsigned*>(static_cast<unsigned char*>(X.peers[g]) + flags_off) + X.rank, epoch);
+  }
+}
+// whole block: until every rank has published this step (traps after ~2 s instead of hanging the device)
+__device__ __forceinline__ void xchg_wait(const ShardXchg& X, int flags_off) {
+  const unsigned char* self = static_cast<const unsigned char*>(X.peers[X.rank]);
+  if (int(threadIdx.x) < X.world) {
+    const unsigned epoch = *reinterpret_cast<const volatile unsigned*>(self + kXStep) + 1u;
+    const unsigned* f = reinterpret_cast<const unsigned*>(self + flags_off) + threadIdx.x;
+    const long long t0 = clock64();
+    while (int(ld_acquire_sys(f) - epoch) < 0) {
+      if (clock64() - t0 > 4000000000ll) __trap();
+    }
+  }
+  __syncthreads();
+}
+
 struct MaxSum {  // running (max, sum of exp(x - max)); merge is associative, fixed tree order
   float m, s;
 };
@@ -76,7 +126,7 @@ struct OpMaxSum {
 template <class TIn>
 __global__ void __launch_bounds__(kThreads) shard_stats_kernel(const __grid_constant__ ShardRows S,
                                                                const long long* tokens, long long tok_sb,
-                                                               float4* stats) {
+                                                               float4* stats, const ShardXchg X) {
   __shared__ Xchg xc;
   const int job = blockIdx.x, per_b = 2 * S.gamma + 1;
   const int b = job / per_b, k = job - b * per_b;
@@ -124,7 +174,15 @@ __global__ void __launch_bounds__(kThreads) shard_stats_kernel(const __grid_cons
       const long long t = tokens[(long long)b * tok_sb + j] - S.v_begin;
       if (t >= 0 && t < S.Vs) tokx = scale_logit(to_f32(row[t]), temp), has = 1.0f;
     }
-    stats[job] = make_float4(acc.m, acc.s, tokx, has);
+    const float4 v = make_float4(acc.m, acc.s, tokx, has);
+    if (X.peers == nullptr) {
+      stats[job] = v;
+    } else {  // straight into every rank's gather buffer, slot [rank][job]
+      const long long slot = (long long)X.rank * gridDim.x + job;
+      for (int g = 0; g < X.world; ++g)
+        reinterpret_cast<float4*>(static_cast<unsigned char*>(X.peers[g]) + X.off_stats)[slot] = v;
+      xchg_publish(X, kXFlags1, kXCnt1, gridDim.x);
+    }
   }
 }
 
@@ -149,7 +207,11 @@ __device__ __forceinline__ void shard_merge(const float4* gathered, int G, int r
 // one warp per sequence (gamma <= 32)
 __global__ void shard_accept_kernel(const float4* gathered, int G, int B, int gamma, const float* r, long long r_sb,
                                     unsigned char* accept_mask, float* sel_p, float* sel_q, long long* accepted_len,
-                                    unsigned char* all_accepted, ShardPlan* plan) {
+                                    unsigned char* all_accepted, ShardPlan* plan, const ShardXchg X) {
+  if (X.peers != nullptr) {
+    xchg_wait(X, kXFlags1);
+    gathered = reinterpret_cast<const float4*>(static_cast<const unsigned char*>(X.peers[X.rank]) + X.off_stats);
+  }
   const int b = blockIdx.x, lane = threadIdx.x;
   const int per_b = 2 * gamma + 1, rows = B * per_b, base = b * per_b;
   int accept = 1;
@@ -203,7 +265,8 @@ struct OpMaxKey2 {
 template <class TIn>
 __global__ void __launch_bounds__(kThreads) shard_sample_kernel(const __grid_constant__ ShardRows S,
                                                                 const ShardPlan* plan, const float* noise,
-                                                                long long noise_sb, ShardPartial* out) {
+                                                                long long noise_sb, ShardPartial* out,
+                                                                const ShardXchg X) {
   __shared__ Xchg xc;
   const int b = blockIdx.y, nslice = gridDim.x;
   const ShardPlan pl = plan[b];
@@ -215,20 +278,21 @@ __global__ void __launch_bounds__(kThreads) shard_sample_kernel(const __grid_con
   const int lo = min(int(blockIdx.x) * per, S.Vs), hi = min(lo + per, S.Vs);
   const float rZp = __frcp_rn(pl.Zp), rZq = __frcp_rn(pl.Zq);
   const float mp = pl.Mp * kShardLog2e, mq = pl.Mq * kShardLog2e;
-  float mass = 0.0f;
-  unsigned long long key = 0ull, bdk = 0ull;
+  float mass = 0.0f, bkey = -1.0f, bdv = -INFINITY;
+  int bidx = 0x7fffffff, bdi = 0x7fffffff;
+  // branch-free per entry; a thread meets its indices in increasing order, so strict ">" keeps the lowest
+  // index of a tie (same arithmetic as the fused path's sample kernel: __fdividef race keys)
   auto one = [&](float xp, float xq, float e, int i) {
     float d = ex2f(fmaf(scale_logit(xp, S.t_temp), kShardLog2e, -mp)) * rZp;
     if (!pl.bonus) d -= ex2f(fmaf(scale_logit(xq, S.d_temp), kShardLog2e, -mq)) * rZq;
-    const unsigned gi = 0xffffffffu - unsigned(S.v_begin + i);
-    if (d > 0.0f) {
-      mass += d;
-      const unsigned long long k = ((unsigned long long)__float_as_uint(__fdiv_rn(d, e)) << 32) | gi;
-      key = k > key ? k : key;
-    }
-    const float dz = (d == d && fabsf(d) != INFINITY) ? d : 0.0f;
-    const unsigned long long k2 = ((unsigned long long)okey(dz) << 32) | gi;
-    bdk = k2 > bdk ? k2 : bdk;
+    const bool pos = d > 0.0f;
+    mass += pos ? d : 0.0f;
+    const float k = pos ? __fdividef(d, e) : -1.0f;
+    const bool bk = k > bkey;
+    bkey = bk ? k : bkey, bidx = bk ? i : bidx;
+    const float dz = (fabsf(d) < INFINITY) ? d : 0.0f;  // NaN and +-inf count as 0
+    const bool bd = dz > bdv;
+    bdv = bd ? dz : bdv, bdi = bd ? i : bdi;
   };
   const bool vec = row_vec8(prow, S.Vs) && row_vec8(qrow, S.Vs) && (reinterpret_cast<uintptr_t>(nz) & 31) == 0;
   if (vec) {
@@ -244,6 +308,11 @@ __global__ void __launch_bounds__(kThreads) shard_sample_kernel(const __grid_con
     for (int i = lo + threadIdx.x; i < hi; i += kThreads)
       one(to_f32(prow[i]), pl.bonus ? 0.0f : to_f32(qrow[i]), nz[i], i);
   }
+  const unsigned long long key =
+      bidx == 0x7fffffff ? 0ull
+                         : ((unsigned long long)__float_as_uint(bkey) << 32) | (0xffffffffu - unsigned(S.v_begin + bidx));
+  const unsigned long long bdk =
+      bdi == 0x7fffffff ? 0ull : ((unsigned long long)okey(bdv) << 32) | (0xffffffffu - unsigned(S.v_begin + bdi));
   mass = block_allreduce(mass, OpSumF(), &xc);
   const uint4 kk = block_allreduce(make_uint4(unsigned(key >> 32), unsigned(key), unsigned(bdk >> 32), unsigned(bdk)),
                                    OpMaxKey2(), &xc);
@@ -252,23 +321,42 @@ __global__ void __launch_bounds__(kThreads) shard_sample_kernel(const __grid_con
     p.mass = mass, p.pad = 0u;
     p.key = ((unsigned long long)kk.x << 32) | kk.y;
     p.bd = ((unsigned long long)kk.z << 32) | kk.w;
-    out[(long long)b * nslice + blockIdx.x] = p;
+    if (X.peers == nullptr) {
+      out[(long long)b * nslice + blockIdx.x] = p;
+    } else {
+      const long long slot = ((long long)X.rank * gridDim.y + b) * nslice + blockIdx.x;
+      for (int g = 0; g < X.world; ++g)
+        reinterpret_cast<ShardPartial*>(static_cast<unsigned char*>(X.peers[g]) + X.off_partial)[slot] = p;
+      xchg_publish(X, kXFlags2, kXCnt2, gridDim.x * gridDim.y);
+    }
   }
 }
 
-__global__ void shard_finish_kernel(const ShardPartial* gathered, int G, int B, int nslice, long long* token) {
-  const int b = blockIdx.x * blockDim.x + threadIdx.x;
-  if (b >= B) return;
-  float mass = 0.0f;
-  unsigned long long key = 0ull, bd = 0ull;
-  for (int g = 0; g < G * nslice; ++g) {  // rank-major, then slice: the same order on every rank
-    const ShardPartial p = gathered[((long long)(g / nslice) * B + b) * nslice + (g % nslice)];
-    mass += p.mass;
-    key = p.key > key ? p.key : key;
-    bd = p.bd > bd ? p.bd : bd;
+__global__ void shard_finish_kernel(const ShardPartial* gathered, int G, int B, int nslice, long long* token,
+                                    const ShardXchg X) {
+  if (X.peers != nullptr) {  // (one block in this mode: it closes the step)
+    xchg_wait(X, kXFlags2);
+    gathered = reinterpret_cast<const ShardPartial*>(static_cast<const unsigned char*>(X.peers[X.rank]) + X.off_partial);
   }
-  const unsigned long long win = (mass > 0.0f && key != 0ull) ? key : bd;
-  token[b] = win == 0ull ? 0 : (long long)(0xffffffffu - unsigned(win & 0xffffffffull));
+  for (int b = blockIdx.x * blockDim.x + threadIdx.x; b < B; b += gridDim.x * blockDim.x) {
+    float mass = 0.0f;
+    unsigned long long key = 0ull, bd = 0ull;
+    for (int g = 0; g < G * nslice; ++g) {  // rank-major, then slice: the same order on every rank
+      const ShardPartial p = gathered[((long long)(g / nslice) * B + b) * nslice + (g % nslice)];
+      mass += p.mass;
+      key = p.key > key ? p.key : key;
+      bd = p.bd > bd ? p.bd : bd;
+    }
+    const unsigned long long win = (mass > 0.0f && key != 0ull) ? key : bd;
+    token[b] = win == 0ull ? 0 : (long long)(0xffffffffu - unsigned(win & 0xffffffffull));
+  }
+  if (X.peers != nullptr) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      unsigned* step = reinterpret_cast<unsigned*>(static_cast<unsigned char*>(X.peers[X.rank]) + kXStep);
+      *step = *step + 1u;  // the next step's kernels (stream order) publish and wait for step + 1
+    }
+  }
 }
 
 }  // namespace duodec

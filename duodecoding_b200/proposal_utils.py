@@ -43,9 +43,10 @@ class _StageHistory:
 
 
 def build_draft_probs_override(cache, stage_start_len: int, rebuilt_draft_probs: Optional[torch.Tensor],
-                               lazy: bool = False) -> Optional[torch.Tensor]:
-    """src/proposal_utils.py:14-27.  ``lazy=True`` returns the copy-free view above (same indexing
-    results for everything the verification ops read); the default matches the reference's tensor."""
+                               lazy: bool = True) -> Optional[torch.Tensor]:
+    """src/proposal_utils.py:14-27.  By default the copy-free view above is returned: every access the
+    verification ops make (``.shape[1]``, ``[:, a:b, :]`` with a >= P-1, ``[:, n, :V]``) gives the tensor the
+    reference's ``cat`` would give, without copying the history; ``lazy=False`` builds the reference's tensor."""
     if rebuilt_draft_probs is None:
         return None
     if lazy:

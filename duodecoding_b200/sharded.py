@@ -46,56 +46,71 @@ class _CudaBackend:
     def _rows(self, t):
         return (t.data_ptr(), t.stride(0), t.stride(1)) if t is not None and t.numel() else (None, 0, 0)
 
-    def row_stats(self, draft, target, tokens, v_begin, t_temp, d_temp):
+    def row_stats(self, draft, target, tokens, v_begin, t_temp, d_temp, stats=None, xchg=None):
         B, gamma = tokens.shape
         self.ops._need_cuda(draft, target, tokens)
-        stats = torch.empty((B * (2 * gamma + 1), 4), dtype=torch.float32, device=target.device)
+        if stats is None and xchg is None:
+            stats = torch.empty((B * (2 * gamma + 1), 4), dtype=torch.float32, device=target.device)
         dp, dsb, dss = self._rows(draft)
         tp, tsb, tss = self._rows(target)
         with torch.cuda.device(target.device):
             self.check(self.lib.duodec_shard_stats(dp, tp, self.ops._code(target), dsb, dss, tsb, tss, B, gamma,
                                                    target.shape[-1], int(v_begin), tokens.data_ptr(),
                                                    tokens.stride(0) if gamma else 0, float(t_temp), float(d_temp),
-                                                   stats.data_ptr(), self.ops._stream()), "duodec_shard_stats")
+                                                   stats.data_ptr() if stats is not None else None, xchg,
+                                                   self.ops._stream()), "duodec_shard_stats")
         return stats
 
-    def accept(self, gathered, B, gamma, r):
-        dev = gathered.device
-        out = {
-            "accept_mask": torch.empty((B, gamma), dtype=torch.bool, device=dev),
-            "selected_target_p": torch.empty((B, gamma), dtype=torch.float32, device=dev),
-            "selected_draft_p": torch.empty((B, gamma), dtype=torch.float32, device=dev),
-            "accepted_len": torch.empty((B,), dtype=torch.int64, device=dev),
-            "all_accepted": torch.empty((B,), dtype=torch.bool, device=dev),
-        }
-        plan = torch.empty((B, self.PLAN), dtype=torch.uint8, device=dev)
+    def accept(self, gathered, B, gamma, r, out=None, plan=None, xchg=None, world=None):
+        dev = r.device if gathered is None else gathered.device
+        if out is None:
+            out = {
+                "accept_mask": torch.empty((B, gamma), dtype=torch.bool, device=dev),
+                "selected_target_p": torch.empty((B, gamma), dtype=torch.float32, device=dev),
+                "selected_draft_p": torch.empty((B, gamma), dtype=torch.float32, device=dev),
+                "accepted_len": torch.empty((B,), dtype=torch.int64, device=dev),
+                "all_accepted": torch.empty((B,), dtype=torch.bool, device=dev),
+            }
+        if plan is None:
+            plan = torch.empty((B, self.PLAN), dtype=torch.uint8, device=dev)
         with torch.cuda.device(dev):
-            self.check(self.lib.duodec_shard_accept(gathered.data_ptr(), gathered.shape[0], B, gamma, r.data_ptr(),
+            self.check(self.lib.duodec_shard_accept(gathered.data_ptr() if gathered is not None else None,
+                                                    world if gathered is None else gathered.shape[0], B, gamma,
+                                                    r.data_ptr(),
                                                     r.stride(0) if gamma else 0, out["accept_mask"].data_ptr(),
                                                     out["selected_target_p"].data_ptr(),
                                                     out["selected_draft_p"].data_ptr(), out["accepted_len"].data_ptr(),
-                                                    out["all_accepted"].data_ptr(), plan.data_ptr(),
+                                                    out["all_accepted"].data_ptr(), plan.data_ptr(), xchg,
                                                     self.ops._stream()), "duodec_shard_accept")
         return out, plan
 
-    def sample_partial(self, draft, target, plan, noise, v_begin, t_temp, d_temp, gamma):
+    @staticmethod
+    def nslice(B, Vs):
+        return max(1, min(-(-Vs // 4096), -(-592 // max(B, 1))))  # >= 4 blocks per SM in total
+
+    def sample_partial(self, draft, target, plan, noise, v_begin, t_temp, d_temp, gamma, partial=None, xchg=None):
         B = target.shape[0]
-        nslice = max(1, min(-(-target.shape[-1] // 4096), -(-592 // max(B, 1))))  # >= 4 blocks per SM in total
-        partial = torch.empty((B, nslice, self.PARTIAL), dtype=torch.uint8, device=target.device)
+        nslice = self.nslice(B, target.shape[-1])
+        if partial is None and xchg is None:
+            partial = torch.empty((B, nslice, self.PARTIAL), dtype=torch.uint8, device=target.device)
         dp, dsb, dss = self._rows(draft)
         tp, tsb, tss = self._rows(target)
         with torch.cuda.device(target.device):
             self.check(self.lib.duodec_shard_sample(dp, tp, self.ops._code(target), dsb, dss, tsb, tss, B, gamma,
                                                     target.shape[-1], int(v_begin), float(t_temp), float(d_temp),
                                                     plan.data_ptr(), noise.data_ptr(), noise.stride(0), nslice,
-                                                    partial.data_ptr(), self.ops._stream()), "duodec_shard_sample")
+                                                    partial.data_ptr() if partial is not None else None, xchg,
+                                                    self.ops._stream()), "duodec_shard_sample")
         return partial
 
-    def finish(self, gathered, B):
-        token = torch.empty((B,), dtype=torch.int64, device=gathered.device)
-        with torch.cuda.device(gathered.device):
-            self.check(self.lib.duodec_shard_finish(gathered.data_ptr(), gathered.shape[0], B, gathered.shape[2],
-                                                    token.data_ptr(),
+    def finish(self, gathered, B, token=None, xchg=None, world=None, nslice=None):
+        if token is None:
+            token = torch.empty((B,), dtype=torch.int64, device=gathered.device)
+        with torch.cuda.device(token.device):
+            self.check(self.lib.duodec_shard_finish(gathered.data_ptr() if gathered is not None else None,
+                                                    world if gathered is None else gathered.shape[0], B,
+                                                    nslice if gathered is None else gathered.shape[2],
+                                                    token.data_ptr(), xchg,
                                                     self.ops._stream()), "duodec_shard_finish")
         return token
 
@@ -103,7 +118,8 @@ class _CudaBackend:
 class ShardedVerifier:
     """Verification step over vocabulary slices; call :meth:`verify` with THIS rank's slices."""
 
-    def __init__(self, V: int, rank: Optional[int] = None, world: Optional[int] = None, group=None, backend=None):
+    def __init__(self, V: int, rank: Optional[int] = None, world: Optional[int] = None, group=None, backend=None,
+                 fused_exchange: bool = True):
         self.group = group
         self.world = dist.get_world_size(group) if world is None else int(world)
         self.rank = dist.get_rank(group) if rank is None else int(rank)
@@ -115,33 +131,180 @@ class ShardedVerifier:
             backend = _CudaBackend()
         self.backend = backend
         self.collectives = 0
+        self.use_graphs = True
+        self.fused = fused_exchange and self.world > 1 and isinstance(backend, _CudaBackend)
+        self._bufs: dict = {}
+        self._graphs: dict = {}
+        self._symm: dict = {}
 
     def slice_of(self, full: torch.Tensor) -> torch.Tensor:
         """This rank's columns of a [..., V] tensor (what a sharded LM head would have produced)."""
         return full[..., self.v_begin:self.v_end]
 
-    def _all_gather(self, local: torch.Tensor) -> torch.Tensor:
+    def _all_gather(self, local: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         if self.world == 1:
             return local.unsqueeze(0)
         local = local.contiguous()
-        out = torch.empty((self.world * local.shape[0],) + tuple(local.shape[1:]), dtype=local.dtype,
-                          device=local.device)
-        dist.all_gather_into_tensor(out, local, group=self.group)  # rank-major concatenation along dim 0
+        if out is None:
+            out = torch.empty((self.world * local.shape[0],) + tuple(local.shape[1:]), dtype=local.dtype,
+                              device=local.device)
+        dist.all_gather_into_tensor(out.view((self.world * local.shape[0],) + tuple(local.shape[1:])), local,
+                                    group=self.group)  # rank-major concatenation along dim 0
         self.collectives += 1
         return out.view((self.world,) + tuple(local.shape))
 
+    @property
+    def exchange_kind(self) -> str:
+        if self.world == 1:
+            return "none (one rank)"
+        return ("fused: peer stores + release/acquire flags over symmetric memory, inside the kernels" if self.fused
+                else "nccl all_gather_into_tensor (captured in the step's CUDA graph)")
+
+    @property
+    def exchanges_per_step(self) -> int:
+        return 2 if self.world > 1 else 0
+
+    def _symmetric(self, B: int, gamma: int, Vs: int, dev: torch.device):
+        """Peer-mapped exchange buffer of this shape (torch symmetric memory: CUDA VMM handles exchanged over the
+        process group, every rank maps every peer's buffer) and the duodec_shard_xchg that describes it."""
+        key = (B, gamma, Vs, dev.index)
+        ent = self._symm.get(key)
+        if ent is None:
+            import torch.distributed._symmetric_memory as symm_mem
+            from ._lib import ShardXchg
+            rows, W = B * (2 * gamma + 1), self.world
+            nslice = self.backend.nslice(B, Vs)
+            off_stats = 1024
+            off_partial = off_stats + ((W * rows * 16 + 127) // 128) * 128
+            nbytes = off_partial + W * B * nslice * 24
+            t = symm_mem.empty(nbytes, dtype=torch.uint8, device=dev)
+            t.zero_()
+            hdl = symm_mem.rendezvous(t, self.group if self.group is not None else dist.group.WORLD)
+            torch.cuda.synchronize(dev)
+            dist.barrier(group=self.group)  # every header is zero before anybody publishes
+            x = ShardXchg(hdl.buffer_ptrs_dev, self.rank, W, off_stats, off_partial)
+            ent = (t, hdl, x, nslice)
+            self._symm[key] = ent
+        return ent
+
+    def _buffers(self, B: int, gamma: int, Vs: int, dev: torch.device) -> dict:
+        """Every intermediate of a step, allocated once per (B, gamma, slice width): the step itself allocates
+        nothing, so it can be captured in a CUDA graph."""
+        key = (B, gamma, Vs, dev.index)
+        buf = self._bufs.get(key)
+        if buf is None:
+            rows, W = B * (2 * gamma + 1), self.world
+            nslice = getattr(self.backend, "nslice", lambda b, v: 1)(B, Vs)
+            e = lambda shape, dt: torch.empty(shape, dtype=dt, device=dev)  # noqa: E731
+            buf = {
+                "stats": e((rows, 4), torch.float32), "gstats": e((W, rows, 4), torch.float32),
+                "plan": e((B, 32), torch.uint8), "partial": e((B, nslice, 24), torch.uint8),
+                "gpartial": e((W, B, nslice, 24), torch.uint8), "token": e((B,), torch.int64),
+                "out": {"accept_mask": e((B, gamma), torch.bool), "selected_target_p": e((B, gamma), torch.float32),
+                        "selected_draft_p": e((B, gamma), torch.float32), "accepted_len": e((B,), torch.int64),
+                        "all_accepted": e((B,), torch.bool)},
+            }
+            self._bufs[key] = buf
+        return buf
+
+    def _step(self, draft, target, tokens, r, noise, temperature, d_temp, buf=None):
+        B, gamma = tokens.shape
+        be = self.backend
+        if buf is None:  # injected test backends: plain allocating calls
+            stats = be.row_stats(draft, target, tokens, self.v_begin, temperature, d_temp)
+            out, plan = be.accept(self._all_gather(stats), B, gamma, r)
+            partial = be.sample_partial(draft, target, plan, noise, self.v_begin, temperature, d_temp, gamma)
+            out["token"] = be.finish(self._all_gather(partial), B)
+            return out
+        if self.fused and self.world > 1:
+            import ctypes
+            _, _, x, nslice = self._symmetric(B, gamma, target.shape[-1], target.device)
+            xp = ctypes.byref(x)
+            be.row_stats(draft, target, tokens, self.v_begin, temperature, d_temp, xchg=xp)
+            out, plan = be.accept(None, B, gamma, r, out=buf["out"], plan=buf["plan"], xchg=xp, world=self.world)
+            be.sample_partial(draft, target, plan, noise, self.v_begin, temperature, d_temp, gamma, xchg=xp)
+            out = dict(out)
+            out["token"] = be.finish(None, B, token=buf["token"], xchg=xp, world=self.world, nslice=nslice)
+            return out
+        stats = be.row_stats(draft, target, tokens, self.v_begin, temperature, d_temp, stats=buf["stats"])
+        out, plan = be.accept(self._all_gather(stats, buf["gstats"]), B, gamma, r, out=buf["out"], plan=buf["plan"])
+        partial = be.sample_partial(draft, target, plan, noise, self.v_begin, temperature, d_temp, gamma,
+                                    partial=buf["partial"])
+        out = dict(out)
+        out["token"] = be.finish(self._all_gather(partial, buf["gpartial"]), B, token=buf["token"])
+        return out
+
+    def phase_times(self, inputs, temperature: float = 1.0, reps: int = 10) -> Optional[dict]:
+        """Measurement hook: microseconds of each kernel / exchange of a step (eager launches, CUDA events)."""
+        if not isinstance(self.backend, _CudaBackend) or self.fused:
+            return None  # (with the fused exchange the kernels of a step wait on the peers: no stand-alone phases)
+        draft, target, tokens, r, noise = inputs
+        B, gamma = tokens.shape
+        be, buf = self.backend, self._buffers(B, gamma, target.shape[-1], target.device)
+        phases = [
+            ("stats", lambda: be.row_stats(draft, target, tokens, self.v_begin, temperature, temperature, stats=buf["stats"])),
+            ("exchange1", lambda: self._all_gather(buf["stats"], buf["gstats"])),
+            ("accept", lambda: be.accept(self._all_gather(buf["stats"], buf["gstats"]) if self.world == 1 else buf["gstats"],
+                                         B, gamma, r, out=buf["out"], plan=buf["plan"])),
+            ("sample", lambda: be.sample_partial(draft, target, buf["plan"], noise, self.v_begin, temperature,
+                                                 temperature, gamma, partial=buf["partial"])),
+            ("exchange2", lambda: self._all_gather(buf["partial"], buf["gpartial"])),
+            ("finish", lambda: be.finish(buf["gpartial"] if self.world > 1 else buf["partial"].unsqueeze(0), B,
+                                         token=buf["token"])),
+        ]
+        self._step(draft, target, tokens, r, noise, temperature, temperature, buf)
+        out = {}
+        for name, fn in phases:
+            fn()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(reps):
+                fn()
+            e1.record()
+            torch.cuda.synchronize()
+            out[name] = e0.elapsed_time(e1) * 1e3 / reps
+        return out
+
     def verify(self, draft: torch.Tensor, target: torch.Tensor, tokens: torch.Tensor, r: torch.Tensor,
-               noise: torch.Tensor, temperature: float = 1.0,
-               draft_temperature: Optional[float] = None) -> Dict[str, torch.Tensor]:
+               noise: torch.Tensor, temperature: float = 1.0, draft_temperature: Optional[float] = None,
+               graph: Optional[bool] = None) -> Dict[str, torch.Tensor]:
         """draft [B, >=gamma, Vs], target [B, >=gamma+1, Vs], noise [B, Vs]: this rank's slices;
-        tokens [B, gamma] (global ids), r [B, gamma]: replicated.  Returns the dict of verify_fused."""
+        tokens [B, gamma] (global ids), r [B, gamma]: replicated.  Returns the dict of verify_fused (tensors
+        owned by the verifier: valid until the next call with the same shapes).
+
+        With the CUDA backend the four kernels and the two exchanges of a step are captured in ONE CUDA graph
+        per set of input buffers (the second call with the same tensors replays it; `graph=False` disables)."""
         B, gamma = tokens.shape
         d_temp = temperature if draft_temperature is None else draft_temperature
         if target.shape[-1] != self.v_end - self.v_begin:
             raise ValueError("target slice width does not match this rank's vocabulary slice")
-        be = self.backend
-        stats = be.row_stats(draft, target, tokens, self.v_begin, temperature, d_temp)
-        out, plan = be.accept(self._all_gather(stats), B, gamma, r)
-        partial = be.sample_partial(draft, target, plan, noise, self.v_begin, temperature, d_temp, gamma)
-        out["token"] = be.finish(self._all_gather(partial), B)
-        return out
+        if not isinstance(self.backend, _CudaBackend):
+            return self._step(draft, target, tokens, r, noise, temperature, d_temp)
+        buf = self._buffers(B, gamma, target.shape[-1], target.device)
+        if graph is None:
+            graph = self.use_graphs
+        if not graph or gamma == 0:
+            return self._step(draft, target, tokens, r, noise, temperature, d_temp, buf)
+        key = (draft.data_ptr(), target.data_ptr(), tokens.data_ptr(), r.data_ptr(), noise.data_ptr(),
+               tuple(draft.stride()), tuple(target.stride()), B, gamma, target.shape[-1], float(temperature),
+               float(d_temp))
+        ent = self._graphs.get(key)
+        if ent is None:
+            # first call with these buffers: one eager step (also the warm-up NCCL wants), then the capture
+            out = self._step(draft, target, tokens, r, noise, temperature, d_temp, buf)
+            torch.cuda.current_stream().synchronize()
+            g = torch.cuda.CUDAGraph()
+            side = torch.cuda.Stream(device=target.device)
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                with torch.cuda.graph(g, stream=side):
+                    out = self._step(draft, target, tokens, r, noise, temperature, d_temp, buf)
+            torch.cuda.current_stream().wait_stream(side)
+            if len(self._graphs) >= 16:
+                self._graphs.pop(next(iter(self._graphs)))
+            # the input tensors are kept alive with the graph that reads them
+            self._graphs[key] = (g, out, (draft, target, tokens, r, noise))
+            ent = self._graphs[key]
+        ent[0].replay()
+        return ent[1]

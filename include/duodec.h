@@ -163,17 +163,32 @@ int duodec_kv_truncate(int32_t* seq_len, const int64_t* end_pos_vec, int64_t end
  *            residual mass, best race key, zero-mass fallback key; gathered as [world, B, nslice] */
 #define DUODEC_SHARD_PLAN_BYTES 32
 #define DUODEC_SHARD_PARTIAL_BYTES 24
+/* Optional fused exchange (NULL: the caller gathers, e.g. with NCCL).  `peers` is a DEVICE array of `world`
+ * base pointers of peer-mapped (symmetric) buffers, own buffer at [rank]; every buffer starts with a 1 KB
+ * header (zero-filled once: flags, block counters, step number) followed by the gather areas at the given
+ * byte offsets: gstats [world][B*(2*gamma+1)] x 16 B and gpartial [world][B*nslice] x 24 B.  With it
+ * duodec_shard_stats / _sample store their results into every peer's areas and publish the step;
+ * duodec_shard_accept / _finish wait for all ranks and read their own areas (the stats / gathered / partial
+ * pointers may then be NULL).  All ranks must issue the four calls of a step in the same order. */
+typedef struct {
+  void* const* peers;
+  int rank, world;
+  int64_t off_stats, off_partial;
+} duodec_shard_xchg;
+#define DUODEC_SHARD_XCHG_HEADER 1024
 int duodec_shard_stats(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss, int64_t t_sb,
                        int64_t t_ss, int B, int gamma, int Vs, int v_begin, const int64_t* tokens, int64_t tok_sb,
-                       float temperature, float draft_temperature, float* stats, void* stream);
+                       float temperature, float draft_temperature, float* stats, const duodec_shard_xchg* xchg,
+                       void* stream);
 int duodec_shard_accept(const float* gathered_stats, int world, int B, int gamma, const float* r, int64_t r_sb,
                         uint8_t* accept_mask, float* sel_target_p, float* sel_draft_p, int64_t* accepted_len,
-                        uint8_t* all_accepted, void* plan, void* stream);
+                        uint8_t* all_accepted, void* plan, const duodec_shard_xchg* xchg, void* stream);
 int duodec_shard_sample(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss, int64_t t_sb,
                         int64_t t_ss, int B, int gamma, int Vs, int v_begin, float temperature,
                         float draft_temperature, const void* plan, const float* noise, int64_t noise_sb,
-                        int nslice, void* partial, void* stream);
-int duodec_shard_finish(const void* gathered_partials, int world, int B, int nslice, int64_t* token, void* stream);
+                        int nslice, void* partial, const duodec_shard_xchg* xchg, void* stream);
+int duodec_shard_finish(const void* gathered_partials, int world, int B, int nslice, int64_t* token,
+                        const duodec_shard_xchg* xchg, void* stream);
 
 #ifdef __cplusplus
 }

@@ -390,13 +390,14 @@ def fused_verify(
     mask = torch.zeros(B, g, dtype=torch.bool)
     sel_p = torch.zeros(B, g, dtype=torch.float32)
     sel_q = torch.zeros(B, g, dtype=torch.float32)
+    # one norm_logits call per model over [B, gamma(+1), V], as the reference issues it (src/model_gpu.py:253)
+    if inputs_are_probs:
+        q_all, p_all = draft_logits[:, :g], target_logits[:, : g + 1]
+    else:
+        q_all = norm_logits(draft_logits[:, :g], dT, dk, dp)
+        p_all = norm_logits(target_logits[:, : g + 1], temperature, top_k, top_p)
     for b in range(B):
-        if inputs_are_probs:
-            q = draft_logits[b : b + 1, :g]
-            p = target_logits[b : b + 1, : g + 1]
-        else:
-            q = norm_logits(draft_logits[b : b + 1, :g], dT, dk, dp)
-            p = norm_logits(target_logits[b : b + 1, : g + 1], temperature, top_k, top_p)
+        q, p = q_all[b : b + 1], p_all[b : b + 1]
         if q.shape[-1] != p.shape[-1]:
             # the accept gather happens on draft-vocab indices in both tensors
             out = accept_rows(q[..., :vlim], p[..., :vlim], tokens[b : b + 1], r[b : b + 1])

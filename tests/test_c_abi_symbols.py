@@ -29,5 +29,5 @@ def test_argument_errors_come_back_as_codes_without_a_gpu():
     lib = _lib.lib
     assert lib.duodec_norm_logits(None, 0, 0, None, 0, 0, 4, 0, 1.0, 0, 0.0, None) == -1      # V <= 0
     assert lib.duodec_norm_logits(None, 0, 0, None, 0, 0, 0, 16, 1.0, 0, 0.0, None) == 0      # no rows: no-op
-    assert lib.duodec_shard_finish(None, 0, 4, 1, None, None) == -1                           # world <= 0
+    assert lib.duodec_shard_finish(None, 0, 4, 1, None, None, None) == -1                           # world <= 0
     assert lib.duodec_verify_workspace_bytes(64, 4) > 0 and lib.duodec_team_size(32000, 2) >= 1

@@ -97,7 +97,7 @@ def test_finalize_positions():  # test/test_engine_finalize_verification.py:42-7
 def test_lazy_stage_history_reads_like_the_cat():
     cache = FakeCache(torch.rand(2, 10, 7), 7)
     rebuilt = torch.rand(2, 3, 7)
-    full = proposal_utils.build_draft_probs_override(cache, 6, rebuilt)
+    full = proposal_utils.build_draft_probs_override(cache, 6, rebuilt, lazy=False)
     lazy = proposal_utils.build_draft_probs_override(cache, 6, rebuilt, lazy=True)
     assert full.shape == lazy.shape == (2, 8, 7)
     assert torch.equal(lazy[:, 5:8, :], full[:, 5:8, :]) and torch.equal(lazy[:, 6, :4], full[:, 6, :4])

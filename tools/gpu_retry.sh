@@ -5,7 +5,7 @@
 T=$1; CMD=$2; LOG=${3:-/tmp/gpurun_retry.log}
 for i in $(seq 1 60); do
   while [ -e /tmp/repo.lock ]; do sleep 5; done
-  /usr/local/graft/bin/gpurun --timeout "$T" -- "$CMD" > "$LOG" 2>&1
+  /usr/local/graft/bin/gpurun ${GPUS:+--gpus $GPUS} --timeout "$T" -- "$CMD" > "$LOG" 2>&1
   rc=$?
   if [ $rc -ne 3 ]; then exit $rc; fi
   sleep 20
