@@ -156,6 +156,19 @@ def hbm_peak():
     return 6650.0, "B200_PROFILING.md fallback (of fallback)"
 
 
+def finish_ranks(dist):
+    """End of a multi-rank run: one last barrier, then leave without tearing the communicators down (a teardown
+    that hangs would hold eight GPUs until the caller's timeout)."""
+    try:
+        torch.cuda.synchronize()
+        dist.barrier()
+        torch.cuda.synchronize()
+    finally:
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
+
+
 def dist_env():
     return int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0"))
 
@@ -482,8 +495,7 @@ def run_ours(args):
     if world > 1:
         dist.barrier()
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
+        finish_ranks(dist)
         return 0
 
     # ---- roofline of the dominant kernel
@@ -535,7 +547,7 @@ def run_ours(args):
         line["c5"] = c5
     emit(line)
     if world > 1:
-        dist.destroy_process_group()
+        finish_ranks(dist)
     return 0
 
 
@@ -642,7 +654,7 @@ def run_c5(args):
         }
         emit(line)
     if world > 1:
-        dist.destroy_process_group()
+        finish_ranks(dist)
     return 0
 
 

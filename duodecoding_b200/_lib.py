@@ -81,7 +81,8 @@ SIGNATURES = {
 class ShardXchg(ctypes.Structure):
     """duodec_shard_xchg (include/duodec.h): the fused peer-memory exchange of the sharded step."""
 
-    _fields_ = [("peers", c_void_p), ("rank", c_int), ("world", c_int), ("off_stats", c_i64), ("off_partial", c_i64)]
+    _fields_ = [("peers", c_void_p), ("rank", c_int), ("world", c_int), ("off_stats", c_i64), ("off_partial", c_i64),
+                ("mode", c_int)]
 
 
 class DuodecError(RuntimeError):

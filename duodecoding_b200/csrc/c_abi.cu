@@ -389,8 +389,8 @@ static bool xchg_ok(const duodec_shard_xchg* x) {
                           x->off_partial % 8 == 0);
 }
 static ShardXchg xchg_of(const duodec_shard_xchg* x) {
-  if (x == nullptr) return ShardXchg{nullptr, 0, 1, 0, 0};
-  return ShardXchg{x->peers, x->rank, x->world, x->off_stats, x->off_partial};
+  if (x == nullptr) return ShardXchg{nullptr, 0, 1, 0, 0, 0};
+  return ShardXchg{x->peers, x->rank, x->world, x->off_stats, x->off_partial, x->mode};
 }
 
 int duodec_shard_stats(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss, int64_t t_sb,

@@ -75,6 +75,7 @@ struct ShardXchg {
   void* const* peers;  // device array of `world` base pointers (own base at [rank]); nullptr: no fused exchange
   int rank, world;
   long long off_stats, off_partial;  // byte offsets of gstats [world][rows] float4 / gpartial [world][B * nslice]
+  int mode;  // 0: every block stores its result into every peer; 1: the last block copies the rank's slab to the peers
 };
 __device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
   unsigned v;
@@ -84,14 +85,54 @@ __device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
 __device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
-// thread 0 of every block, after its stores into the peers: the last block of the grid publishes the step
-__device__ __forceinline__ void xchg_publish(const ShardXchg& X, int flags_off, int cnt_off, unsigned nblocks) {
-  __threadfence_system();
+// Whole block, after its thread 0 stored the block's result into the rank's OWN slab of the gather area: the block
+// that finishes last copies the slab (slab_bytes, a multiple of 8) into every peer's area with coalesced stores,
+// then publishes the step to a flag in every peer.  One system-scope fence per grid, not per block.
+__device__ __forceinline__ void xchg_publish(const ShardXchg& X, int flags_off, int cnt_off, unsigned nblocks,
+                                             long long area_off, long long slab_bytes, long long item_off,
+                                             int item_bytes) {
+  __shared__ int s_last;
   unsigned char* self = static_cast<unsigned char*>(X.peers[X.rank]);
-  unsigned* cnt = reinterpret_cast<unsigned*>(self + cnt_off);
-  if (atomicAdd(cnt, 1u) == nblocks - 1u) {
-    *cnt = 0u;  // (every block of this grid has counted: ready for the next step)
-    __threadfence_system();
+  if (X.mode == 0) {  // every block pushes its own item (at item_off inside the rank's slab) to every peer
+    if (threadIdx.x == 0) {
+      const unsigned long long* src =
+          reinterpret_cast<const unsigned long long*>(self + area_off + X.rank * slab_bytes + item_off);
+      for (int g = 0; g < X.world; ++g) {
+        if (g == X.rank) continue;
+        unsigned long long* dst = reinterpret_cast<unsigned long long*>(static_cast<unsigned char*>(X.peers[g]) +
+                                                                        area_off + X.rank * slab_bytes + item_off);
+        for (int i = 0; i < item_bytes / 8; ++i) dst[i] = src[i];
+      }
+      __threadfence_system();
+      if (atomicAdd(reinterpret_cast<unsigned*>(self + cnt_off), 1u) == nblocks - 1u) {
+        *reinterpret_cast<unsigned*>(self + cnt_off) = 0u;
+        __threadfence_system();
+        const unsigned epoch = *reinterpret_cast<volatile unsigned*>(self + kXStep) + 1u;
+        for (int g = 0; g < X.world; ++g)
+          st_release_sys(reinterpret_cast<unsigned*>(static_cast<unsigned char*>(X.peers[g]) + flags_off) + X.rank, epoch);
+      }
+    }
+    return;
+  }
+  if (threadIdx.x == 0) {
+    __threadfence();
+    s_last = atomicAdd(reinterpret_cast<unsigned*>(self + cnt_off), 1u) == nblocks - 1u;
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  const unsigned long long* src = reinterpret_cast<const unsigned long long*>(self + area_off + X.rank * slab_bytes);
+  const long long n8 = slab_bytes / 8;
+  for (int g = 0; g < X.world; ++g) {
+    if (g == X.rank) continue;
+    unsigned long long* dst =
+        reinterpret_cast<unsigned long long*>(static_cast<unsigned char*>(X.peers[g]) + area_off + X.rank * slab_bytes);
+    for (long long i = threadIdx.x; i < n8; i += blockDim.x) dst[i] = __ldcg(src + i);
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    *reinterpret_cast<unsigned*>(self + cnt_off) = 0u;  // (every block of this grid has counted: ready for the next step)
     const unsigned epoch = *reinterpret_cast<volatile unsigned*>(self + kXStep) + 1u;
     for (int g = 0; g < X.world; ++g)
       st_release_sys(reinterpret_cast<unsigned*>(static_cast<unsigned char*>(X.peers[g]) + flags_off) + X.rank, epoch);
@@ -175,15 +216,12 @@ __global__ void __launch_bounds__(kThreads) shard_stats_kernel(const __grid_cons
       if (t >= 0 && t < S.Vs) tokx = scale_logit(to_f32(row[t]), temp), has = 1.0f;
     }
     const float4 v = make_float4(acc.m, acc.s, tokx, has);
-    if (X.peers == nullptr) {
-      stats[job] = v;
-    } else {  // straight into every rank's gather buffer, slot [rank][job]
-      const long long slot = (long long)X.rank * gridDim.x + job;
-      for (int g = 0; g < X.world; ++g)
-        reinterpret_cast<float4*>(static_cast<unsigned char*>(X.peers[g]) + X.off_stats)[slot] = v;
-      xchg_publish(X, kXFlags1, kXCnt1, gridDim.x);
-    }
+    if (X.peers == nullptr) stats[job] = v;
+    else  // the rank's own slab of the gather area, slot [rank][job]
+      reinterpret_cast<float4*>(static_cast<unsigned char*>(X.peers[X.rank]) + X.off_stats)[(long long)X.rank * gridDim.x + job] = v;
   }
+  if (X.peers != nullptr)
+    xchg_publish(X, kXFlags1, kXCnt1, gridDim.x, X.off_stats, (long long)gridDim.x * 16, (long long)job * 16, 16);
 }
 
 struct ShardPlan {  // per sequence, written by shard_accept_kernel
@@ -321,15 +359,14 @@ __global__ void __launch_bounds__(kThreads) shard_sample_kernel(const __grid_con
     p.mass = mass, p.pad = 0u;
     p.key = ((unsigned long long)kk.x << 32) | kk.y;
     p.bd = ((unsigned long long)kk.z << 32) | kk.w;
-    if (X.peers == nullptr) {
-      out[(long long)b * nslice + blockIdx.x] = p;
-    } else {
-      const long long slot = ((long long)X.rank * gridDim.y + b) * nslice + blockIdx.x;
-      for (int g = 0; g < X.world; ++g)
-        reinterpret_cast<ShardPartial*>(static_cast<unsigned char*>(X.peers[g]) + X.off_partial)[slot] = p;
-      xchg_publish(X, kXFlags2, kXCnt2, gridDim.x * gridDim.y);
-    }
+    if (X.peers == nullptr) out[(long long)b * nslice + blockIdx.x] = p;
+    else
+      reinterpret_cast<ShardPartial*>(static_cast<unsigned char*>(X.peers[X.rank]) + X.off_partial)
+          [((long long)X.rank * gridDim.y + b) * nslice + blockIdx.x] = p;
   }
+  if (X.peers != nullptr)
+    xchg_publish(X, kXFlags2, kXCnt2, gridDim.x * gridDim.y, X.off_partial, (long long)gridDim.x * gridDim.y * 24,
+                 ((long long)b * nslice + blockIdx.x) * 24, 24);
 }
 
 __global__ void shard_finish_kernel(const ShardPartial* gathered, int G, int B, int nslice, long long* token,

@@ -54,6 +54,107 @@ def _lastdim_contig(t: torch.Tensor) -> torch.Tensor:
     return t if (t.numel() == 0 or t.stride(-1) == 1) else t.contiguous()
 
 
+# --------------------------------------------------------------------------
+# torch.library registration: every kernel launch of this package is a `duodec::` custom op with its outputs
+# annotated as mutated (`Tensor(a!)`), implemented for CUDA by the C-ABI call (ctypes) and for Meta by a
+# no-op - the "thin torch custom-op layer" over libduodec.so.  The functions below prepare views / outputs
+# and then call torch.ops.duodec.*; nothing else in the package launches kernels.
+# --------------------------------------------------------------------------
+_TL = torch.library.Library("duodec", "DEF")
+
+
+def _register(schema: str, fn) -> None:
+    name = schema.split("(")[0]
+    _TL.define(schema)
+    _TL.impl(name, fn, "CUDA")
+    _TL.impl(name, lambda *a, **k: None, "Meta")
+
+
+def _op_norm_logits(logits, out, temperature, top_k, top_p):
+    V = logits.shape[-1]
+    with torch.cuda.device(logits.device):
+        if logits.dim() == 3:
+            check(lib.duodec_norm_logits_batched(
+                logits.data_ptr(), _code(logits), logits.stride(0), logits.stride(1), out.data_ptr(), _code(out),
+                out.stride(0), out.stride(1), logits.shape[0], logits.shape[1], V, float(temperature), int(top_k),
+                float(top_p), _stream()), "duodec_norm_logits_batched")
+        else:
+            check(lib.duodec_norm_logits(
+                logits.data_ptr(), _code(logits), logits.stride(0), out.data_ptr(), _code(out), out.stride(0),
+                logits.shape[0], V, float(temperature), int(top_k), float(top_p), _stream()), "duodec_norm_logits")
+
+
+def _op_verify_fused(dl, tl, tokens, r, noise, T, k, p, dT, dk, dp, flags, accept_mask, sel_p, sel_q, accepted_len,
+                     token, all_accepted, ws):
+    B, gamma = tokens.shape
+    with torch.cuda.device(tl.device):
+        check(lib.duodec_verify_fused(
+            dl.data_ptr(), tl.data_ptr(), _code(tl), dl.stride(0), dl.stride(1), tl.stride(0), tl.stride(1),
+            B, gamma, dl.shape[-1], tl.shape[-1],
+            tokens.data_ptr(), tokens.stride(0) if gamma else 0, r.data_ptr(), r.stride(0) if gamma else 0,
+            noise.data_ptr(), noise.stride(0), float(T), int(k), float(p), float(dT), int(dk), float(dp), int(flags),
+            accept_mask.data_ptr(), sel_p.data_ptr(), sel_q.data_ptr(), accepted_len.data_ptr(), token.data_ptr(),
+            all_accepted.data_ptr(), ws.data_ptr(), ws.numel(), _stream()), "duodec_verify_fused")
+
+
+def _op_accept_probs(dq, tp, tokens, r, V, accept_mask, sel_q, sel_p, accepted_len):
+    B, gamma = tokens.shape
+    with torch.cuda.device(dq.device):
+        check(lib.duodec_accept_probs(
+            dq.data_ptr(), dq.stride(0), dq.stride(1) if gamma else 0, tp.data_ptr(), tp.stride(0),
+            tp.stride(1) if gamma else 0, _code(dq), tokens.data_ptr(), tokens.stride(0) if gamma else 0,
+            r.data_ptr(), r.stride(0) if gamma else 0, B, gamma, int(V), accept_mask.data_ptr(), sel_q.data_ptr(),
+            sel_p.data_ptr(), accepted_len.data_ptr(), _stream()), "duodec_accept_probs")
+
+
+def _op_sample_rows(p, nz, out):
+    with torch.cuda.device(p.device):
+        check(lib.duodec_sample_rows(p.data_ptr(), _code(p), p.stride(0), nz.data_ptr(), nz.stride(0), p.shape[0],
+                                     p.shape[1], out.data_ptr(), _stream()), "duodec_sample_rows")
+
+
+def _op_residual_sample(tp, dq, nz, out):
+    with torch.cuda.device(tp.device):
+        check(lib.duodec_residual_sample(tp.data_ptr(), tp.stride(0), dq.data_ptr(), dq.stride(0), _code(tp),
+                                         nz.data_ptr(), nz.stride(0), tp.shape[0], tp.shape[1], out.data_ptr(),
+                                         _stream()), "duodec_residual_sample")
+
+
+def _op_max_fn(x2, out):
+    with torch.cuda.device(x2.device):
+        check(lib.duodec_max_fn(x2.data_ptr(), _code(x2), x2.stride(0), x2.shape[0], x2.shape[1], out.data_ptr(),
+                                out.stride(0), _stream()), "duodec_max_fn")
+
+
+def _op_topk_rebuild(p2, k, mode, out):
+    with torch.cuda.device(p2.device):
+        check(lib.duodec_topk_rebuild(p2.data_ptr(), _code(p2), p2.stride(0), out.data_ptr(), out.stride(0),
+                                      p2.shape[0], p2.shape[1], int(k), int(mode), _stream()), "duodec_topk_rebuild")
+
+
+def _op_kv_truncate(seq_len, end_vec, end_pos):
+    with torch.cuda.device(seq_len.device):
+        check(lib.duodec_kv_truncate(seq_len.data_ptr(), end_vec.data_ptr() if end_vec is not None else None,
+                                     int(end_pos), seq_len.numel(), _stream()), "duodec_kv_truncate")
+
+
+_register("norm_logits(Tensor logits, Tensor(a!) out, float temperature, int top_k, float top_p) -> ()", _op_norm_logits)
+_register("verify_fused(Tensor draft, Tensor target, Tensor tokens, Tensor r, Tensor noise, float temperature, "
+          "int top_k, float top_p, float draft_temperature, int draft_top_k, float draft_top_p, int flags, "
+          "Tensor(a!) accept_mask, Tensor(b!) sel_target_p, Tensor(c!) sel_draft_p, Tensor(d!) accepted_len, "
+          "Tensor(e!) token, Tensor(f!) all_accepted, Tensor(g!) workspace) -> ()", _op_verify_fused)
+_register("accept_probs(Tensor draft_probs, Tensor target_probs, Tensor tokens, Tensor r, int V, "
+          "Tensor(a!) accept_mask, Tensor(b!) sel_draft_p, Tensor(c!) sel_target_p, Tensor(d!) accepted_len) -> ()",
+          _op_accept_probs)
+_register("sample_rows(Tensor probs, Tensor noise, Tensor(a!) out) -> ()", _op_sample_rows)
+_register("residual_sample(Tensor target_probs, Tensor draft_probs, Tensor noise, Tensor(a!) out) -> ()",
+          _op_residual_sample)
+_register("max_fn(Tensor x, Tensor(a!) out) -> ()", _op_max_fn)
+_register("topk_rebuild(Tensor probs, int k, int mode, Tensor(a!) out) -> ()", _op_topk_rebuild)
+_register("kv_truncate(Tensor(a!) seq_len, Tensor? end_pos_vec, int end_pos) -> ()", _op_kv_truncate)
+_D = torch.ops.duodec
+
+
 def set_team_size(team: int) -> None:
     """Tuning hook: force the thread-block-cluster size (0 = automatic)."""
     lib.duodec_set_team_size(int(team))
@@ -112,17 +213,8 @@ def norm_logits(
     if logits.dim() == 3 and out.dim() == 3 and logits.stride(-1) == 1 and out.stride(-1) == 1 and \
             logits.shape == out.shape:
         # [B, S, V] views with their own batch / row strides (history buffers): one launch, no copy
-        Bn, Sn = logits.shape[0], logits.shape[1]
-        if Bn and Sn:
-            with torch.cuda.device(logits.device):
-                check(
-                    lib.duodec_norm_logits_batched(
-                        logits.data_ptr(), _code(logits), logits.stride(0), logits.stride(1), out.data_ptr(),
-                        _code(out), out.stride(0), out.stride(1), Bn, Sn, V, float(temperature), int(top_k),
-                        float(top_p), _stream(),
-                    ),
-                    "duodec_norm_logits_batched",
-                )
+        if logits.shape[0] and logits.shape[1]:
+            _D.norm_logits(logits, out, float(temperature), int(top_k), float(top_p))
         return out
     x = _rows(logits)
     rows = x.shape[0]
@@ -130,14 +222,7 @@ def norm_logits(
     if o.numel() and (o.stride(-1) != 1 or o.data_ptr() != out.data_ptr()):
         raise ValueError("out must have unit stride along the vocabulary and rows that flatten without a copy")
     if rows:
-        with torch.cuda.device(logits.device):
-            check(
-                lib.duodec_norm_logits(
-                    x.data_ptr(), _code(x), x.stride(0), o.data_ptr(), _code(o), o.stride(0), rows, V,
-                    float(temperature), int(top_k), float(top_p), _stream(),
-                ),
-                "duodec_norm_logits",
-            )
+        _D.norm_logits(x, o, float(temperature), int(top_k), float(top_p))
     return out
 
 
@@ -207,21 +292,10 @@ def verify_fused(
     if B == 0:
         return out
     ws = _workspace(dev, B, gamma)
-    with torch.cuda.device(dev):
-        check(
-            lib.duodec_verify_fused(
-                dl.data_ptr(), tl.data_ptr(), _code(tl), dl.stride(0), dl.stride(1), tl.stride(0), tl.stride(1),
-                B, gamma, Vd, Vt,
-                tokens.data_ptr(), tokens.stride(0) if gamma else 0, r.data_ptr(), r.stride(0) if gamma else 0,
-                noise.data_ptr(), noise.stride(0),
-                float(temperature), int(top_k), float(top_p), float(dT), int(dk), float(dp),
-                (ROW0_RULE if row0_rule else 0) | ((_PATH & 15) << 4) | ((_PHASES & 3) << 8),
-                out["accept_mask"].data_ptr(), out["selected_target_p"].data_ptr(),
-                out["selected_draft_p"].data_ptr(), out["accepted_len"].data_ptr(), out["token"].data_ptr(),
-                out["all_accepted"].data_ptr(), ws.data_ptr(), ws.numel(), _stream(),
-            ),
-            "duodec_verify_fused",
-        )
+    _D.verify_fused(dl, tl, tokens, r, noise, float(temperature), int(top_k), float(top_p), float(dT), int(dk), float(dp),
+                    (ROW0_RULE if row0_rule else 0) | ((_PATH & 15) << 4) | ((_PHASES & 3) << 8),
+                    out["accept_mask"], out["selected_target_p"], out["selected_draft_p"], out["accepted_len"],
+                    out["token"], out["all_accepted"], ws)
     return out
 
 
@@ -252,17 +326,8 @@ def accept_probs(
     }
     if B == 0:
         return out
-    with torch.cuda.device(dev):
-        check(
-            lib.duodec_accept_probs(
-                dq.data_ptr(), dq.stride(0), dq.stride(1) if gamma else 0, tp.data_ptr(), tp.stride(0),
-                tp.stride(1) if gamma else 0, _code(dq), tokens.data_ptr(), tokens.stride(0) if gamma else 0,
-                r.data_ptr(), r.stride(0) if gamma else 0, B, gamma, V, out["accept_mask"].data_ptr(),
-                out["selected_draft_p"].data_ptr(), out["selected_target_p"].data_ptr(),
-                out["accepted_len"].data_ptr(), _stream(),
-            ),
-            "duodec_accept_probs",
-        )
+    _D.accept_probs(dq, tp, tokens, r, V, out["accept_mask"], out["selected_draft_p"], out["selected_target_p"],
+                    out["accepted_len"])
     return out
 
 
@@ -283,12 +348,7 @@ def sample_rows(probs: torch.Tensor, noise: Optional[torch.Tensor] = None) -> to
     nz = _rows(noise.to(torch.float32))
     out = torch.empty((rows,), dtype=torch.int64, device=p.device)
     if rows:
-        with torch.cuda.device(p.device):
-            check(
-                lib.duodec_sample_rows(p.data_ptr(), _code(p), p.stride(0), nz.data_ptr(), nz.stride(0), rows, V,
-                                       out.data_ptr(), _stream()),
-                "duodec_sample_rows",
-            )
+        _D.sample_rows(p, nz, out)
     return out.reshape(*probs.shape[:-1], 1)
 
 
@@ -308,12 +368,7 @@ def residual_sample(target_probs: torch.Tensor, draft_probs: torch.Tensor,
     nz = _rows(noise.to(torch.float32))
     out = torch.empty((rows,), dtype=torch.int64, device=tp.device)
     if rows:
-        with torch.cuda.device(tp.device):
-            check(
-                lib.duodec_residual_sample(tp.data_ptr(), tp.stride(0), dq.data_ptr(), dq.stride(0), _code(tp),
-                                           nz.data_ptr(), nz.stride(0), rows, V, out.data_ptr(), _stream()),
-                "duodec_residual_sample",
-            )
+        _D.residual_sample(tp, dq, nz, out)
     return out.reshape(*target_probs.shape[:-1], 1)
 
 
@@ -326,12 +381,7 @@ def max_fn(x: torch.Tensor) -> torch.Tensor:
     rows, V = x2.shape
     out = torch.empty((rows, V), dtype=torch.float32, device=x.device)
     if rows:
-        with torch.cuda.device(x.device):
-            check(
-                lib.duodec_max_fn(x2.data_ptr(), _code(x2), x2.stride(0), rows, V, out.data_ptr(), out.stride(0),
-                                  _stream()),
-                "duodec_max_fn",
-            )
+        _D.max_fn(x2, out)
     return out.reshape(x.shape)
 
 
@@ -343,12 +393,7 @@ def topk_rebuild(probs: torch.Tensor, k: int, mode: int) -> torch.Tensor:
     rows, V = p2.shape
     out = torch.empty((rows, V), dtype=p2.dtype, device=p2.device)
     if rows:
-        with torch.cuda.device(p2.device):
-            check(
-                lib.duodec_topk_rebuild(p2.data_ptr(), _code(p2), p2.stride(0), out.data_ptr(), out.stride(0), rows,
-                                        V, int(k), int(mode), _stream()),
-                "duodec_topk_rebuild",
-            )
+        _D.topk_rebuild(p2, int(k), int(mode), out)
     return out.reshape(probs.shape).to(probs.dtype)
 
 
@@ -367,10 +412,5 @@ def kv_truncate(seq_len: torch.Tensor, end_pos) -> torch.Tensor:
     else:
         scalar = int(end_pos)
     if B:
-        with torch.cuda.device(seq_len.device):
-            check(
-                lib.duodec_kv_truncate(seq_len.data_ptr(), vec.data_ptr() if vec is not None else None, scalar, B,
-                                       _stream()),
-                "duodec_kv_truncate",
-            )
+        _D.kv_truncate(seq_len, vec, scalar)
     return seq_len

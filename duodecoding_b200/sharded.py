@@ -119,7 +119,7 @@ class ShardedVerifier:
     """Verification step over vocabulary slices; call :meth:`verify` with THIS rank's slices."""
 
     def __init__(self, V: int, rank: Optional[int] = None, world: Optional[int] = None, group=None, backend=None,
-                 fused_exchange: bool = True):
+                 fused_exchange: bool = False):
         self.group = group
         self.world = dist.get_world_size(group) if world is None else int(world)
         self.rank = dist.get_rank(group) if rank is None else int(rank)
@@ -130,12 +130,17 @@ class ShardedVerifier:
                 raise RuntimeError("ShardedVerifier needs a CUDA device (duodecoding_b200 has no CPU path)")
             backend = _CudaBackend()
         self.backend = backend
+        # Exchange: NCCL all-gathers captured in the step's graph by default.  `fused_exchange=True` moves both
+        # exchanges into the kernels (peer stores + release/acquire flags over symmetric memory); measured on one
+        # 8 x B200 box at C5 it is slower than the captured NCCL all-gathers (174 / 213 us vs 147 us per step,
+        # profiles/r02_c5_exchange_ab.txt), so it stays opt-in.
         self.collectives = 0
         self.use_graphs = True
         self.fused = fused_exchange and self.world > 1 and isinstance(backend, _CudaBackend)
         self._bufs: dict = {}
         self._graphs: dict = {}
         self._symm: dict = {}
+        self.xchg_mode = 0  # 0: every block pushes its result to the peers; 1: the last block copies the slab
 
     def slice_of(self, full: torch.Tensor) -> torch.Tensor:
         """This rank's columns of a [..., V] tensor (what a sharded LM head would have produced)."""
@@ -182,7 +187,7 @@ class ShardedVerifier:
             hdl = symm_mem.rendezvous(t, self.group if self.group is not None else dist.group.WORLD)
             torch.cuda.synchronize(dev)
             dist.barrier(group=self.group)  # every header is zero before anybody publishes
-            x = ShardXchg(hdl.buffer_ptrs_dev, self.rank, W, off_stats, off_partial)
+            x = ShardXchg(hdl.buffer_ptrs_dev, self.rank, W, off_stats, off_partial, int(self.xchg_mode))
             ent = (t, hdl, x, nslice)
             self._symm[key] = ent
         return ent

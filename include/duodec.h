@@ -174,6 +174,7 @@ typedef struct {
   void* const* peers;
   int rank, world;
   int64_t off_stats, off_partial;
+  int mode; /* 0: every block stores its result into every peer; 1: the last block copies the rank's slab */
 } duodec_shard_xchg;
 #define DUODEC_SHARD_XCHG_HEADER 1024
 int duodec_shard_stats(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss, int64_t t_sb,

@@ -31,3 +31,21 @@ def test_argument_errors_come_back_as_codes_without_a_gpu():
     assert lib.duodec_norm_logits(None, 0, 0, None, 0, 0, 0, 16, 1.0, 0, 0.0, None) == 0      # no rows: no-op
     assert lib.duodec_shard_finish(None, 0, 4, 1, None, None, None) == -1                           # world <= 0
     assert lib.duodec_verify_workspace_bytes(64, 4) > 0 and lib.duodec_team_size(32000, 2) >= 1
+
+
+def test_kernels_are_registered_torch_library_ops():
+    """Every kernel launch is a `duodec::` custom op whose outputs are annotated as mutated (SURVEY 8b)."""
+    import torch
+
+    import duodecoding_b200.ops  # noqa: F401  (registration happens at import)
+
+    want = {"norm_logits": 1, "verify_fused": 7, "accept_probs": 4, "sample_rows": 1, "residual_sample": 1,
+            "max_fn": 1, "topk_rebuild": 1, "kv_truncate": 1}
+    for name, nmut in want.items():
+        schema = getattr(torch.ops.duodec, name).default._schema
+        mutated = [a for a in schema.arguments if a.alias_info is not None and a.alias_info.is_write]
+        assert len(mutated) == nmut, (name, str(schema))
+        assert len(schema.returns) == 0
+    # the Meta implementation lets shape-only tracing pass through without a device
+    x = torch.empty(3, 16, device="meta")
+    torch.ops.duodec.max_fn(x, torch.empty(3, 16, device="meta"))
