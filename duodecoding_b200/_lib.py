@@ -59,6 +59,12 @@ SIGNATURES = {
     "duodec_max_fn": (c_int, [c_void_p, c_int, c_i64, c_int, c_int, c_void_p, c_i64, c_void_p]),
     "duodec_topk_rebuild": (c_int, [c_void_p, c_int, c_i64, c_void_p, c_i64, c_int, c_int, c_int, c_int, c_void_p]),
     "duodec_kv_truncate": (c_int, [c_void_p, c_void_p, c_i64, c_int, c_void_p]),
+    "duodec_compact_nonzero": (
+        c_int, [c_void_p, c_int, c_i64, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "duodec_shard_topk_apply": (
+        c_int,
+        [c_void_p, c_int, c_i64, c_void_p, c_i64, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+         c_void_p]),
     "duodec_shard_stats": (
         c_int,
         [c_void_p, c_void_p, c_int, c_i64, c_i64, c_i64, c_i64, c_int, c_int, c_int, c_int, c_void_p, c_i64]

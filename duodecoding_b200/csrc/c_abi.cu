@@ -462,4 +462,38 @@ int duodec_shard_finish(const void* gathered_partials, int world, int B, int nsl
   return int(cudaGetLastError());
 }
 
+int duodec_compact_nonzero(const void* x, int dtype, int64_t stride, int rows, int Vs, int v_begin, int kcap,
+                           float* cand_val, int32_t* cand_idx, int32_t* count, void* stream) {
+  if (rows < 0 || Vs <= 0 || kcap <= 0) return DUODEC_EINVAL;
+  if (rows == 0) return 0;
+  if (!x || !cand_val || !cand_idx || !count || (dtype != DUODEC_F32 && dtype != DUODEC_BF16)) return DUODEC_EINVAL;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dtype == DUODEC_F32)
+    compact_nonzero_kernel<float><<<rows, 256, 0, st>>>(static_cast<const float*>(x), stride, Vs, v_begin, kcap,
+                                                        cand_val, cand_idx, count);
+  else
+    compact_nonzero_kernel<__nv_bfloat16><<<rows, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(x), stride, Vs,
+                                                                v_begin, kcap, cand_val, cand_idx, count);
+  return int(cudaGetLastError());
+}
+
+int duodec_shard_topk_apply(const void* x, int dtype, int64_t in_stride, void* out, int64_t out_stride, int rows,
+                            int Vs, int v_begin, const float* tau, const int32_t* istar, const float* fill,
+                            const float* total, void* stream) {
+  if (rows < 0 || Vs <= 0) return DUODEC_EINVAL;
+  if (rows == 0) return 0;
+  if (!x || !out || !tau || !istar || !fill || !total || (dtype != DUODEC_F32 && dtype != DUODEC_BF16))
+    return DUODEC_EINVAL;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dtype == DUODEC_F32)
+    shard_topk_apply_kernel<float><<<rows, 256, 0, st>>>(static_cast<const float*>(x), in_stride,
+                                                         static_cast<float*>(out), out_stride, Vs, v_begin, tau,
+                                                         istar, fill, total);
+  else
+    shard_topk_apply_kernel<__nv_bfloat16><<<rows, 256, 0, st>>>(
+        static_cast<const __nv_bfloat16*>(x), in_stride, static_cast<__nv_bfloat16*>(out), out_stride, Vs, v_begin,
+        tau, istar, fill, total);
+  return int(cudaGetLastError());
+}
+
 }  // extern "C"

@@ -190,3 +190,73 @@ __global__ void kv_truncate_kernel(int* __restrict__ seq_len, const long long* _
 }
 
 }  // namespace duodec
+
+namespace duodec {
+
+// ---------------------------------------------------------------------------
+// transfer_top_k under vocabulary sharding (merge of per-shard top-k candidates)
+//   compact_nonzero_kernel   one block per row: the non-zero entries of a (locally top-k compressed) slice as
+//                            (value, GLOBAL index) pairs in index order; free slots hold (-1, INT_MAX)
+//   shard_topk_apply_kernel  one block per row: with the merged boundary (tau, istar) of the global top-k,
+//                            rebuild the slice like utils.rebuild_topk_probs (src/utils.py:751-777): kept
+//                            entries keep their value, every exact zero takes `fill`, all divided by `total`
+// ---------------------------------------------------------------------------
+template <class T>
+__global__ void __launch_bounds__(256) compact_nonzero_kernel(const T* __restrict__ x, long long stride, int Vs,
+                                                              int v_begin, int kcap, float* __restrict__ cand_val,
+                                                              int* __restrict__ cand_idx, int* __restrict__ count) {
+  __shared__ int warp_tot[8];
+  const long long row = blockIdx.x;
+  const T* p = x + row * stride;
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const int chunk = (Vs + 255) / 256;  // a thread owns a contiguous chunk, so list order is index order
+  const int lo = min(tid * chunk, Vs), hi = min(lo + chunk, Vs);
+  int c = 0;
+  for (int i = lo; i < hi; ++i) c += to_f32(p[i]) != 0.0f;
+  int inc = c;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int o = __shfl_up_sync(0xffffffffu, inc, d);
+    if (lane >= d) inc += o;
+  }
+  if (lane == 31) warp_tot[w] = inc;
+  __syncthreads();
+  int base = inc - c, total = 0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    if (k < w) base += warp_tot[k];
+    total += warp_tot[k];
+  }
+  float* cv = cand_val + row * kcap;
+  int* ci = cand_idx + row * kcap;
+  for (int i = lo; i < hi; ++i) {
+    const float v = to_f32(p[i]);
+    if (v != 0.0f) {
+      if (base < kcap) cv[base] = v, ci[base] = v_begin + i;
+      ++base;
+    }
+  }
+  for (int s = min(total, kcap) + tid; s < kcap; s += 256) cv[s] = -1.0f, ci[s] = 0x7fffffff;
+  if (tid == 0) count[row] = total;
+}
+
+template <class T>
+__global__ void __launch_bounds__(256) shard_topk_apply_kernel(const T* __restrict__ x, long long in_stride,
+                                                               T* __restrict__ out, long long out_stride, int Vs,
+                                                               int v_begin, const float* __restrict__ tau,
+                                                               const int* __restrict__ istar,
+                                                               const float* __restrict__ fill,
+                                                               const float* __restrict__ total) {
+  const long long row = blockIdx.x;
+  const T* p = x + row * in_stride;
+  T* o = out + row * out_stride;
+  const float t = tau[row], f = fill[row], tot = total[row];
+  const int is = istar[row];
+  for (int i = threadIdx.x; i < Vs; i += 256) {
+    const float v = to_f32(p[i]);
+    const bool kept = (v > t || (v == t && v_begin + i <= is)) && v != 0.0f;
+    o[i] = from_f32<T>(__fdiv_rn(kept ? v : f, tot));
+  }
+}
+
+}  // namespace duodec

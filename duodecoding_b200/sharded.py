@@ -313,3 +313,103 @@ class ShardedVerifier:
             ent = self._graphs[key]
         ent[0].replay()
         return ent[1]
+
+
+class ShardedTopK:
+    """transfer_top_k (``utils.rebuild_topk_uniform_probs``, /root/reference/src/utils.py:751-784) when every rank
+    holds a vocabulary slice of the probability rows: a merge of per-shard top-k candidates.
+
+        local     the slice's own top-min(k, Vs) entries           kernel  duodec_topk_rebuild (mode 1)
+        compact   (value, global index) lists in index order       kernel  duodec_compact_nonzero
+        gather    all ranks' lists: k x 8 B per row and rank        all_gather_into_tensor
+        merge     global top-k among the G x k candidates,         kernel  duodec_topk_rebuild (mode 1) on the
+                  lowest index on ties                                     gathered values (rank order = index order)
+        apply     kept entries keep their value, holes take the     kernel  duodec_shard_topk_apply
+                  uniform refill, renormalise
+
+    Every rank ends with its slice of exactly the row the unsharded operator produces."""
+
+    def __init__(self, V: int, rank: Optional[int] = None, world: Optional[int] = None, group=None):
+        self.group = group
+        self.world = dist.get_world_size(group) if world is None else int(world)
+        self.rank = dist.get_rank(group) if rank is None else int(rank)
+        self.V = int(V)
+        self.v_begin, self.v_end = shard_bounds(self.V, self.rank, self.world)
+
+    # ---- the three local stages (also what the single-device tests drive rank by rank)
+    def local_candidates(self, probs: torch.Tensor, k: int, v_begin: Optional[int] = None):
+        """probs [rows, Vs] -> (cand_val [rows, kl] f32, cand_idx [rows, kl] i32), kl = min(k, Vs)."""
+        from . import _lib, ops
+        v_begin = self.v_begin if v_begin is None else v_begin
+        rows, Vs = probs.shape
+        kl = min(int(k), Vs)
+        dense = ops.topk_rebuild(probs, kl, 1) if kl < Vs else probs
+        val = torch.empty((rows, kl), dtype=torch.float32, device=probs.device)
+        idx = torch.empty((rows, kl), dtype=torch.int32, device=probs.device)
+        cnt = torch.empty((rows,), dtype=torch.int32, device=probs.device)
+        if rows:
+            with torch.cuda.device(probs.device):
+                _lib.check(_lib.lib.duodec_compact_nonzero(dense.data_ptr(), ops._code(dense), dense.stride(0), rows, Vs,
+                                                           int(v_begin), kl, val.data_ptr(), idx.data_ptr(),
+                                                           cnt.data_ptr(), ops._stream()), "duodec_compact_nonzero")
+        return val, idx
+
+    def merge(self, vals: torch.Tensor, idxs: torch.Tensor, k: int):
+        """Gathered lists [G, rows, kl] (rank-major) -> per-row boundary (tau, istar), refill and normaliser."""
+        from . import ops
+        G, rows, kl = vals.shape
+        v = vals.permute(1, 0, 2).reshape(rows, G * kl).contiguous()
+        i = idxs.permute(1, 0, 2).reshape(rows, G * kl)
+        picked = ops.topk_rebuild(v.clamp_min(0.0), int(k), 1) if k < G * kl else v.clamp_min(0.0)
+        kept = picked > 0
+        inf = torch.full_like(v, float("inf"))
+        tau = torch.where(kept, v, inf).amin(-1)
+        istar = torch.where(kept & (v == tau.unsqueeze(-1)), i, torch.full_like(i, -1)).amax(-1).to(torch.int32)
+        S = picked.sum(-1)
+        holes = (self.V - kept.sum(-1)).to(torch.float32)
+        tail = (1.0 - S).clamp_min(0.0)
+        fill = torch.where(holes > 0, tail / holes.clamp_min(1.0), torch.zeros_like(tail))
+        total = (S + fill * holes).clamp_min(1e-12)
+        return tau.contiguous(), istar.contiguous(), fill.contiguous(), total.contiguous()
+
+    def apply(self, probs: torch.Tensor, boundary, v_begin: Optional[int] = None) -> torch.Tensor:
+        from . import _lib, ops
+        tau, istar, fill, total = boundary
+        v_begin = self.v_begin if v_begin is None else v_begin
+        rows, Vs = probs.shape
+        out = torch.empty_like(probs)
+        if rows:
+            with torch.cuda.device(probs.device):
+                _lib.check(_lib.lib.duodec_shard_topk_apply(probs.data_ptr(), ops._code(probs), probs.stride(0),
+                                                            out.data_ptr(), out.stride(0), rows, Vs, int(v_begin),
+                                                            tau.data_ptr(), istar.data_ptr(), fill.data_ptr(),
+                                                            total.data_ptr(), ops._stream()), "duodec_shard_topk_apply")
+        return out
+
+    def rebuild(self, probs_slice: torch.Tensor, k: Optional[int]) -> torch.Tensor:
+        """This rank's slice [..., Vs] of rebuild_topk_uniform_probs(full rows, k)."""
+        if k is None or k <= 0 or k >= self.V or probs_slice.numel() == 0:
+            return probs_slice
+        shape = probs_slice.shape
+        p = probs_slice.reshape(-1, shape[-1])
+        if p.stride(-1) != 1:
+            p = p.contiguous()
+        if p.dtype not in (torch.float32, torch.bfloat16):
+            p = p.float()
+        val, idx = self.local_candidates(p, k)
+        if self.world > 1:
+            kl = torch.tensor([val.shape[1]], device=p.device)
+            kmax = kl.clone()
+            dist.all_reduce(kmax, op=dist.ReduceOp.MAX, group=self.group)  # (the last slice may be narrower than k)
+            pad = int(kmax) - val.shape[1]
+            if pad:
+                val = torch.nn.functional.pad(val, (0, pad), value=-1.0)
+                idx = torch.nn.functional.pad(idx, (0, pad), value=0x7fffffff)
+            gv = torch.empty((self.world,) + tuple(val.shape), dtype=val.dtype, device=p.device)
+            gi = torch.empty((self.world,) + tuple(idx.shape), dtype=idx.dtype, device=p.device)
+            dist.all_gather_into_tensor(gv.view(-1, val.shape[1]), val.contiguous(), group=self.group)
+            dist.all_gather_into_tensor(gi.view(-1, idx.shape[1]), idx.contiguous(), group=self.group)
+        else:
+            gv, gi = val.unsqueeze(0), idx.unsqueeze(0)
+        out = self.apply(p, self.merge(gv, gi, int(k)))
+        return out.reshape(shape).to(probs_slice.dtype)

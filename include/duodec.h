@@ -191,6 +191,23 @@ int duodec_shard_sample(const void* draft, const void* target, int dtype, int64_
 int duodec_shard_finish(const void* gathered_partials, int world, int B, int nslice, int64_t* token,
                         const duodec_shard_xchg* xchg, void* stream);
 
+/* ---- transfer_top_k under vocabulary sharding (merge of per-shard top-k candidates) ------------------
+ * Replaces utils.rebuild_topk_probs (src/utils.py:751-777) / communication._apply_top_k_compression
+ * (src/communication.py:288-308) when every rank holds a vocabulary slice of the probability rows:
+ *   1. duodec_topk_rebuild(mode 1) on the local slice keeps the slice's own top-min(k, Vs) entries;
+ *   2. duodec_compact_nonzero lists them as (value, GLOBAL index) in index order, kcap slots per row, free
+ *      slots (-1, INT_MAX), count[row] = number of non-zero entries found;
+ *   3. the caller gathers the lists of all ranks (rank order = global index order), runs
+ *      duodec_topk_rebuild(mode 1) over the gathered values to pick the global top-k (lowest index on ties)
+ *      and derives the boundary (tau, istar), the kept mass and the number of holes;
+ *   4. duodec_shard_topk_apply writes the rebuilt slice: kept entries (v > tau, or v == tau and global index
+ *      <= istar, v != 0) keep their value, every other entry takes fill[row]; all divided by total[row]. */
+int duodec_compact_nonzero(const void* x, int dtype, int64_t stride, int rows, int Vs, int v_begin, int kcap,
+                           float* cand_val, int32_t* cand_idx, int32_t* count, void* stream);
+int duodec_shard_topk_apply(const void* x, int dtype, int64_t in_stride, void* out, int64_t out_stride, int rows,
+                            int Vs, int v_begin, const float* tau, const int32_t* istar, const float* fill,
+                            const float* total, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -57,3 +57,32 @@ def test_sharded_verifier_world1_and_edge_cases():
     assert got["accepted_len"].tolist() == [2, 2, 2] and got["all_accepted"].all()
     with pytest.raises(ValueError):
         sv.verify(dl[..., :100].to(dev), tl[..., :100].to(dev), toks.to(dev), r.to(dev), noise[..., :100].to(dev))
+
+
+@pytest.mark.parametrize("world", [1, 2, 8])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_sharded_topk_candidate_merge_matches_unsharded_rebuild(world, dtype):
+    """transfer_top_k over vocabulary slices (merge of per-shard top-k candidates) == the unsharded operator
+    (src/utils.py:751-784 on the oracle), ties included (bf16 grid: many equal probabilities at the k-th place)."""
+    from duodecoding_b200.sharded import ShardedTopK, shard_bounds
+    dev = torch.device("cuda:0")
+    g = torch.Generator().manual_seed(3)
+    V = 6000
+    rows = 7
+    p = torch.softmax(torch.randn(rows, V, generator=g) * 2.5, -1).to(dtype)
+    p[3] = 0
+    p[3, 17] = 1.0  # a one-hot row: k - 1 kept zeros are holes
+    p[4] = torch.softmax(torch.randn(V, generator=g) * 2.5, -1).to(torch.bfloat16).to(dtype)  # heavy ties
+    for k in (1, 100, 1024, 5999):
+        want = oracle.rebuild_topk_uniform_probs(p.float(), k)
+        sl = [shard_bounds(V, r, world) for r in range(world)]
+        ranks = [ShardedTopK(V, rank=r, world=world) for r in range(world)]
+        parts = [p[:, a:b].contiguous().to(dev) for a, b in sl]
+        cands = [rk.local_candidates(x, k) for rk, x in zip(ranks, parts)]
+        kmax = max(c[0].shape[1] for c in cands)
+        pad = lambda t, v: torch.nn.functional.pad(t, (0, kmax - t.shape[1]), value=v)  # noqa: E731
+        gv = torch.stack([pad(c[0], -1.0) for c in cands])
+        gi = torch.stack([pad(c[1], 0x7fffffff) for c in cands])
+        got = torch.cat([rk.apply(x, rk.merge(gv, gi, k)) for rk, x in zip(ranks, parts)], -1).cpu().float()
+        # (atol: with k = V - 1 the single hole takes 1 - sum(kept), a cancellation of order 1 ulp of 1.0)
+        torch.testing.assert_close(got, want, rtol=1e-5 if dtype == torch.float32 else 1e-2, atol=2e-7)
