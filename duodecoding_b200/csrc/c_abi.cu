@@ -191,7 +191,7 @@ int duodec_verify_fused(const void* draft, const void* target, int dtype, int64_
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int path = (flags >> 4) & 15, phases = (flags >> 8) & 3;
   const bool row0 = (flags & DUODEC_VERIFY_ROW0_RULE) != 0 && B > 1 && gamma > 0;
-  if (path != 0 && path != 1 && path != 5 && path != 6) return DUODEC_EINVAL;
+  if (path != 0 && path != 1 && path != 5) return DUODEC_EINVAL;
   if (path != 1) {
     // fast path: persistent row-stream kernel (stream_launch.cu); falls through when the call does not qualify
     StreamCall c;

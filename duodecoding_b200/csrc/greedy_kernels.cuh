@@ -16,7 +16,7 @@
 //                         row's 64-bit cell.  One pass over the logits at copy speed.
 //   greedy_close_kernel   one thread per sequence: decodes the 2*gamma+1 cells, accept tests, leading run
 //                         (its own, or sequence 0's under the batch rule), token, outputs.
-// The cells live in the workspace (record area) and are zeroed by a memset node ahead of the first kernel.
+// The cells live in their own zero-initialised area of the workspace; the close kernel leaves them zeroed.
 #pragma once
 
 #include "split_kernels.cuh"
@@ -121,22 +121,38 @@ __device__ __forceinline__ int greedy_run(const GreedyParams& P, int b, bool wri
   return n;
 }
 
-__global__ void __launch_bounds__(128) greedy_close_kernel(const __grid_constant__ GreedyParams P) {
-  const int b = blockIdx.x * 128 + threadIdx.x;
-  if (b >= P.B) return;
-  int n = greedy_run(P, b, true);
-  if (P.row0_rule && b != 0) n = greedy_run(P, 0, false);  // reference batch rule (src/decoding_ops.py:144-147)
-  const unsigned long long* c = P.cells + (long long)b * (2 * P.gamma + 1);
-  long long tok;
-  if (n == P.gamma) {
-    tok = greedy_cell_index(__ldcg(c + 2 * P.gamma));
-  } else {
-    const long long am_q = greedy_cell_index(__ldcg(c + 2 * n)), am_p = greedy_cell_index(__ldcg(c + 2 * n + 1));
-    tok = am_p != am_q ? am_p : 0;  // equal one-hots: zero residual mass -> first arg-max of p - q == 0 is index 0
+// One block closes every sequence: all reads of the cells (a sequence's own and, under the batch rule, sequence
+// 0's) happen before the barrier, the cells are zeroed after it - the workspace is ready for the next launch
+// without a memset.  Launched with programmatic stream serialization: it becomes resident while the arg-max
+// kernel drains.
+__global__ void __launch_bounds__(256) greedy_close_kernel(const __grid_constant__ GreedyParams P) {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  const int per_b = 2 * P.gamma + 1;
+  // reference batch rule (src/decoding_ops.py:144-147): sequence 0's count, read before anything is zeroed
+  const int n0 = P.row0_rule ? greedy_run(P, 0, false) : 0;
+  for (int b0 = 0; b0 < P.B; b0 += 256) {
+    const int b = b0 + threadIdx.x;
+    int n = 0;
+    long long tok = 0;
+    if (b < P.B) {
+      n = greedy_run(P, b, true);
+      if (P.row0_rule) n = n0;
+      const unsigned long long* c = P.cells + (long long)b * per_b;
+      if (n == P.gamma) {
+        tok = greedy_cell_index(__ldcg(c + 2 * P.gamma));
+      } else {
+        const long long am_q = greedy_cell_index(__ldcg(c + 2 * n)), am_p = greedy_cell_index(__ldcg(c + 2 * n + 1));
+        tok = am_p != am_q ? am_p : 0;  // equal one-hots: zero residual mass -> first arg-max of p - q == 0 is index 0
+      }
+    }
+    __syncthreads();
+    if (b < P.B) {
+      P.accepted_len[b] = n;
+      P.token[b] = tok;
+      P.all_accepted[b] = (unsigned char)(n == P.gamma);
+      for (int k = 0; k < per_b; ++k) P.cells[(long long)b * per_b + k] = 0ull;
+    }
   }
-  P.accepted_len[b] = n;
-  P.token[b] = tok;
-  P.all_accepted[b] = (unsigned char)(n == P.gamma);
 }
 
 }  // namespace greedy

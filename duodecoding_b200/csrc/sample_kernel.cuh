@@ -1,5 +1,4 @@
-// Sample kernel of the fused verify, staged variant (device path 5): same arithmetic and outputs as
-// seq_sample_kernel (split_kernels.cuh), but a block's three slices - the noise, the target row p_n and
+// Sample kernel of the fused verify: a block's three slices - the noise, the target row p_n and
 // the draft row q_n - arrive in shared memory through TMA bulk copies: one L2 round trip for the whole
 // slice instead of one per group of four entries.  The noise copy is issued before the grid dependency
 // resolves (programmatic launch: it overlaps the scan kernel's tail); the row copies as soon as the
@@ -14,121 +13,6 @@ namespace duodec {
 constexpr size_t sample_smem_bytes() { return size_t(3) * kSlice3 * 4; }
 static_assert(sizeof(Scratch3) + (2 * 64 + 1) * sizeof(RowRecord) <= size_t(2) * kSlice3 * 2,
               "scratch + records must fit under the row slices (bf16 rows)");
-
-// Compact mode of the sample kernel: the scan kernel left the capture state of target row p_n in the
-// row's workspace slot (capture_kernel.cuh: list columns [slots][128] of scaled logits in capture order,
-// bit map [stage][128] of the captured positions, overflow pool).  Only kept entries of p_n can have
-// max(0, p - q) > 0 (or p > 0 for the bonus draw), so the token is drawn from those: this block takes
-// `cpb` of the 128 columns, thread (column, part) walks the stages part, part + parts, ... of its column,
-// turns bits into (slot, index) pairs, and for kept entries gathers the draft logit and the noise.  Same
-// per-entry arithmetic as the sliced loop of the kernel, so the winner is the same entry.  Returns the
-// block's partial residual mass and best race key through mass / pk.
-template <class TIn>
-__device__ __noinline__ void compact_partial(const unsigned char* slot, int nslots, int nchunk, int col0, int cpb,
-                                             int npool, const TIn* qrow, const float* nz, float d_temp, bool bonus,
-                                             RowRecord rp, RowRecord rq, float invZp, float invZq, float* mass_out,
-                                             unsigned long long* pk_out, int* stats, long long t0) {
-  const int tid = threadIdx.x;
-  const float* lst = reinterpret_cast<const float*>(slot);
-  const unsigned short* bm = reinterpret_cast<const unsigned short*>(slot + size_t(nslots) * 128 * 4);
-  float mass = 0.0f;
-  unsigned long long pk = 0ull;
-  auto entry = [&](float x, int i, float y, float nzv) {
-    float d = row_exp(x, rp.m0) * invZp;
-    if (!bonus) {
-      const float ys = scale_logit(y, d_temp);
-      const bool kq = (ys > rq.xstar) | ((ys == rq.xstar) & (i <= rq.istar));
-      d -= kq ? row_exp(ys, rq.m0) * invZq : 0.0f;
-    }
-    if (d > 0.0f) {
-      mass += d;
-      const float key = __fdividef(d, nzv);
-      const unsigned long long k2 =
-          ((unsigned long long)__float_as_uint(key) << 32) | (unsigned long long)(0xffffffffu - unsigned(i));
-      if (key >= 0.0f && k2 > pk) pk = k2;  // (a NaN key never wins, as in the sliced loop)
-    }
-  };
-  const int parts = kT3 / cpb;
-  const int col = col0 + tid % cpb, part = tid / cpb;
-  int j0 = 0;  // slot of the column's next entry
-  for (int c0 = 0; c0 < nchunk; c0 += 8) {
-    unsigned hms[8];
-#pragma unroll
-    for (int u = 0; u < 8; ++u) hms[u] = c0 + u < nchunk ? unsigned(__ldg(bm + (c0 + u) * 128 + col)) : 0u;
-    if (tid == 0 && hms[0] != 0xffffffffu) CSTAMP(stats, 2, t0);
-#pragma unroll
-    for (int u = 0; u < 8; ++u) {
-      const int c = c0 + u;
-      unsigned hm = hms[u];
-      if ((c % parts) != part) {
-        j0 += __popc(hm);
-        continue;
-      }
-      while (hm != 0u) {  // up to four entries per trip: slots and indices, then the loads in three rounds
-        int jj[4], ii[4];
-        float xv[4], yv[4], nv[4];
-        bool kp[4];
-#pragma unroll
-        for (int t = 0; t < 4; ++t) {
-          jj[t] = -1, ii[t] = 0;
-          if (hm != 0u) {
-            const int k = __ffs(hm) - 1;
-            hm &= hm - 1u;
-            jj[t] = j0++;
-            ii[t] = c * kStageElems + ((k >> 2) * 128 + col) * 4 + (k & 3);
-          }
-        }
-#pragma unroll
-        for (int t = 0; t < 4; ++t) xv[t] = jj[t] >= 0 ? __ldg(lst + jj[t] * 128 + col) : -INFINITY;
-        if (tid == 0 && xv[0] != 12345.0f) CSTAMP(stats, 3, t0);
-#pragma unroll
-        for (int t = 0; t < 4; ++t) {
-          kp[t] = jj[t] >= 0 && ((xv[t] > rp.xstar) | ((xv[t] == rp.xstar) & (ii[t] <= rp.istar)));
-          yv[t] = (kp[t] && !bonus) ? to_f32(__ldcg(qrow + ii[t])) : 0.0f;
-          nv[t] = kp[t] ? __ldg(nz + ii[t]) : 1.0f;
-        }
-#pragma unroll
-        for (int t = 0; t < 4; ++t)
-          if (kp[t]) entry(xv[t], ii[t], yv[t], nv[t]);
-      }
-    }
-  }
-  if (col0 == 0) {  // the overflow pool (entries that did not fit their column) rides with the first block
-    const ListEntry* pool = reinterpret_cast<const ListEntry*>(slot + 30720 + 16);
-    for (int o = tid; o < npool; o += kT3) {
-      const int2 raw = __ldg(reinterpret_cast<const int2*>(pool + o));
-      const float x = __int_as_float(raw.x);
-      const int i = raw.y;
-      if ((x > rp.xstar) | ((x == rp.xstar) & (i <= rp.istar)))
-        entry(x, i, bonus ? 0.0f : to_f32(__ldcg(qrow + i)), __ldg(nz + i));
-    }
-  }
-  if (tid == 0 && mass != -1.0f) CSTAMP(stats, 4, t0);
-  *mass_out = mass;
-  *pk_out = pk;
-}
-
-// Zero residual mass (src/utils.py:787-810 fallback; essentially never with a rejected draft): first arg-max of
-// p - q over the whole row (NaN and +-inf count as 0), by one thread with plain loads.
-template <class TIn>
-__device__ __noinline__ long long zero_mass_token(const TIn* prow, const TIn* qrow, int V, float t_temp, float d_temp,
-                                                  bool bonus, RowRecord rp, RowRecord rq, float invZp, float invZq) {
-  unsigned long long pb = 0ull;
-  for (int i = 0; i < V; ++i) {
-    const float x = scale_logit(to_f32(__ldcg(prow + i)), t_temp);
-    const bool kp = (x > rp.xstar) | ((x == rp.xstar) & (i <= rp.istar));
-    float d = kp ? row_exp(x, rp.m0) * invZp : 0.0f;
-    if (!bonus) {
-      const float y = scale_logit(to_f32(__ldcg(qrow + i)), d_temp);
-      const bool kq = (y > rq.xstar) | ((y == rq.xstar) & (i <= rq.istar));
-      d -= kq ? row_exp(y, rq.m0) * invZq : 0.0f;
-    }
-    const float dz = (fabsf(d) < INFINITY) ? d : 0.0f;
-    const unsigned long long k2 = ((unsigned long long)okey(dz) << 32) | (unsigned long long)(0xffffffffu - unsigned(i));
-    pb = k2 > pb ? k2 : pb;
-  }
-  return pb == 0ull ? 0 : (long long)(0xffffffffu - unsigned(pb & 0xffffffffull));
-}
 
 template <class TIn>
 __global__ void __launch_bounds__(kT3, 4) seq_sample_tma_kernel(const __grid_constant__ SplitParams P) {
@@ -154,7 +38,7 @@ __global__ void __launch_bounds__(kT3, 4) seq_sample_tma_kernel(const __grid_con
     mbar_init(&mb[0], 1);
     mbar_init(&mb[1], 1);
     mbar_fence_init();
-    if (b < P.B && !P.compact_hint) {
+    if (b < P.B) {
       // the noise does not depend on the scan kernel (the caller wrote it before the scan kernel was launched)
       mbar_expect_tx(&mb[0], unsigned(ne) * 4u);
       bulk_g2s(s_noise, P.noise + (long long)b * P.noise_sb + s0, unsigned(ne) * 4u, &mb[0]);
@@ -166,7 +50,6 @@ __global__ void __launch_bounds__(kT3, 4) seq_sample_tma_kernel(const __grid_con
   grid_dep_wait();
   grid_dep_launch();
   if (tid == 0) STAMP(P.stats, 13);
-  const long long t0 = clock64();
 
   if (b == P.B) {  // the extra block row: block 0 of it aggregates the next launch's prediction, off the critical path
     if (slice != 0) return;
@@ -240,24 +123,6 @@ __global__ void __launch_bounds__(kT3, 4) seq_sample_tma_kernel(const __grid_con
   const RowRecord rp = srec[bonus ? 2 * gamma : 2 * n + 1];
   const RowRecord rq = bonus ? rp : srec[2 * n];
   const float invZp = __frcp_rn(rp.Z), invZq = __frcp_rn(rq.Z);
-  if (tid == 0) STAMP(P.stats, 14);
-  if (tid == 0) CSTAMP(P.stats, 1, t0);
-  float mass = 0.0f, bkey = -1.0f, bdv = -INFINITY;
-  int bidx = 0x7fffffff, bdi = 0x7fffffff;
-  unsigned long long pk = 0ull, pb = 0ull;
-  const bool compact = P.compact_hint && rp.pad > 0;
-  if (compact) {
-    // ---- compact mode: the token is drawn from the kept entries of p_n in the scan kernel's dump; up to eight
-    // blocks of the sequence share the 128 list columns, the others only arrive (no copy of this block is in
-    // flight: the noise prefetch is off under compact_hint)
-    int np = 1;
-    while (np * 2 <= int(gridDim.x) && np < 8) np *= 2;
-    if (slice < np)
-      compact_partial<TIn>(reinterpret_cast<const unsigned char*>(P.lists + (long long)(b * (gamma + 1) + n) * kListCap),
-                           P.cap_slots, (V + kStageElems - 1) / kStageElems, slice * (128 / np), 128 / np, rp.pad - 1,
-                           split_row<TIn>(P, RowJob{b, bonus ? 0 : n, 0}), P.noise + (long long)b * P.noise_sb,
-                           P.d_temp, bonus, rp, rq, invZp, invZq, &mass, &pk, P.stats, t0);
-  } else {
   // scratch and records are in registers everywhere: their shared memory becomes the row slices
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic accesses above, async writes below
   bar3();
@@ -266,16 +131,14 @@ __global__ void __launch_bounds__(kT3, 4) seq_sample_tma_kernel(const __grid_con
     mbar_expect_tx(&mb[1], unsigned(ne) * unsigned(kElt) * (bonus ? 1u : 2u));
     bulk_g2s(s_p, prow + s0, unsigned(ne) * unsigned(kElt), &mb[1]);
     if (!bonus) bulk_g2s(s_q, split_row<TIn>(P, RowJob{b, n, 0}) + s0, unsigned(ne) * unsigned(kElt), &mb[1]);
-    if (P.compact_hint) {  // a sequence without list under the hint (rare): the noise slice is fetched only now
-      mbar_expect_tx(&mb[0], unsigned(ne) * 4u);
-      bulk_g2s(s_noise, P.noise + (long long)b * P.noise_sb + s0, unsigned(ne) * 4u, &mb[0]);
-    }
   }
   if (tid == 0) STAMP(P.stats, 14);
   mbar_wait(&mb[0], 0u);
   mbar_wait(&mb[1], 0u);
   if (tid == 0) STAMP(P.stats, 24);
 
+  float mass = 0.0f, bkey = -1.0f, bdv = -INFINITY;
+  int bidx = 0x7fffffff, bdi = 0x7fffffff;
 #pragma unroll
   for (int u = 0; u < kSlice3 / (4 * kT3); ++u) {
     const int l0 = u * 4 * kT3 + 4 * tid, i0 = s0 + l0;
@@ -318,12 +181,12 @@ __global__ void __launch_bounds__(kT3, 4) seq_sample_tma_kernel(const __grid_con
       }
     }
   }
-  pk = bidx == 0x7fffffff ? 0ull
-                          : ((unsigned long long)__float_as_uint(bkey) << 32) |
-                                (unsigned long long)(0xffffffffu - unsigned(bidx));
-  pb = bdi == 0x7fffffff ? 0ull
-                         : ((unsigned long long)okey(bdv) << 32) | (unsigned long long)(0xffffffffu - unsigned(bdi));
-  }  // (sliced mode)
+  unsigned long long pk = bidx == 0x7fffffff ? 0ull
+                                            : ((unsigned long long)__float_as_uint(bkey) << 32) |
+                                                  (unsigned long long)(0xffffffffu - unsigned(bidx));
+  unsigned long long pb =
+      bdi == 0x7fffffff ? 0ull
+                        : ((unsigned long long)okey(bdv) << 32) | (unsigned long long)(0xffffffffu - unsigned(bdi));
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     mass += __shfl_xor_sync(0xffffffffu, mass, o);
@@ -352,9 +215,6 @@ __global__ void __launch_bounds__(kT3, 4) seq_sample_tma_kernel(const __grid_con
       const unsigned long long d = atomicMax(&P.seq_bd[b], 0ull);
       const unsigned long long win = (m > 0.0f && k != 0ull) ? k : d;
       long long tok = win == 0ull ? 0 : (long long)(0xffffffffu - unsigned(win & 0xffffffffull));
-      if (compact && !(m > 0.0f && k != 0ull))
-        tok = zero_mass_token<TIn>(split_row<TIn>(P, RowJob{b, n, 1}), split_row<TIn>(P, RowJob{b, bonus ? 0 : n, 0}), V,
-                                   P.t_temp, P.d_temp, bonus, rp, rq, invZp, invZq);
       P.accepted_len[b] = n;
       P.token[b] = tok;
       P.all_accepted[b] = (unsigned char)(n == gamma);
@@ -362,9 +222,7 @@ __global__ void __launch_bounds__(kT3, 4) seq_sample_tma_kernel(const __grid_con
       P.seq_key[b] = 0ull;
       P.seq_bd[b] = 0ull;
       P.seq_arrive[b] = 0;
-      CSTAMP(P.stats, 6, t0);
     }
-    CSTAMP(P.stats, 5, t0);
     STAMP(P.stats, 23);
   }
 }

@@ -87,9 +87,6 @@ struct SplitParams {
   float* seq_mass;              // [B]
   int* seq_arrive;              // [B]
   int* stats;
-  int cap_rank;      // row-capture kernel: rank (0..31) of the sorted group maxima that gives the capture cut
-  int cap_slots;     // row-capture kernel: list slots per worker thread (layout of a row's dump)
-  int compact_hint;  // sample kernel: target rows are expected to come with a kept-entry list (no noise prefetch)
   int row0_rule;     // sample kernel: sequence 0's accepted count positions every sequence (reference batch rule)
 };
 

@@ -1,12 +1,11 @@
-// Launcher of the fused-verify fast paths: row-capture scan kernel (path 6, default) or row-pair scan
-// kernel (path 5), each followed by the sample kernel under programmatic dependent launch.
+// Launcher of the fused-verify fast paths: the row-pair scan kernel followed by the sample kernel under
+// programmatic dependent launch (T > 0), or the greedy arg-max kernels (T == 0).
 #include <mutex>
 #include <utility>
 #include <vector>
 
 #include "../../include/duodec.h"
 #include "pair_kernel.cuh"
-#include "capture_kernel.cuh"
 #include "greedy_kernels.cuh"
 #include "sample_kernel.cuh"
 #include "stream_launch.h"
@@ -65,15 +64,14 @@ cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t s
 
 }  // namespace
 
-constexpr size_t kCapSmemMax = 232448;  // the capture kernel's shared memory depends on V: opt in to the limit once
-constexpr int kMaxGrid = 320;   // blocks of a persistent scan kernel (two per SM): one scratch list each
+constexpr int kMaxGrid = 320;   // blocks of the persistent scan kernel (two per SM): one scratch list each
 
-// hints | row records | per-sequence cells of the sliced sample mode | kept-entry lists of the target rows +
-// one scratch list per scan block
+// hints | row records | per-sequence cells of the sample kernel | one scratch list per scan block (general search) |
+// the greedy path's arg-max cells
 size_t stream_workspace_bytes(int B, int gamma) {
   const size_t rows = size_t(B) * size_t(2 * gamma + 1);
   return 4 * sizeof(StreamHint) + rows * sizeof(RowRecord) + size_t(B) * 24 + 128 +
-         (size_t(B) * size_t(gamma + 1) + kMaxGrid) * size_t(kListCap) * sizeof(ListEntry);
+         size_t(kMaxGrid) * size_t(kListCap) * sizeof(ListEntry) + rows * 8;  // + the greedy path's arg-max cells
 }
 
 bool stream_try_launch(const StreamCall& c, int* rc) {
@@ -95,15 +93,14 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
     G.accepted_len = reinterpret_cast<long long*>(c.accepted_len), G.token = reinterpret_cast<long long*>(c.token);
     G.all_accepted = c.all_accepted;
     const size_t head = (size_t(c.B) * 8 + size_t(c.B) * size_t(c.gamma + 1) * 8 + 15) & ~size_t(15);
-    G.cells = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(c.workspace) + head + 4 * sizeof(StreamHint));
-    cudaError_t e = cudaMemsetAsync(G.cells, 0, nrows * 8, c.stream);  // (the record area: 32 bytes per row)
+    // the cells sit behind everything the sampled-temperature paths use: zero since the workspace was created
+    G.cells = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(c.workspace) + head +
+                                                    stream_workspace_bytes(c.B, c.gamma) - nrows * 8);
     const dim3 grid(unsigned((c.Vt + greedy::kGSlice - 1) / greedy::kGSlice), unsigned(nrows));
-    if (e == cudaSuccess) {
-      if (c.dtype == DUODEC_F32) greedy::greedy_argmax_kernel<float><<<grid, greedy::kGT, 0, c.stream>>>(G);
-      else greedy::greedy_argmax_kernel<__nv_bfloat16><<<grid, greedy::kGT, 0, c.stream>>>(G);
-      greedy::greedy_close_kernel<<<(c.B + 127) / 128, 128, 0, c.stream>>>(G);
-      e = cudaGetLastError();
-    }
+    if (c.dtype == DUODEC_F32) greedy::greedy_argmax_kernel<float><<<grid, greedy::kGT, 0, c.stream>>>(G);
+    else greedy::greedy_argmax_kernel<__nv_bfloat16><<<grid, greedy::kGT, 0, c.stream>>>(G);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = launch_pdl(greedy::greedy_close_kernel, dim3(1), dim3(256), 0, c.stream, G);
     *rc = int(e);
     return true;
   }
@@ -114,10 +111,8 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
                   (size_t(c.d_ss) * elt) % 16 == 0 && al16(c.noise) && (c.noise_sb % 4) == 0;
   if (!ok) return false;
   const size_t rows = size_t(c.B) * size_t(2 * c.gamma + 1);
-  const bool capture = c.path == 6 && c.B <= 65535 && c.Vt >= cap::kMinV &&
-                       cap::cap_smem_bytes((c.Vt + kStageElems - 1) / kStageElems) <= 232448;
-  const bool pairp = (c.path == 5 || (c.path == 6 && !capture)) && c.B <= 65535;
-  if (pairp || capture) {
+  const bool pairp = c.path == 5 && c.B <= 65535;
+  if (pairp) {
     SplitParams Q;
     Q.draft = c.draft;
     Q.target = c.target;
@@ -168,49 +163,8 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
     w = reinterpret_cast<char*>((reinterpret_cast<uintptr_t>(w) + 127) & ~uintptr_t(127));  // TMA bulk stores land here
     Q.lists = reinterpret_cast<ListEntry*>(w);
     Q.stats = c.stats;
-    Q.cap_rank = 0;
-    Q.cap_slots = cap::kSlots;
-    Q.compact_hint = 0;
     Q.row0_rule = c.row0_rule;
     const dim3 g2(unsigned((c.Vt + kSlice3 - 1) / kSlice3), unsigned(c.B) + 1u);  // + the block row that aggregates the hints
-    if (capture) {
-      const size_t smem = cap::cap_smem_bytes((c.Vt + kStageElems - 1) / kStageElems);
-      const int sms = stream_sm_count();
-      const int per_sm = smem <= 115712 ? 2 : 1;  // two blocks per SM while the bit maps leave room
-      const int npairs = int((rows + 1) / 2);
-      int grid = npairs < per_sm * sms ? npairs : per_sm * sms;
-      if (grid > kMaxGrid) grid = kMaxGrid;
-      // capture cut: the top f of a row by count, f = min(1/11, 2667 / V); a thread's 16 sample entries
-      // all lie below the cut with probability (1 - f)^16, which is the rank among the 32 sorted maxima
-      double f = 2667.0 / double(c.Vt);
-      if (f > 1.0 / 11.0) f = 1.0 / 11.0;
-      double pbelow = 1.0;
-      for (int i = 0; i < 16; ++i) pbelow *= 1.0 - f;
-      int rank = int(32.0 * pbelow);
-      Q.cap_rank = rank < 0 ? 0 : (rank > 31 ? 31 : rank);
-      Q.compact_hint = (c.top_p > 0.0f && c.top_p < 1.0f && (c.Vt + kStageElems - 1) / kStageElems <= cap::kDumpMaxChunks) ? 1 : 0;
-      const dim3 g2c(unsigned((c.Vt + kSlice3 - 1) / kSlice3), unsigned(c.B));  // no hint row: nothing is predicted
-      cudaError_t e;
-      const size_t smem2 = sample_smem_bytes();
-      if (c.dtype == DUODEC_F32) {
-        e = ensure_stream_smem(reinterpret_cast<const void*>(cap::row_capture_kernel<float>), kCapSmemMax);
-        if (e == cudaSuccess) e = ensure_stream_smem(reinterpret_cast<const void*>(seq_sample_tma_kernel<float>), smem2);
-        if (e == cudaSuccess && (c.phases & 1))
-          e = launch_pdl(cap::row_capture_kernel<float>, dim3(grid), dim3(cap::kPT), smem, c.stream, Q);
-        if (e == cudaSuccess && (c.phases & 2))
-          e = launch_pdl(seq_sample_tma_kernel<float>, g2c, dim3(kT3), smem2, c.stream, Q);
-      } else {
-        e = ensure_stream_smem(reinterpret_cast<const void*>(cap::row_capture_kernel<__nv_bfloat16>), kCapSmemMax);
-        if (e == cudaSuccess)
-          e = ensure_stream_smem(reinterpret_cast<const void*>(seq_sample_tma_kernel<__nv_bfloat16>), smem2);
-        if (e == cudaSuccess && (c.phases & 1))
-          e = launch_pdl(cap::row_capture_kernel<__nv_bfloat16>, dim3(grid), dim3(cap::kPT), smem, c.stream, Q);
-        if (e == cudaSuccess && (c.phases & 2))
-          e = launch_pdl(seq_sample_tma_kernel<__nv_bfloat16>, g2c, dim3(kT3), smem2, c.stream, Q);
-      }
-      *rc = int(e != cudaSuccess ? e : cudaGetLastError());
-      return true;
-    }
     if (pairp) {
       const size_t smem = pair::pair_smem_bytes();
       const int sms = stream_sm_count();

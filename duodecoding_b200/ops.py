@@ -160,16 +160,15 @@ def set_team_size(team: int) -> None:
     lib.duodec_set_team_size(int(team))
 
 
-FAST_PATH = 5  # row-pair scan kernel + sliced sample kernel (6: row-capture kernel, experimental)
-_PATH = 0       # DUODEC_VERIFY_PATH: 0 automatic, 1 general team kernel, 5 row-pair kernel, 6 row capture
+FAST_PATH = 5  # row-pair scan kernel + sliced sample kernel
+_PATH = 0       # DUODEC_VERIFY_PATH: 0 automatic, 1 general team kernel, 5 row-pair kernel
 _PHASES = 0     # DUODEC_VERIFY_PHASES: 0 / 3 both kernels, 1 scan only, 2 sample only
 ROW0_RULE = 1   # DUODEC_VERIFY_ROW0_RULE
 
 
 def set_stream_path(path) -> None:
     """Test hook: device path of the following verify_fused calls.  True: automatic (the row-capture fast
-    path when the call qualifies); False / 0: the general team kernel; 5: row-pair scan kernel; 6: row
-    capture.  The choice travels in the call's ``flags`` argument - the library keeps no path state."""
+    path when the call qualifies); False / 0: the general team kernel; 5: row-pair scan kernel.  The choice travels in the call's ``flags`` argument - the library keeps no path state."""
     global _PATH
     if isinstance(path, bool):
         _PATH = 0 if path else 1

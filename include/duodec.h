@@ -90,11 +90,10 @@ int duodec_norm_logits_batched(const void* logits, int in_dtype, int64_t in_batc
  * flags: DUODEC_VERIFY_ROW0_RULE - the reference's batch rule (src/decoding_ops.py:144-147): the
  *   accepted count of sequence 0 positions EVERY sequence (accepted_len[b] = accepted_len[0], every
  *   token drawn at that position); without it every sequence is verified on its own count.  Only
- *   the fast paths implement it (equal vocabularies, no top-k, T > 0, 16-byte aligned rows):
+ *   the fast paths implement it (equal vocabularies, no top-k, 16-byte aligned rows; T > 0 or greedy T == 0):
  *   DUODEC_EINVAL otherwise when B > 1.
  *   DUODEC_VERIFY_PATH(p) - test hook: 0 automatic (row-pair scan kernel when the call qualifies,
- *   else the general team kernel), 1 general team kernel, 5 row-pair scan kernel, 6 row-capture scan
- *   kernel (single pass, experimental).
+ *   else the general team kernel), 1 general team kernel, 5 row-pair scan kernel.
  *   DUODEC_VERIFY_PHASES(m) - measurement hook: 1 scan kernel only, 2 sample kernel only, 0 / 3 both.
  * workspace: duodec_verify_workspace_bytes(B,gamma) bytes, 16-byte aligned, zero-filled ONCE by
  *   the caller before first use (the kernels restore what they need to zero).  One launch in flight

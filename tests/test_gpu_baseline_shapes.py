@@ -106,7 +106,7 @@ def _verify_report(got, want, r, name, tol, rows_t=None, rows_d=None, warp=None,
         REPORT[name][key + "_row_margins_there"] = margins
 
 
-@pytest.mark.parametrize("path", [5, 6, 0])
+@pytest.mark.parametrize("path", [5, 0])
 def test_c2_full_batch(ops, dev, path):
     """BASELINE config 2: B=64, gamma=4, V=32000, fp32, T=1, top_p=0.9 - every sequence against the oracle.
     Probabilities at 1e-5 wherever the nucleus supports agree (north_star tolerance)."""
