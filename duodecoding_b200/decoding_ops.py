@@ -149,14 +149,22 @@ def _fused_verify(draft_cache, target_cache, x: torch.Tensor, prefix_len: int, g
     tokens = x[:, prefix_len:prefix_len + steps].to(dev)
     if r is None:
         r = torch.rand((B, steps), device=dev)
+    # the Exp(1) race noise and the output tensors live with the target cache: no V-sized allocation per step
+    buf = getattr(target_cache, "_fused_buf", None)
+    if buf is None or buf[0] != (B, steps, V, dev):
+        buf = ((B, steps, V, dev), torch.empty((B, V), dtype=torch.float32, device=dev), None)
     if noise is None:
-        noise = torch.empty((B, V), dtype=torch.float32, device=dev).exponential_(1.0)
+        noise = buf[1].exponential_(1.0)
     out = ops.verify_fused(dl, tl, tokens, r, noise, float(target_cache._temperature),
                            int(target_cache._top_k or 0), float(target_cache._top_p or 0.0),
                            float(draft_cache._temperature), int(draft_cache._top_k or 0),
-                           float(draft_cache._top_p or 0.0), row0_rule=True)
+                           float(draft_cache._top_p or 0.0), out=buf[2], row0_rule=True)
+    try:
+        target_cache._fused_buf = (buf[0], buf[1], out)
+    except AttributeError:
+        pass
     accepted = int(out["accepted_len"][0].item())  # the one device->host read of the step (reference: .item())
-    return accepted, int(prefix_len + accepted - 1), out["token"].unsqueeze(1), steps
+    return accepted, int(prefix_len + accepted - 1), out["token"].unsqueeze(1).clone(), steps
 
 
 def sample_reject_token(target_probs: torch.Tensor, draft_probs: torch.Tensor,
