@@ -6,9 +6,9 @@
 // own producer warp), histogram and half-barrier, streaming its own row.  With two blocks per SM
 // that is four rows in flight per SM - at the C2 shape every row of the step is in flight at once,
 // so the latency-bound row tails (bucket scan, second pass, select) overlap instead of queueing
-// behind each other.  The two halves join for the selects, which use all 256 threads
-// (list_select_body) on one row after the other; the list columns of the two rows are disjoint
-// (column = thread).
+// behind each other.  Each half selects its own row (half_select); the halves join only for rows that need
+// the general search.  Pass 2 appends the boundary bucket's entries to per-THREAD list columns with predicated
+// stores (round 1: hit masks, a warp prefix sum and one divergent trip per hit into per-warp regions).
 #pragma once
 
 #include "ring_kernel.cuh"
@@ -24,8 +24,9 @@ constexpr int kPT = kT3 + 64;                    // 256 workers + one producer w
 #endif
 constexpr int kPStages = DUODEC_PAIR_STAGES;     // 8 KB stages per half
 constexpr int kPairCap = 2048;                   // kCap of the block's list_select over one row's (compacted) list
-constexpr int kWarpCap = 320;                    // list entries per worker warp (shared memory): 4 x 320 per row
-constexpr int kHalfCap = kHW * kWarpCap;         // 1280
+constexpr int kColSlots = kHB;                   // list slots of a worker thread: its own column of boundary-bucket entries
+                                                 // = its histogram column, dead after pass 1 (the last 4 slots are slack:
+                                                 // the column is re-checked once per float4)
 
 struct __align__(16) HalfRow {
   double target;
@@ -42,7 +43,7 @@ struct __align__(16) PairSync {
   HalfRow half[2];
   int nlist;
   int pad[3];
-  int wcnt[2][kHW];  // list entries of each worker warp
+  int colfull[2];  // a thread of the half ran out of list slots: general search
 };
 
 // Scratch of one half's own select (half_select below): the level histogram in native 32-bit
@@ -62,9 +63,13 @@ struct __align__(16) HalfScratch {
   int pad[2];
 };
 
-constexpr size_t pair_smem_bytes() {
-  return size_t(2) * kPStages * kStageBytes + size_t(kHB) * kT3 * 4 + size_t(2) * kHalfCap * sizeof(ListEntry) +
-         sizeof(Scratch3) + sizeof(PairSync) + 2 * sizeof(HalfScratch) + 128;
+// bit map of the captured positions: 16 bits per thread and stage (the entries' indices are recovered from it)
+__host__ __device__ constexpr size_t pair_bitmap_bytes(int nchunk) { return (size_t(nchunk) * kHT * 2 + 15) & ~size_t(15); }
+
+// rings | histograms [2][32][128] float (pass 2: the list columns) | scratch | sync | select scratch | bit maps [2]
+__host__ __device__ constexpr size_t pair_smem_bytes(int nchunk) {
+  return size_t(2) * kPStages * kStageBytes + size_t(kHB) * kT3 * 4 + sizeof(Scratch3) + sizeof(PairSync) +
+         2 * sizeof(HalfScratch) + 2 * pair_bitmap_bytes(nchunk) + 128;
 }
 
 __device__ __forceinline__ void barh(int h) {  // named barrier of one half (immediate ids: 2 and 3)
@@ -124,11 +129,29 @@ __device__ __forceinline__ void barh(int h) {  // named barrier of one half (imm
   }
 #endif
 
-// hm |= bit when xa <= x < xb: two compares into one predicate and a predicated OR
-__device__ __forceinline__ void hit_or(unsigned& hm, float x, float xa, float xb, unsigned bit) {
-  asm("{\n\t.reg .pred p;\n\tsetp.ge.f32 p, %1, %2;\n\tsetp.lt.and.f32 p, %1, %3, p;\n\t@p or.b32 %0, %0, %4;\n\t}"
-      : "+r"(hm)
-      : "f"(x), "f"(xa), "f"(xb), "r"(bit));
+// xa <= x < xb: append x to the thread's own list column (predicated store, no atomics, no shuffles), advance the
+// column pointer, mark the entry's bit in the stage's mask
+__device__ __forceinline__ void col_take(unsigned& lp, unsigned& hm, float x, float xa, float xb, unsigned bit) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ge.f32 p, %2, %3;\n\tsetp.lt.and.f32 p, %2, %4, p;\n\t@p st.shared.f32 [%0], %2;\n\t"
+      "@p add.u32 %0, %0, 512;\n\t@p or.b32 %1, %1, %5;\n\t}"
+      : "+r"(lp), "+r"(hm)
+      : "f"(x), "f"(xa), "f"(xb), "r"(bit)
+      : "memory");
+}
+
+// row index of the thread's j-th list entry (capture order) from its bit-map column
+__device__ __forceinline__ int col_index_of(const unsigned short* bmt, int j, int ht) {
+  int stage = 0;
+  unsigned hm = bmt[0];
+  while (__popc(hm) <= j) {
+    j -= __popc(hm);
+    ++stage;
+    hm = bmt[stage * kHT];
+  }
+  for (; j > 0; --j) hm &= hm - 1u;  // drop the j lowest set bits (j < 16)
+  const int k = __ffs(hm) - 1;
+  return stage * kStageElems + ((k >> 2) * kHT + ht) * 4 + (k & 3);
 }
 
 // smallest float x whose histogram bucket (hist_bits of x*log2e - m0) is >= bits; false if the search
@@ -147,13 +170,12 @@ __device__ __forceinline__ bool bucket_edge(int bits, float m0, float* edge) {
 // pair are finished side by side.  Same exact arithmetic and the same answer as list_select_body
 // (split_kernels.cuh): 38-bit fixed-point masses, a level of 128 value buckets over the entries'
 // value range, suffix scan, all-pairs order of the <= 128 entries of the crossing bucket.  The
-// row's entries sit in the half's list hl[4][320], one region per worker warp with wn[w] entries;
-// thread ht looks at the slots j * 128 + ht.  Returns false when the row needs the tie bisection:
-// the caller then runs list_select_body with the whole block.
-__device__ __forceinline__ bool half_select(const ListEntry* hl, const int* wn, int h, int ht, float GB, float Zrow,
-                                            double target, float m0, HalfScratch* hs, RowRecord& rec,
-                                            int* ncand_out) {
-  constexpr int kPer = kHalfCap / kHT;  // list slots of a thread: slot j * 128 + ht belongs to warp slot / 320
+// thread's entries are col[j * 128], j < nt (its own list column, capture order); their row indices
+// come from its bit-map column bmt.  Returns false when the row needs the general search (more equal
+// values than the finish can order).
+__device__ __forceinline__ bool half_select(const float* col, int nt, const unsigned short* bmt, int h, int ht, float xa,
+                                            float xb, float GB, float Zrow, double target, float m0, HalfScratch* hs,
+                                            RowRecord& rec, int* ncand_out, int* stats) {
   constexpr unsigned long long kNone = 0xffffffffffffffffull;
   const int lane = ht & 31, hw = ht >> 5;
   const int ez = int(__float_as_uint(Zrow) >> 23) - 126;               // Z = f * 2^ez, f in [0.5, 1)
@@ -162,31 +184,21 @@ __device__ __forceinline__ bool half_select(const ListEntry* hl, const int* wn, 
   unsigned long long GBf = (unsigned long long)(double(GB) * double(S));
   if (GBf > tgt) GBf = tgt;  // GB is an fp32 scan difference: it may land a few ulps above the target; the top
                              // non-empty bucket is then the crossing one and its largest entry the boundary
-  auto entry = [&](int j) { return &hl[j * kHT + ht]; };
   auto fx = [&](float x) { return __float2ull_rn(row_exp(x, m0) * S); };  // fixed-point mass of an entry
-  float cx[kPer];
-  float emx = -INFINITY, engmn = -INFINITY;
+  // the first bracket is the boundary bucket's own interval [xa, xb) (every list entry lies inside it); only
+  // the unbounded top bucket needs the entries' maximum
+  float A = xa, B = xb;
+  if (!(xb < INFINITY)) {
+    float emx = -INFINITY;
+    for (int j = 0; j < nt; ++j) emx = fmaxf(emx, col[j * kHT]);
 #pragma unroll
-  for (int j = 0; j < kPer; ++j) {
-    const int slot = j * kHT + ht, w = slot / kWarpCap;
-    const bool have = slot - w * kWarpCap < wn[w];
-    float x = -INFINITY;
-    if (have) {
-      x = ld_list_x(entry(j));
-      emx = fmaxf(emx, x), engmn = fmaxf(engmn, -x);
-    }
-    cx[j] = x;
+    for (int o = 16; o > 0; o >>= 1) emx = fmaxf(emx, __shfl_xor_sync(0xffffffffu, emx, o));
+    if (lane == 0) hs->red[hw] = make_float2(emx, 0.0f);
+    barh(h);
+#pragma unroll
+    for (int w = 0; w < kHW; ++w) emx = fmaxf(emx, hs->red[w].x);
+    B = nextafterf(emx, INFINITY);
   }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    emx = fmaxf(emx, __shfl_xor_sync(0xffffffffu, emx, o));
-    engmn = fmaxf(engmn, __shfl_xor_sync(0xffffffffu, engmn, o));
-  }
-  if (lane == 0) hs->red[hw] = make_float2(emx, engmn);
-  barh(h);
-#pragma unroll
-  for (int w = 0; w < kHW; ++w) emx = fmaxf(emx, hs->red[w].x), engmn = fmaxf(engmn, hs->red[w].y);
-  float A = -engmn, B = nextafterf(emx, INFINITY);  // the bracket is the value range of the entries
   bool solved = false, tie_mode = false;
   *ncand_out = 0;
 #pragma unroll 1
@@ -206,17 +218,18 @@ __device__ __forceinline__ bool half_select(const ListEntry* hl, const int* wn, 
       const int bk = int((x - A) * bsc);
       return bk < 0 ? 0 : (bk > kHT - 1 ? kHT - 1 : bk);
     };
-#pragma unroll
-    for (int j = 0; j < kPer; ++j) {
-      if (cx[j] >= A && cx[j] < B) {
-        const int bk = bucket(cx[j]);
-        const unsigned long long f = fx(cx[j]);
+    for (int j = 0; j < nt; ++j) {
+      const float x = col[j * kHT];
+      if (x >= A && x < B) {
+        const int bk = bucket(x);
+        const unsigned long long f = fx(x);
         atomicAdd(&hs->hcnt[bk], 1u);
         atomicAdd(&hs->hlo[bk], unsigned(f) & 0x7ffffu);
         atomicAdd(&hs->hhi[bk], unsigned(f >> 19));
       }
     }
     barh(h);
+    if (ht == 0) STAMP(stats, 25);
     // suffix scan over buckets 127..0 (thread t owns bucket 127 - t)
     const unsigned hc = hs->hcnt[kHT - 1 - ht];
     const unsigned long long hv = ((unsigned long long)hs->hhi[kHT - 1 - ht] << 19) + hs->hlo[kHT - 1 - ht];
@@ -239,15 +252,16 @@ __device__ __forceinline__ bool half_select(const ListEntry* hl, const int* wn, 
     }
     if (ht == kHT - 1 && m_incl <= tgt) hs->bstar = -2;  // rounding only: the whole bracket is kept
     barh(h);
+    if (ht == 0) STAMP(stats, 26);
     const int bstar = hs->bstar;
     if (bstar < 0) {
       // keep everything down to the last entry of the bracket in the reference's order
       unsigned long long kk = kNone;
-#pragma unroll
-      for (int j = 0; j < kPer; ++j) {
-        if (cx[j] >= A && cx[j] < B) {
-          const unsigned idx = unsigned(ld_list_i(entry(j)));
-          const unsigned long long k2 = ((unsigned long long)okey(cx[j]) << 32) | (0xffffffffu - idx);
+      for (int j = 0; j < nt; ++j) {
+        const float x = col[j * kHT];
+        if (x >= A && x < B) {
+          const unsigned idx = unsigned(col_index_of(bmt, j, ht));
+          const unsigned long long k2 = ((unsigned long long)okey(x) << 32) | (0xffffffffu - idx);
           kk = k2 < kk ? k2 : kk;
         }
       }
@@ -270,17 +284,24 @@ __device__ __forceinline__ bool half_select(const ListEntry* hl, const int* wn, 
     const unsigned long long gb_new = hs->gb_new;
     if (bcount <= kHT) {
       // ---- the bucket's entries, ordered exactly like the reference's sort
-#pragma unroll
-      for (int j = 0; j < kPer; ++j) {
-        if (cx[j] >= A && cx[j] < B && bucket(cx[j]) == bstar) {
+      for (int j = 0; j < nt; ++j) {
+        const float x = col[j * kHT];
+        if (x >= A && x < B && bucket(x) == bstar) {
           const int pos = atomicAdd(&hs->ncand, 1);
-          hs->cand_x[pos] = cx[j];
-          hs->cand_f[pos] = fx(cx[j]);
-          hs->cand_i[pos] = ld_list_i(entry(j));
+          hs->cand_x[pos] = x;
+          hs->cand_f[pos] = fx(x);
+          hs->cand_i[pos] = (j << 8) | ht;  // (owner thread, its entry number): the row index is recovered below
         }
       }
       barh(h);
       const int n = hs->ncand;
+      // one thread per candidate walks the owner's bit-map column (in parallel: not once per trip of the loop above)
+      if (ht < n) {
+        const int code = hs->cand_i[ht], owner = code & 0xff;
+        hs->cand_i[ht] = col_index_of(bmt - ht + owner, code >> 8, owner);
+      }
+      barh(h);
+      if (ht == 0) STAMP(stats, 27);
       *ncand_out = n;
       int Pn = 16;
       while (Pn < n) Pn <<= 1;
@@ -306,6 +327,7 @@ __device__ __forceinline__ bool half_select(const ListEntry* hl, const int* wn, 
         hs->res_ok = 1;
       }
       barh(h);
+      if (ht == 0) STAMP(stats, 28);
       if (hs->res_ok) {
         solved = true;
         rec.Z = float(double(hs->gb_new) / double(S));
@@ -317,11 +339,11 @@ __device__ __forceinline__ bool half_select(const ListEntry* hl, const int* wn, 
       break;
     }
     // crowded bucket: shrink the bracket to the bucket's value range and go one level down
-#pragma unroll
-    for (int j = 0; j < kPer; ++j) {
-      if (cx[j] >= A && cx[j] < B && bucket(cx[j]) == bstar) {
-        atomicMin(&hs->kmin, okey(cx[j]));
-        atomicMax(&hs->kmax, okey(cx[j]));
+    for (int j = 0; j < nt; ++j) {
+      const float x = col[j * kHT];
+      if (x >= A && x < B && bucket(x) == bstar) {
+        atomicMin(&hs->kmin, okey(x));
+        atomicMax(&hs->kmax, okey(x));
       }
     }
     barh(h);
@@ -333,12 +355,6 @@ __device__ __forceinline__ bool half_select(const ListEntry* hl, const int* wn, 
     barh(h);
   }
   return solved;
-}
-
-// The whole block's select of one row (rows half_select hands back: ties).  Out of line: rare.
-__device__ __noinline__ void joint_select(const ListEntry* list, int nlist, float GB, float Z, double target, float m0,
-                                          Scratch3* sc, int& phase, RowRecord& rec, int* stats) {
-  list_select_body<kPairCap>(list, nlist, -1, 0.0f, 0.0f, GB, Z, target, m0, sc, phase, rec, stats);
 }
 
 // General search of one row by the 256 workers (rare): exact row maximum first, then the windowed
@@ -364,10 +380,10 @@ template <class TIn>
 __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant__ SplitParams P) {
   extern __shared__ __align__(128) unsigned char smem[];
   float* hist_all = reinterpret_cast<float*>(smem + size_t(2) * kPStages * kStageBytes);
-  ListEntry* slist = reinterpret_cast<ListEntry*>(hist_all + kHB * kT3);  // [2 rows][4 warps][kWarpCap] entries
-  Scratch3* sc = reinterpret_cast<Scratch3*>(slist + 2 * kHalfCap);
+  Scratch3* sc = reinterpret_cast<Scratch3*>(hist_all + kHB * kT3);
   PairSync* ps = reinterpret_cast<PairSync*>(sc + 1);
   HalfScratch* hsc = reinterpret_cast<HalfScratch*>(ps + 1);
+  unsigned char* bm_all = reinterpret_cast<unsigned char*>(hsc + 2);  // [2 rows][nchunk][128] u16 (only with a nucleus)
 
   const int tid = threadIdx.x;
   const int gamma = P.gamma, V = P.V;
@@ -384,6 +400,7 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
       }
     mbar_fence_init();
     ps->nlist = 0;
+    ps->colfull[0] = ps->colfull[1] = 0;
   }
   __syncthreads();
   // nothing above touches global memory; inputs, hints and the workspace are ordered from here on
@@ -427,13 +444,12 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
   unsigned char* ring = smem + size_t(h) * kPStages * kStageBytes;
   float* hist = hist_all + h * kHB * kHT;  // this half's [bucket][thread] histogram
   float* hp = hist + ht;
+  float* col = hp;  // pass 2: the thread's histogram column becomes its list column (same [slot][thread] layout)
+  unsigned short* bmt = reinterpret_cast<unsigned short*>(bm_all + size_t(h) * pair_bitmap_bytes(nchunk)) + ht;
   const int bits0 = __float_as_int(kHTmin + kHMagic);
   ListEntry* list = P.lists + (long long)blockIdx.x * kListCap;
   int phase = 0;
   unsigned seq = 0;
-#pragma unroll
-  for (int b = 0; b < kHB; ++b) hp[b * kHT] = 0.0f;
-
 #pragma unroll 1
   for (int pr = blockIdx.x; pr < npairs; pr += gridDim.x) {
     const int job = 2 * pr + h;
@@ -454,7 +470,8 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
     const uint4 hint = __ldg(reinterpret_cast<const uint4*>(&P.hints[jb.is_target]));
     const float m0 = int(hint.w) != 0 ? __uint_as_float(hint.x) : 0.0f;
 
-    int state = 0;
+    int state = 0, nt = 0;
+    float xa = INFINITY, xb = INFINITY;  // the boundary bucket's interval of scaled logits
     float Z = 0.0f, mxl = m0, GB = 0.0f;
     double target = 0.0;
     if (have && !nucleus) {
@@ -480,7 +497,9 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
       mxl = mx * kLog2e;
       state = (!(fabsf(mxl - m0) <= 32.0f) || !(Z < INFINITY) || !(Z > 0.0f)) ? 3 : 1;
     } else if (have) {
-      // ---- pass 1: per-thread mass histogram over the exponent
+      // ---- pass 1: per-thread mass histogram over the exponent (the column held the last row's list: clear it)
+#pragma unroll
+      for (int b = 0; b < kHB; ++b) hp[b * kHT] = 0.0f;
 #pragma unroll 1
       for (int c = 0; c < nchunk; ++c) {
         PAIR_STAGE_BEGIN(c)
@@ -521,7 +540,6 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
 #pragma unroll
         for (int k = 0; k < kHT / 32; ++k) {
           s += hist[b * kHT + k * 32 + lane];
-          hist[b * kHT + k * 32 + lane] = 0.0f;  // ready for the next row
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
@@ -556,73 +574,44 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
       }
       // ---- pass 2: the boundary bucket's entries (always consumed: the producer streams the row twice).
       // The bucket is an interval [xa, xb) of scaled logits (the bucket function is monotone): two compares.
-      float xa = INFINITY, xb = INFINITY;
+      xa = INFINITY, xb = INFINITY;
       if (bstar > 0 && !slow) {
         if (!bucket_edge(bits0 + bstar, m0, &xa)) slow = true;
         if (bstar < kHB - 1 && !bucket_edge(bits0 + bstar + 1, m0, &xb)) slow = true;
         if (slow) xa = INFINITY;
       }
-      // Per stage: the 16-bit hit mask of the thread's entries (two compares and a bit each), a warp
-      // prefix sum of the hit counts, then one short trip per hit that copies the entry from the stage to
-      // the WARP's list region (any slot order will do) - no atomics, addresses in the shared window.
-      const unsigned wl_s = smem_u32(slist + (h * kHW + hw) * kWarpCap);
-      int wcnt = 0;
+      // Per stage: every entry of the interval goes to the thread's OWN list column with a predicated store
+      // (5 instructions per entry, no atomics, no shuffles, no divergent trips); the stage's 16-bit mask of
+      // captured positions goes to the bit map, from which the select recovers the indices it needs.
+      const unsigned lp0 = smem_u32(col), lim = lp0 + unsigned(kColSlots - 4) * unsigned(kHT * 4);
+      unsigned lp = lp0;
 #ifndef ABL_NOPASS2
 #pragma unroll 1
       for (int c = 0; c < nchunk; ++c) {
         PAIR_STAGE_BEGIN(c)
-#ifdef ABL_NOPICK
-        if (v4[0].x == 12345.678f) wcnt += i00;
-#else
-        unsigned hm = 0;
+        unsigned hm = 0u;
+#define COL_GROUP(u)                                                  \
+  {                                                                   \
+    const float xe = lp < lim ? xa : INFINITY; /* column full: stop */ \
+    col_take(lp, hm, v4[u].x, xe, xb, 1u << (4 * u));                  \
+    col_take(lp, hm, v4[u].y, xe, xb, 2u << (4 * u));                  \
+    col_take(lp, hm, v4[u].z, xe, xb, 4u << (4 * u));                  \
+    col_take(lp, hm, v4[u].w, xe, xb, 8u << (4 * u));                  \
+  }
         if (i00 + 3 * kHT * 4 < V) {  // every stage but a row's last one is whole
-          _Pragma("unroll") for (int u = 0; u < 4; ++u) {
-            hit_or(hm, v4[u].x, xa, xb, 1u << (4 * u)), hit_or(hm, v4[u].y, xa, xb, 2u << (4 * u));
-            hit_or(hm, v4[u].z, xa, xb, 4u << (4 * u)), hit_or(hm, v4[u].w, xa, xb, 8u << (4 * u));
-          }
+          COL_GROUP(0) COL_GROUP(1) COL_GROUP(2) COL_GROUP(3)
         } else {
-          _Pragma("unroll") for (int u = 0; u < 4; ++u) {
-            if (i00 + u * kHT * 4 < V) {
-              hit_or(hm, v4[u].x, xa, xb, 1u << (4 * u)), hit_or(hm, v4[u].y, xa, xb, 2u << (4 * u));
-              hit_or(hm, v4[u].z, xa, xb, 4u << (4 * u)), hit_or(hm, v4[u].w, xa, xb, 8u << (4 * u));
-            }
-          }
+          if (i00 < V) COL_GROUP(0)
+          if (i00 + kHT * 4 < V) COL_GROUP(1)
+          if (i00 + 2 * kHT * 4 < V) COL_GROUP(2)
+          if (i00 + 3 * kHT * 4 < V) COL_GROUP(3)
         }
-        if (__any_sync(0xffffffffu, hm != 0u)) {
-          const int nh = __popc(hm);
-          int inc = nh;
-          _Pragma("unroll") for (int d = 1; d < 32; d <<= 1) {
-            const int o = __shfl_up_sync(0xffffffffu, inc, d);
-            if (lane >= d) inc += o;
-          }
-          int pos = wcnt + inc - nh;
-          wcnt += __shfl_sync(0xffffffffu, inc, 31);
-          const unsigned st_s = smem_u32(st);
-          while (hm) {
-            const int k = __ffs(hm) - 1;
-            hm &= hm - 1;
-            const int off = ((k >> 2) * kHT + ht) * 4 + (k & 3);
-            float x;
-            if (kElt == 4) {
-              asm volatile("ld.shared.f32 %0, [%1];" : "=f"(x) : "r"(st_s + unsigned(off) * 4u));
-            } else {
-              unsigned short raw;
-              asm volatile("ld.shared.u16 %0, [%1];" : "=h"(raw) : "r"(st_s + unsigned(off) * 2u));
-              x = __uint_as_float(unsigned(raw) << 16);
-            }
-            if (temp != 1.0f) x = __fdiv_rn(x, temp);
-            if (pos < kWarpCap)
-              asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(wl_s + unsigned(pos) * 8u), "r"(__float_as_int(x)),
-                           "r"(c * kStageElems + off)
-                           : "memory");
-            ++pos;
-          }
-        }
-#endif
+        bmt[c * kHT] = (unsigned short)hm;
         PAIR_STAGE_END()
       }
 #endif
-      if (lane == 0) ps->wcnt[h][hw] = wcnt;
+      nt = int((lp - lp0) / unsigned(kHT * 4));
+      if (__any_sync(0xffffffffu, lp >= lim) && lane == 0) ps->colfull[h] = 1;
       if (ht == 0) STAMP(P.stats, 10);
       state = slow ? 3 : (bstar > 0 ? 2 : 4);
 #if defined(ABL_NOPASS2) || defined(ABL_NOSELECT) || defined(ABL_NOPICK)
@@ -634,16 +623,13 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
     rec.m0 = m0, rec.Z = Z, rec.xstar = -INFINITY, rec.istar = 0x7fffffff;
     rec.sel = 0.0f, rec.mxl = mxl, rec.dens = 0.0f;
     if (state == 2) {
-      barh(h);  // the half's four warp lists and their counts are complete
-      bool fits = true;
-#pragma unroll
-      for (int w = 0; w < kHW; ++w) fits = fits && ps->wcnt[h][w] <= kWarpCap;
-      if (!fits) {
-        state = 3;  // more entries than the list holds: general search below
+      barh(h);  // every column and bit map of the half is complete
+      if (ps->colfull[h]) {
+        state = 3;  // a thread ran out of list slots: general search below
       } else {
         int ncand = 0;
-        const bool ok = half_select(slist + h * kHalfCap, ps->wcnt[h], h, ht, GB, Z, target, m0, hsc + h, rec, &ncand);
-        if (!ok) state = 5;  // ties: the whole block's bisection below
+        const bool ok = half_select(col, nt, bmt, h, ht, xa, xb, GB, Z, target, m0, hsc + h, rec, &ncand, P.stats);
+        if (!ok) state = 3;  // more equal values than the finish can order: general search below
         if (P.stats && ht == 0) {
           atomicAdd(&P.stats[0], 1);
           atomicAdd(&P.stats[ok ? 16 : 17], 1);
@@ -656,6 +642,7 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
       hr.target = target, hr.GB = GB, hr.Z = Z, hr.m0 = m0, hr.mxl = mxl, hr.state = state;
       hr.pad[0] = hr.pad[1] = hr.pad[2] = 0;
       ps->half[h] = hr;
+      ps->colfull[h] = 0;  // (read above, behind the half barrier; the next row sets it again after the join)
       if (state == 1 || state == 2 || state == 4) {
         if (tok >= 0 && tok < V) {
           const float e = kept(rec, xtok, int(tok)) ? row_exp(xtok, rec.m0) : 0.0f;
@@ -668,37 +655,6 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
     bar3();  // ---- the halves join: rows that need the whole block (rare) are finished one after the other
 
     const int st[2] = {ps->half[0].state, ps->half[1].state};
-#pragma unroll 1
-    for (int hh = 0; hh < 2; ++hh) {
-      if (st[hh] != 5) continue;
-      const HalfRow hr = ps->half[hh];
-      RowRecord r2;
-      r2.m0 = hr.m0, r2.Z = hr.Z, r2.xstar = -INFINITY, r2.istar = 0x7fffffff;
-      r2.sel = 0.0f, r2.mxl = hr.mxl, r2.dens = 0.0f;
-      // the four warp regions become one list, then the block's select in its linear-list mode
-      ListEntry* hl = slist + hh * kHalfCap;
-      int total = ps->wcnt[hh][0];
-#pragma unroll 1
-      for (int w = 1; w < kHW; ++w) {
-        const int n = ps->wcnt[hh][w];
-        ListEntry t0 = ListEntry{0.0f, 0}, t1 = t0;
-        if (tid < n) t0 = hl[w * kWarpCap + tid];
-        if (tid + kT3 < n) t1 = hl[w * kWarpCap + tid + kT3];
-        bar3();
-        if (tid < n) hl[total + tid] = t0;
-        if (tid + kT3 < n) hl[total + tid + kT3] = t1;
-        bar3();
-        total += n;
-      }
-      joint_select(hl, total, hr.GB, hr.Z, hr.target, hr.m0, sc, phase, r2, P.stats);
-      if (tid == hh * kHT) {
-        if (tok >= 0 && tok < V) {
-          const float e = kept(r2, xtok, int(tok)) ? row_exp(xtok, r2.m0) : 0.0f;
-          r2.sel = __fdiv_rn(e, r2.Z);
-        }
-        store_record(&P.records[2 * pr + hh], r2);
-      }
-    }
 #pragma unroll 1
     for (int hh = 0; hh < 2; ++hh) {
       if (st[hh] != 3) continue;

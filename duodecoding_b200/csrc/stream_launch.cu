@@ -64,6 +64,7 @@ cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t s
 
 }  // namespace
 
+constexpr size_t kPairSmemMax = 232448;  // the scan kernel's shared memory depends on V (bit maps): opt in to the limit once
 constexpr int kMaxGrid = 320;   // blocks of the persistent scan kernel (two per SM): one scratch list each
 
 // hints | row records | per-sequence cells of the sample kernel | one scratch list per scan block (general search) |
@@ -166,20 +167,23 @@ bool stream_try_launch(const StreamCall& c, int* rc) {
     Q.row0_rule = c.row0_rule;
     const dim3 g2(unsigned((c.Vt + kSlice3 - 1) / kSlice3), unsigned(c.B) + 1u);  // + the block row that aggregates the hints
     if (pairp) {
-      const size_t smem = pair::pair_smem_bytes();
+      const bool any_nucleus = (c.top_p > 0.0f) || (c.draft_top_p > 0.0f);
+      const size_t smem = pair::pair_smem_bytes(any_nucleus ? int((c.Vt + kStageElems - 1) / kStageElems) : 0);
+      if (smem > kPairSmemMax) return false;  // (vocabularies beyond ~700 k with a nucleus: general kernel)
       const int sms = stream_sm_count();
+      const int per_sm = smem <= 115712 ? 2 : 1;  // two blocks per SM while the bit maps leave room (V <= ~40 k)
       const int npairs = int((rows + 1) / 2);
-      const int grid = npairs < 2 * sms ? npairs : 2 * sms;  // two blocks per SM, two rows per block
+      const int grid = npairs < per_sm * sms ? npairs : per_sm * sms;  // two rows per block
       cudaError_t e;
       const size_t smem2 = sample_smem_bytes();
       if (c.dtype == DUODEC_F32) {
-        e = ensure_stream_smem(reinterpret_cast<const void*>(pair::row_pair_kernel<float>), smem);
+        e = ensure_stream_smem(reinterpret_cast<const void*>(pair::row_pair_kernel<float>), kPairSmemMax);
         if (e == cudaSuccess) e = ensure_stream_smem(reinterpret_cast<const void*>(seq_sample_tma_kernel<float>), smem2);
         if (e == cudaSuccess && (c.phases & 1))
           e = launch_pdl(pair::row_pair_kernel<float>, dim3(grid), dim3(pair::kPT), smem, c.stream, Q);
         if (e == cudaSuccess && (c.phases & 2)) e = launch_pdl(seq_sample_tma_kernel<float>, g2, dim3(kT3), smem2, c.stream, Q);
       } else {
-        e = ensure_stream_smem(reinterpret_cast<const void*>(pair::row_pair_kernel<__nv_bfloat16>), smem);
+        e = ensure_stream_smem(reinterpret_cast<const void*>(pair::row_pair_kernel<__nv_bfloat16>), kPairSmemMax);
         if (e == cudaSuccess)
           e = ensure_stream_smem(reinterpret_cast<const void*>(seq_sample_tma_kernel<__nv_bfloat16>), smem2);
         if (e == cudaSuccess && (c.phases & 1))
