@@ -59,6 +59,10 @@ SIGNATURES = {
     "duodec_max_fn": (c_int, [c_void_p, c_int, c_i64, c_int, c_int, c_void_p, c_i64, c_void_p]),
     "duodec_topk_rebuild": (c_int, [c_void_p, c_int, c_i64, c_void_p, c_i64, c_int, c_int, c_int, c_int, c_void_p]),
     "duodec_kv_truncate": (c_int, [c_void_p, c_void_p, c_i64, c_int, c_void_p]),
+    "duodec_uncertainty_tokens": (
+        c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_i64, c_int, c_void_p, c_void_p]),
+    "duodec_compressed_vocab_size": (
+        c_int, [c_void_p, c_void_p, c_int, ctypes.c_double, ctypes.c_double, c_void_p, c_void_p]),
     "duodec_compact_nonzero": (
         c_int, [c_void_p, c_int, c_i64, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "duodec_shard_topk_apply": (

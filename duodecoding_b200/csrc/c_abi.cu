@@ -9,6 +9,7 @@
 
 #include "../../include/duodec.h"
 #include "prob_kernels.cuh"
+#include "cuhlm_kernels.cuh"
 #include "row_kernels.cuh"
 #include "shard_kernels.cuh"
 #include "stream_launch.h"
@@ -493,6 +494,33 @@ int duodec_shard_topk_apply(const void* x, int dtype, int64_t in_stride, void* o
     shard_topk_apply_kernel<__nv_bfloat16><<<rows, 256, 0, st>>>(
         static_cast<const __nv_bfloat16*>(x), in_stride, static_cast<__nv_bfloat16*>(out), out_stride, Vs, v_begin,
         tau, istar, fill, total);
+  return int(cudaGetLastError());
+}
+
+int duodec_uncertainty_tokens(const void* logits, int dtype, int V, const float* temps, const float* noise,
+                              int64_t noise_stride, int M, int64_t* tokens, void* stream) {
+  if (V <= 0 || M < 0) return DUODEC_EINVAL;
+  if (M == 0) return 0;
+  if (!logits || !temps || !noise || !tokens || (dtype != DUODEC_F32 && dtype != DUODEC_BF16)) return DUODEC_EINVAL;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dtype == DUODEC_F32)
+    uncertainty_tokens_kernel<float><<<M, kThreads, 0, st>>>(static_cast<const float*>(logits), V, temps, noise,
+                                                            noise_stride, reinterpret_cast<long long*>(tokens));
+  else
+    uncertainty_tokens_kernel<__nv_bfloat16><<<M, kThreads, 0, st>>>(static_cast<const __nv_bfloat16*>(logits), V,
+                                                                    temps, noise, noise_stride,
+                                                                    reinterpret_cast<long long*>(tokens));
+  return int(cudaGetLastError());
+}
+
+int duodec_compressed_vocab_size(const float* sorted_probs, const double* prefix, int V, double denominator,
+                                 double theta, int32_t* k_out, void* stream) {
+  if (V <= 1) return DUODEC_EINVAL;
+  if (!sorted_probs || !prefix || !k_out || !(denominator > 0.0)) return DUODEC_EINVAL;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  cudaError_t e = cudaMemsetAsync(k_out, 0x7f, sizeof(int32_t), st);  // 0x7f7f7f7f: "no k found"
+  if (e != cudaSuccess) return int(e);
+  compressed_vocab_kernel<<<(V - 1 + 255) / 256, 256, 0, st>>>(sorted_probs, prefix, V, denominator, theta, k_out);
   return int(cudaGetLastError());
 }
 

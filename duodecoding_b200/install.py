@@ -50,6 +50,14 @@ def install(package: str = "src") -> Dict[str, List[str]]:
             _SAVED.append((sim, name, sim.__dict__[name]))
             setattr(sim, name, staticmethod(getattr(communication, name.lstrip("_"))))
             done.setdefault("communication", []).append(name)
+        cuhlm = getattr(importlib.import_module(f"{package}.communication"), "CUHLM", None)
+        if cuhlm is not None:  # the CUHLM helpers (src/communication.py:541-575, :681-755)
+            _SAVED.append((cuhlm, "calculate_uncertainty", cuhlm.__dict__["calculate_uncertainty"]))
+            cuhlm.calculate_uncertainty = staticmethod(communication.calculate_uncertainty)
+            _SAVED.append((cuhlm, "_calculate_compressed_vocab_size", cuhlm.__dict__["_calculate_compressed_vocab_size"]))
+            cuhlm._calculate_compressed_vocab_size = communication.CUHLM._calculate_compressed_vocab_size
+            done.setdefault("communication", []).extend(["CUHLM.calculate_uncertainty",
+                                                         "CUHLM._calculate_compressed_vocab_size"])
     except Exception:  # noqa: BLE001
         pass
     return done

@@ -207,6 +207,20 @@ int duodec_shard_topk_apply(const void* x, int dtype, int64_t in_stride, void* o
                             int Vs, int v_begin, const float* tau, const int32_t* istar, const float* fill,
                             const float* total, void* stream);
 
+/* ---- CUHLM helpers (CommunicationSimulator) --------------------------------------------
+ * duodec_uncertainty_tokens: calculate_uncertainty (src/communication.py:541-575) - for each of M
+ *   temperatures temps[m] > 0 one draw from softmax(logits / temps[m]) of ONE row logits[V], as
+ *   argmax_i p_i / noise[m, i] (noise: Exp(1), what torch.multinomial draws); tokens[M] int64.  The
+ *   uncertainty is the fraction of tokens that differ from the draft token (one reduction on M values).
+ * duodec_compressed_vocab_size: _calculate_compressed_vocab_size (src/communication.py:681-755) - with the
+ *   probabilities sorted descending (float32) and their inclusive float64 prefix sums, the smallest
+ *   k in [1, V) with sum_{i>=k} |s_i - (1 - sum_{i<k} s_i)/(V-k)| / denominator <= theta; *k_out is
+ *   0x7f7f7f7f when no k qualifies (the caller applies the reference's conservative default). */
+int duodec_uncertainty_tokens(const void* logits, int dtype, int V, const float* temps, const float* noise,
+                              int64_t noise_stride, int M, int64_t* tokens, void* stream);
+int duodec_compressed_vocab_size(const float* sorted_probs, const double* prefix, int V, double denominator,
+                                 double theta, int32_t* k_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

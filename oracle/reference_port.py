@@ -56,6 +56,10 @@ __all__ = [
     "top_p_margin",
     "accept_margin",
     "race_gap",
+    "calculate_uncertainty_tokens",
+    "calculate_uncertainty",
+    "softplus",
+    "compressed_vocab_size",
 ]
 
 
@@ -451,3 +455,57 @@ def race_gap(probs: torch.Tensor, noise: torch.Tensor) -> torch.Tensor:
     keys = probs.double() / noise.double()
     top2 = torch.topk(keys, 2, dim=-1)[0]
     return (top2[..., 0] - top2[..., 1]) / top2[..., 0].clamp_min(1e-300)
+
+
+# --------------------------------------------------------------------------
+# CUHLM helpers (CommunicationSimulator)
+# --------------------------------------------------------------------------
+def calculate_uncertainty_tokens(logits: torch.Tensor, temperatures: torch.Tensor, noise: torch.Tensor) -> torch.Tensor:
+    """The M tempered draws of ``calculate_uncertainty`` (src/communication.py:556-570) with the
+    temperatures and the multinomial's Exp(1) noise injected: tokens [M]."""
+    if logits.dim() > 1:
+        logits = logits[0]
+    pert = logits.float().unsqueeze(0) / temperatures.float().unsqueeze(1)
+    pert = pert - pert.max(dim=1, keepdim=True)[0]
+    return race_argmax(torch.softmax(pert, dim=-1), noise)
+
+
+def calculate_uncertainty(logits, temperatures, noise, draft_token: int) -> float:
+    """src/communication.py:541-575: share of the M draws that differ from the draft token."""
+    toks = calculate_uncertainty_tokens(logits, temperatures, noise)
+    return int((toks != int(draft_token)).sum().item()) / int(toks.numel())
+
+
+def softplus(z: float, eta: float = 1.0) -> float:
+    """src/communication.py:678-679."""
+    return float(torch.log(1 + torch.exp(eta * torch.tensor(float(z)))) / eta)
+
+
+def compressed_vocab_size(uncertainty: float, current_probs: torch.Tensor, vocab_size: int, theta: float = 0.1,
+                          draft_token: Optional[int] = None, default_size: int = 300) -> int:
+    """``_calculate_compressed_vocab_size`` (src/communication.py:681-755): smallest k whose uniform-refill
+    error bound is <= theta.  Same arithmetic as the reference's loops (fp32 ``torch.sum`` of the head,
+    float64 accumulation of the tail), the inner Python loop written as one vector expression per k."""
+    if current_probs is None or current_probs.numel() == 0:
+        return 0
+    if len(current_probs) != vocab_size:
+        return max(1, min(300, vocab_size // 100))
+    a, b = 0.815, -0.066
+    beta_d = max(0, min(1, a * uncertainty + b))
+    sorted_probs, _ = torch.sort(current_probs, descending=True)
+    if draft_token is None or not (0 <= draft_token < len(current_probs)):
+        x_d = sorted_probs[0].item()
+    else:
+        x_d = current_probs[draft_token].item()
+    denominator = (1 - x_d) * softplus(-1.0) + x_d * softplus(-beta_d)
+    if denominator <= 0:
+        return 30
+    s64 = sorted_probs.double()
+    for k in range(1, vocab_size):
+        top_k_sum = torch.sum(sorted_probs[:k]).item()
+        residual = 1.0 - top_k_sum
+        uniform = 0 if residual <= 0 else residual / (vocab_size - k)
+        numerator = float((s64[k:] - uniform).abs().sum())
+        if numerator / denominator <= theta:
+            return k
+    return min(default_size, vocab_size // 100)

@@ -396,3 +396,47 @@ def test_verify_draft_sequence_comm_accounting_and_empty_history(mods, dev):  # 
     ac, n = dops.verify_draft_sequence(Cache(q[:, :4], V), Cache(p, V), x, P, gamma, comm_simulator=comm,
                                        transfer_mode="batch_before", decoding_metrics=metrics)
     assert (ac, n) == (0, P - 1) and comm.calls == [] and metrics["draft_generated_tokens"] == 0
+
+
+def test_cuhlm_helpers_match_reference_goldens_and_oracle(mods, dev):
+    """CUHLM.calculate_uncertainty / _calculate_compressed_vocab_size (src/communication.py:541-575, :681-755)."""
+    import os
+    from unittest.mock import patch
+
+    import numpy as np
+
+    import duodecoding_b200.ops as ops
+    comm = mods[3]
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "cuhlm_v1.npz"))
+    for ci in range(3):  # the reference's own outputs, with its temperatures and multinomial noise injected
+        pre = f"unc/{ci}/"
+        M, theta_max, draft = z[pre + "params"]
+        u, noise = torch.from_numpy(z[pre + "u"]).to(dev), torch.from_numpy(z[pre + "noise"]).to(dev)
+        with patch.object(torch, "rand", lambda *a, **k: u.clone()), \
+                patch.object(ops, "draw_noise", lambda rows, v, d, generator=None: noise):
+            got = comm.CUHLM.calculate_uncertainty(torch.from_numpy(z[pre + "logits"]).to(dev), M=int(M),
+                                                   theta_max=float(theta_max), draft_token=int(draft))
+        assert got == float(z[pre + "value"][0]), ci
+    for ci in range(5):
+        pre = f"kstar/{ci}/"
+        unc, theta, draft = z[pre + "params"]
+        probs = torch.from_numpy(z[pre + "probs"]).to(dev)
+        sim = comm.CUHLM(vocab_size=len(probs))
+        got = sim._calculate_compressed_vocab_size(float(unc), probs, theta=float(theta),
+                                                   draft_token=None if draft < 0 else int(draft))
+        assert got == int(z[pre + "k"][0]), (ci, got)
+    # a full-size vocabulary against the oracle (the reference's O(V^2) loop would take hours here)
+    g = torch.Generator().manual_seed(8)
+    V = 32000
+    logits = torch.randn(V, generator=g) * 3
+    temps = torch.clamp(torch.rand(20, generator=g) * 2.0, min=1e-6)
+    noise = torch.empty(20, V).exponential_(1, generator=g)
+    want = oracle.calculate_uncertainty_tokens(logits, temps, noise)
+    got = comm.uncertainty_tokens(logits.to(dev), temps.to(dev), noise.to(dev))
+    assert torch.equal(got.cpu(), want.reshape(-1))
+    probs = torch.softmax(logits, -1)
+    for unc, theta in ((0.3, 0.1), (0.9, 0.02)):
+        want_k = oracle.compressed_vocab_size(unc, probs, V, theta, 5)
+        assert comm.compressed_vocab_size(unc, probs.to(dev), V, theta, 5) == want_k
+    assert comm.CUHLM.calculate_uncertainty(None) == 1.0
+    assert comm.CUHLM(vocab_size=10)._calculate_compressed_vocab_size(0.5, probs[:7].to(dev)) == 1  # length mismatch rule

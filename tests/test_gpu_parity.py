@@ -516,3 +516,27 @@ def test_kv_truncate(ops, dev):
 def test_cpu_tensors_are_rejected(ops):
     with pytest.raises(RuntimeError):
         ops.norm_logits(torch.randn(2, 10), 1.0)
+
+
+def test_verify_fused_on_two_streams_does_not_share_a_workspace(ops, dev):
+    """Calls with the same (B, gamma) issued on different CUDA streams may overlap on the device: each stream
+    gets its own workspace (records, per-sequence cells, hints), so the results equal the serial ones."""
+    cases = [_make_case(51 + i, 16, 4, 32000, 1.0, 1.0, 0, 0.9) for i in range(2)]
+    args = [[t.to(dev) for t in c] for c in cases]
+    serial = [{k: v.clone() for k, v in ops.verify_fused(*a, 1.0, 0, 0.9).items()} for a in args]
+    torch.cuda.synchronize()
+    streams = [torch.cuda.Stream(device=dev) for _ in range(2)]
+    outs = [[], []]
+    for it in range(20):
+        for s in range(2):
+            with torch.cuda.stream(streams[s]):
+                outs[s].append({k: v.clone() for k, v in ops.verify_fused(*args[s], 1.0, 0, 0.9).items()})
+    torch.cuda.synchronize()
+    keys = {k[:2] for k in ops._WORKSPACES}
+    assert len({k for k in ops._WORKSPACES if k[2:] == (16, 4)}) >= 3, keys  # default stream + the two streams
+    for s in range(2):
+        for got in outs[s]:
+            for k in ("accepted_len", "token", "accept_mask"):
+                assert torch.equal(got[k], serial[s][k]), (s, k)
+            # (each workspace carries its own exponent-offset hint: a boundary entry may flip, cf. NUCLEUS_RTOL)
+            torch.testing.assert_close(got["selected_target_p"], serial[s]["selected_target_p"], rtol=NUCLEUS_RTOL, atol=1e-9)

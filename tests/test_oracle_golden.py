@@ -116,3 +116,29 @@ def test_finalize_and_resolve_positions(golden):
         assert [a, n, tok, int(plan.all_accepted)] == want
         t_end = plan.target_end_pos_accept if plan.all_accepted else plan.target_end_pos_reject
         assert [plan.draft_end_pos, t_end] == golden[f"resolve/{name}/rollbacks"].tolist()
+
+
+def test_cuhlm_oracle_is_pinned_to_the_reference():
+    """oracle.calculate_uncertainty / compressed_vocab_size against outputs of the UNMODIFIED reference
+    (tests/golden/cuhlm_v1.npz, written by oracle/gen_golden_cuhlm.py)."""
+    import os
+
+    import numpy as np
+    import torch
+
+    import oracle
+
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "cuhlm_v1.npz"))
+    for ci in range(3):
+        pre = f"unc/{ci}/"
+        M, theta_max, draft = z[pre + "params"]
+        temps = torch.clamp(torch.from_numpy(z[pre + "u"]) * float(theta_max), min=1e-6)
+        got = oracle.calculate_uncertainty(torch.from_numpy(z[pre + "logits"]), temps, torch.from_numpy(z[pre + "noise"]),
+                                           int(draft))
+        assert got == float(z[pre + "value"][0]), ci
+    for ci in range(5):
+        pre = f"kstar/{ci}/"
+        unc, theta, draft = z[pre + "params"]
+        probs = torch.from_numpy(z[pre + "probs"])
+        got = oracle.compressed_vocab_size(float(unc), probs, len(probs), float(theta), None if draft < 0 else int(draft))
+        assert got == int(z[pre + "k"][0]), (ci, got)
