@@ -465,18 +465,24 @@ def run_ours(args):
     api = api_leg(wl, sets[0], dev, max(10, min(K, 100))) if rank == 0 else None
 
     # ---- end to end: pinned host logits -> HostVerifier -> pinned host results
-    hv = HostVerifier(wl.B, wl.gamma, wl.V, wl.dtype, dev, nsplit=4)
+    hv = HostVerifier(wl.B, wl.gamma, wl.V, wl.dtype, dev)
     hsets = []
-    for s in sets[:2]:
-        hsets.append(tuple(t.cpu().pin_memory() for t in s[:4]))
+    for s in sets[:2]:  # two pinned input sets (the producer's double buffer), filled before the timed region
+        hs = hv.host_set()
+        hs["draft"].copy_(s[0][:, :wl.gamma])
+        hs["target"].copy_(s[1][:, :wl.gamma + 1])
+        hs["tokens"].copy_(s[2])
+        hs["r"].copy_(s[3])
+        hsets.append(hs)
+    torch.cuda.synchronize()
     Ke = max(3, min(K, 50))
     for i in range(3):
-        hv.verify(*hsets[i % 2], None, *warp)
+        hv.verify_set(hsets[i % 2], False, *warp)
     barrier()
     t0 = time.perf_counter()
     chk = 0
     for i in range(Ke):
-        res = hv.verify(*hsets[i % 2], None, *warp)
+        res = hv.verify_set(hsets[i % 2], False, *warp)
         chk += int(res["accepted_len"][0])  # the Python-int read the reference's callers make
     torch.cuda.synchronize()
     dte = time.perf_counter() - t0
@@ -537,7 +543,7 @@ def run_ours(args):
         "clocks": clk,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes, "steps": Ke,
                 "ms_per_step": dte / Ke * 1e3,
-                "api": "duodecoding_b200.host.HostVerifier.verify (pinned host logits, 4-way copy/verify pipeline)"},
+                "api": "duodecoding_b200.host.HostVerifier.verify_set (pinned host arena: one H2D copy, fused verify, one D2H copy, one sync)"},
         "gpu_launches": (3 if greedy else 2) * K,
         "api": api,
         "roofline": roofline,
@@ -723,13 +729,24 @@ def run_c4(args):
     dt = (time.perf_counter() - t0) / K
     clk = clocks.stop()
     # the dominant kernel alone: transfer_top_k rebuild of the 9 stage-2 rows
-    probs = caches[1][0].prob_history[:, P - 1:P - 1 + g1, :].contiguous()
+    dcm = caches[1][0]  # (the step's rollback shortened the history: restore the 9 stage-2 rows first)
+    dcm._current_seq_len = dcm._past_key_values.n = P - 1 + g1
+    dcm._prob_done = P - 1
+    probs = dcm.prob_history[:, P - 1:P - 1 + g1, :].contiguous()
+    assert probs.shape == (B, g1, V), probs.shape
     for _ in range(3):
         ops.topk_rebuild(probs, k, 0)
+    torch.cuda.synchronize()
+    side = torch.cuda.Stream(device=dev)  # (the host side of the op costs more than the kernel: time a graph of launches)
+    gr = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(gr, stream=side):
+        for _ in range(50):
+            ops.topk_rebuild(probs, k, 0)
+    gr.replay()
+    torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(50):
-        ops.topk_rebuild(probs, k, 0)
+    gr.replay()
     e1.record()
     torch.cuda.synchronize()
     kus = e0.elapsed_time(e1) * 1e3 / 50
@@ -756,7 +773,7 @@ def run_c4(args):
                 "note": "histories live on the device (the models write them); the read-back is the two accepted counts"},
         "roofline": {"bound": "hbm", "achieved": kbytes / (kus * 1e-6) / 1e9, "peak": peak, "unit": "GB/s",
                      "frac": kbytes / (kus * 1e-6) / 1e9 / peak, "traffic": None,
-                     "kernel": "topk_rebuild_kernel<__nv_bfloat16> mode 0, [8, 9, 32000], k=1024",
+                     "kernel": "rowsel::topk_reg_kernel<__nv_bfloat16> mode 0, [8, 9, 32000], k=1024 (graph of 50 launches)",
                      "alg_bytes_per_launch": kbytes, "us_per_launch": kus, "peak_source": peak_src,
                      "step_alg_bytes": alg, "step_GBps": alg / dt / 1e9},
         "cpu_baseline": cpu,

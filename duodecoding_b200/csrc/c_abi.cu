@@ -11,6 +11,7 @@
 #include "prob_kernels.cuh"
 #include "cuhlm_kernels.cuh"
 #include "row_kernels.cuh"
+#include "select_kernels.cuh"
 #include "shard_kernels.cuh"
 #include "stream_launch.h"
 #include "verify_kernels.cuh"
@@ -345,6 +346,33 @@ int duodec_topk_rebuild(const void* probs, int dtype, int64_t in_stride, void* o
   if (!probs || !out) return DUODEC_EINVAL;
   if (mode != 3 && (k <= 0 || k >= V)) return DUODEC_EINVAL;
   if (dtype != DUODEC_F32 && dtype != DUODEC_BF16) return DUODEC_EINVAL;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (g_team_override.load() == 0 && rowsel::select_smem_bytes(V) <= kMaxDynSmem) {
+    // the row fits one SM: one block per row, one read and one write of the row (select_kernels.cuh)
+    TopkParams S;
+    S.probs = probs, S.in_stride = in_stride, S.out = out, S.out_stride = out_stride;
+    S.rows = rows, S.V = V, S.k = k, S.mode = mode, S.per = V, S.slice_floats = 0;
+    const size_t bytes = rowsel::select_smem_bytes(V);
+    const size_t elt = dtype == DUODEC_F32 ? 4 : 2;
+    const int per = int(16 / elt);
+    // rows of <= 32768 entries with 128-bit aligned rows live in registers; the others in shared memory
+    const bool regs = V <= rowsel::kRegRowMax && V % per == 0 && (reinterpret_cast<size_t>(probs) & 15) == 0 &&
+                      (reinterpret_cast<size_t>(out) & 15) == 0 && (size_t(in_stride) * elt) % 16 == 0 &&
+                      (size_t(out_stride) * elt) % 16 == 0;
+    if (regs) {
+      if (dtype == DUODEC_F32) rowsel::topk_reg_kernel<float><<<unsigned(rows), rowsel::kRT, 0, st>>>(S);
+      else rowsel::topk_reg_kernel<__nv_bfloat16><<<unsigned(rows), rowsel::kRT, 0, st>>>(S);
+    } else if (dtype == DUODEC_F32) {
+      cudaError_t e = ensure_smem(reinterpret_cast<const void*>(rowsel::topk_select_kernel<float>));
+      if (e != cudaSuccess) return int(e);
+      rowsel::topk_select_kernel<float><<<unsigned(rows), rowsel::kRT, bytes, st>>>(S);
+    } else {
+      cudaError_t e = ensure_smem(reinterpret_cast<const void*>(rowsel::topk_select_kernel<__nv_bfloat16>));
+      if (e != cudaSuccess) return int(e);
+      rowsel::topk_select_kernel<__nv_bfloat16><<<unsigned(rows), rowsel::kRT, bytes, st>>>(S);
+    }
+    return int(cudaGetLastError());
+  }
   const int C = pick_team(V, 1);
   if (C == 0) return DUODEC_ETOOBIG;
   TopkParams P;
@@ -359,7 +387,6 @@ int duodec_topk_rebuild(const void* probs, int dtype, int64_t in_stride, void* o
   P.per = C == 1 ? V : ((((V + C - 1) / C) + 7) & ~7);
   P.slice_floats = ((P.per + 7) & ~7) + 8;
   const size_t smem = team_smem_bytes(V, 1, C);
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
   cudaError_t e = cudaSuccess;
   DISPATCH_TEAM(C, {
     if (dtype == DUODEC_F32) e = launch_team(topk_rebuild_kernel<float, kC>, P, rows, kC, smem, st);

@@ -486,7 +486,7 @@ def test_topk_rebuild_golden(golden, ops, dev):
     _close(ops.topk_rebuild(p3.to(dev), 16, 2), _t(golden["comm/compress_rebuild16"]))
 
 
-@pytest.mark.parametrize("team", [1, 2, 8])
+@pytest.mark.parametrize("team", [0, 1, 2, 8])  # 0: the one-block-per-row select kernel (default)
 def test_topk_rebuild_ties_lowest_index_first(ops, dev, team):
     g = torch.Generator().manual_seed(33)
     # bf16-grid probabilities: many exact ties at the k-th value
@@ -503,6 +503,67 @@ def test_topk_rebuild_ties_lowest_index_first(ops, dev, team):
             assert torch.equal(got1.cpu(), want1)
     finally:
         ops.set_team_size(0)
+
+
+def test_topk_select_kernel_edges(ops, dev):
+    """The one-block-per-row select kernel (select_kernels.cuh): ragged V (scalar tail, unaligned rows), k at both
+    ends, rows with thousands of equal values, bf16 rows, the comm modes - against the oracle restatements of
+    src/utils.py:751-784 and src/communication.py:288-395."""
+    g = torch.Generator().manual_seed(91)
+    for V in (5, 33, 1000, 4099, 32001):
+        p = torch.softmax(torch.randn(6, V, generator=g) * 3, -1)
+        p[1] = 1.0 / V  # every entry equal: the index cut decides everything
+        p[2, : V // 2] = p[2, 0]  # a long run of equal values
+        p[2] /= p[2].sum()
+        p[3, V // 3:] = 0.0  # exact zeros below the k-th value
+        for k in sorted({1, 2, V // 2, V - 1}):
+            if k <= 0 or k >= V:
+                continue
+            want1 = torch.stack([oracle.apply_top_k_compression(row, k) for row in p])
+            got1 = ops.topk_rebuild(p.to(dev), k, 1)
+            assert torch.equal(got1.cpu(), want1), (V, k)
+            _close(ops.topk_rebuild(p.to(dev), k, 0), oracle.rebuild_topk_probs(p, k), atol=3e-7)
+            want2 = oracle.compress_rebuild_probs(p[None], k)[0]
+            _close(ops.topk_rebuild(p.to(dev), k, 2), want2, atol=3e-7)
+        comp = torch.stack([oracle.apply_top_k_compression(row, max(1, V // 4)) for row in p])
+        _close(ops.topk_rebuild(comp.to(dev), 0, 3), oracle.rebuild_full_probs(comp), atol=3e-7)
+    # rows of a strided [B, S, V] view (row stride != V) and bf16 storage
+    p3 = torch.softmax(torch.randn(3, 5, 4096, generator=g) * 2, -1)
+    view = p3.to(dev)[:, 1:4]
+    got = ops.topk_rebuild(view, 64, 1)
+    want = torch.stack([oracle.apply_top_k_compression(row, 64) for row in p3[:, 1:4].reshape(-1, 4096)]).view(3, 3, 4096)
+    assert torch.equal(got.cpu(), want)
+    pb = torch.softmax(torch.randn(4, 32000, generator=g) * 3, -1).bfloat16()
+    gotb = ops.topk_rebuild(pb.to(dev), 1024, 1)
+    wantb = torch.stack([oracle.apply_top_k_compression(row, 1024) for row in pb.float()]).bfloat16()
+    assert torch.equal(gotb.cpu(), wantb)
+    _close(ops.topk_rebuild(pb.to(dev), 1024, 0), oracle.rebuild_topk_probs(pb.float(), 1024).bfloat16(), rtol=1e-2, atol=1e-8)
+
+
+def test_host_verifier_matches_device_call(ops, dev):
+    """duodecoding_b200.host.HostVerifier: the pinned-arena step (one H2D copy, one D2H copy) and the per-tensor
+    ``verify`` give exactly what ops.verify_fused gives on device tensors."""
+    from duodecoding_b200.host import HostVerifier
+
+    B, gamma, V = 8, 4, 32000
+    draft, target, tokens, r, noise = _make_case(77, B, gamma, V, 1.0, 1.0, 0, 0.9)
+    want = {k: v.cpu() for k, v in ops.verify_fused(*(t.to(dev) for t in (draft, target, tokens, r, noise)), 1.0, 0, 0.9).items()}
+    for nsplit in (1, 3):
+        hv = HostVerifier(B, gamma, V, torch.float32, dev, nsplit=nsplit)
+        hs = hv.host_set()
+        hs["draft"].copy_(draft[:, :gamma]), hs["target"].copy_(target), hs["tokens"].copy_(tokens)
+        hs["r"].copy_(r), hs["noise"].copy_(noise)
+        for _ in range(2):  # the second step reuses the arenas
+            got = hv.verify_set(hs, True, 1.0, 0, 0.9)
+            for k in ("accepted_len", "token", "accept_mask", "all_accepted"):
+                assert torch.equal(got[k], want[k]), (nsplit, k)
+            torch.testing.assert_close(got["selected_target_p"], want["selected_target_p"], rtol=NUCLEUS_RTOL, atol=1e-9)
+        assert hv.h2d_bytes == (B * (2 * gamma + 1) * V + B * V) * 4 + B * gamma * 12
+        got = hv.verify(draft.pin_memory(), target.pin_memory(), tokens, r, noise, 1.0, 0, 0.9)
+        for k in ("accepted_len", "token", "accept_mask", "all_accepted"):
+            assert torch.equal(got[k], want[k]), (nsplit, k)
+        no_noise = hv.verify_set(hs, False, 1.0, 0, 0.9)  # device-drawn Exp(1): the accept side does not depend on it
+        assert torch.equal(no_noise["accepted_len"], want["accepted_len"])
 
 
 def test_kv_truncate(ops, dev):
