@@ -46,6 +46,16 @@ SIGNATURES = {
         + [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]  # outputs
         + [c_void_p, c_size_t, c_void_p],  # workspace, stream
     ),
+    "duodec_verify_static_max_bytes": (c_size_t, []),
+    "duodec_verify_fused_static": (
+        c_int,
+        [c_void_p, c_void_p, c_int, c_i64, c_i64, c_i64, c_i64, c_int, c_int, c_int, c_int]  # rows / shapes
+        + [c_void_p, c_i64, c_void_p, c_i64, c_void_p, c_i64]  # tokens, r, noise
+        + [c_float, c_int, c_float, c_float, c_int, c_float]  # target warp, draft warp
+        + [c_int]  # flags
+        + [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]  # outputs
+        + [c_void_p],  # stream
+    ),
     "duodec_accept_probs": (
         c_int,
         [c_void_p, c_i64, c_i64, c_void_p, c_i64, c_i64, c_int, c_void_p, c_i64, c_void_p, c_i64]
@@ -116,7 +126,9 @@ def _load() -> ctypes.CDLL:
 lib = _load()
 
 _ERRORS = {-1: "DUODEC_EINVAL (bad shape, null pointer or dtype)", -2: "DUODEC_ETOOBIG (row too large)",
-           -3: "DUODEC_EWORKSPACE (workspace too small)"}
+           -3: "DUODEC_EWORKSPACE (workspace too small)",
+           -4: "DUODEC_ESTATICMAX (the call needs more scratch than the library's built-in 12 MiB array: use "
+               "duodec_verify_fused with a caller workspace)"}
 
 
 def check(code: int, what: str) -> None:

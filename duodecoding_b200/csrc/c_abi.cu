@@ -258,6 +258,66 @@ int duodec_verify_fused(const void* draft, const void* target, int dtype, int64_
   return int(e);
 }
 
+// ---- no-allocation variant of duodec_verify_fused (include/duodec.h): the workspace is this array.
+// In host code the array's name is a host-side stand-in, not a device address: the address is resolved
+// below, once per device, with that device current.
+}  // extern "C"
+
+static __device__ __align__(256) unsigned char g_static_workspace[DUODEC_VERIFY_STATIC_BYTES];
+
+namespace {
+struct StaticWorkspace {
+  void* ptr = nullptr;       // device address of g_static_workspace on this device
+  long long shape = -1;      // (B, gamma) of the last call: the layout inside the array depends on them
+};
+StaticWorkspace g_static_ws[64];
+std::mutex g_static_mu;
+}  // namespace
+
+extern "C" {
+
+size_t duodec_verify_static_max_bytes(void) { return size_t(DUODEC_VERIFY_STATIC_BYTES); }
+
+int duodec_verify_fused_static(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss,
+                               int64_t t_sb, int64_t t_ss, int B, int gamma, int Vd, int Vt, const int64_t* tokens,
+                               int64_t tok_sb, const float* r, int64_t r_sb, const float* noise, int64_t noise_sb,
+                               float temperature, int top_k, float top_p, float draft_temperature, int draft_top_k,
+                               float draft_top_p, int flags, uint8_t* accept_mask, float* sel_target_p,
+                               float* sel_draft_p, int64_t* accepted_len, int64_t* token, uint8_t* all_accepted,
+                               void* stream) {
+  if (B < 0 || gamma < 0) return DUODEC_EINVAL;
+  if (B == 0) return 0;
+  const size_t need = duodec_verify_workspace_bytes(B, gamma);
+  if (need > size_t(DUODEC_VERIFY_STATIC_BYTES)) return DUODEC_ESTATICMAX;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return int(e);
+  if (dev < 0 || dev >= 64) return DUODEC_EINVAL;
+  void* ws = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    StaticWorkspace& w = g_static_ws[dev];
+    if (!w.ptr) {
+      void* p = nullptr;
+      e = cudaGetSymbolAddress(&p, g_static_workspace);
+      if (e != cudaSuccess) return int(e);
+      w.ptr = p;
+    }
+    const long long shape = ((long long)B << 32) | (long long)gamma;
+    if (w.shape != shape) {
+      // the array holds another layout's contents (or nothing yet): what this call uses starts at zero
+      e = cudaMemsetAsync(w.ptr, 0, need, static_cast<cudaStream_t>(stream));
+      if (e != cudaSuccess) return int(e);
+      w.shape = shape;
+    }
+    ws = w.ptr;
+  }
+  return duodec_verify_fused(draft, target, dtype, d_sb, d_ss, t_sb, t_ss, B, gamma, Vd, Vt, tokens, tok_sb, r, r_sb,
+                             noise, noise_sb, temperature, top_k, top_p, draft_temperature, draft_top_k, draft_top_p,
+                             flags, accept_mask, sel_target_p, sel_draft_p, accepted_len, token, all_accepted, ws,
+                             size_t(DUODEC_VERIFY_STATIC_BYTES), stream);
+}
+
 int duodec_accept_probs(const void* draft_probs, int64_t d_sb, int64_t d_ss, const void* target_probs,
                         int64_t t_sb, int64_t t_ss, int dtype, const int64_t* tokens, int64_t tok_sb,
                         const float* r, int64_t r_sb, int B, int gamma, int V, uint8_t* accept_mask,

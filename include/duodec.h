@@ -39,6 +39,7 @@ extern "C" {
 #define DUODEC_EINVAL (-1)   /* bad shape / null pointer / unsupported dtype */
 #define DUODEC_ETOOBIG (-2)  /* row does not fit the largest team (V too large) */
 #define DUODEC_EWORKSPACE (-3)
+#define DUODEC_ESTATICMAX (-4) /* duodec_verify_fused_static: the call needs more scratch than the built-in array holds */
 
 /* Library / build identification: "duodec-b200 <version> sm_100a". */
 const char* duodec_version(void);
@@ -110,6 +111,32 @@ int duodec_verify_fused(const void* draft, const void* target, int dtype, int64_
                         int flags, uint8_t* accept_mask, float* sel_target_p, float* sel_draft_p,
                         int64_t* accepted_len, int64_t* token, uint8_t* all_accepted, void* workspace,
                         size_t workspace_bytes, void* stream);
+
+/* No counterpart in the reference: added for callers that
+ * cannot allocate device memory (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  duodec_verify_fused with the same arguments and results, minus the workspace: the
+ * scratch is a file-scope `static __device__ __align__(256)` array of DUODEC_VERIFY_STATIC_BYTES
+ * (12 MiB) inside the library, which every GPU that loads the library holds until exit.  The entry
+ * point allocates nothing (no cudaMalloc / cudaFree, no allocating library routine); it resolves the
+ * array's device address once per device (cudaGetSymbolAddress) and launches the same kernels.
+ *   - limit: duodec_verify_workspace_bytes(B, gamma) <= DUODEC_VERIFY_STATIC_BYTES (about 30 000 rows
+ *     B * (2 * gamma + 1); C2 needs 10.5 MB, C5 10.7 MB), else DUODEC_ESTATICMAX and nothing is launched;
+ *     duodec_verify_static_max_bytes() returns the limit.
+ *   - EVERY call on a device shares the one array and it keeps the last call's contents: the call
+ *     zero-fills the part it uses (cudaMemsetAsync on `stream`, ahead of the kernels) whenever
+ *     (B, gamma) differ from the previous call on that device; with equal shapes the kernels restore
+ *     what must be zero themselves and the exponent-offset hints of the previous call are reused.
+ *   - calls that overlap on the GPU (different streams, or graphs replayed concurrently) RACE on the
+ *     array: serialise them, or use duodec_verify_fused with one workspace per stream. */
+#define DUODEC_VERIFY_STATIC_BYTES (12u << 20)
+size_t duodec_verify_static_max_bytes(void);
+int duodec_verify_fused_static(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss,
+                               int64_t t_sb, int64_t t_ss, int B, int gamma, int Vd, int Vt, const int64_t* tokens,
+                               int64_t tok_sb, const float* r, int64_t r_sb, const float* noise, int64_t noise_sb,
+                               float temperature, int top_k, float top_p, float draft_temperature, int draft_top_k,
+                               float draft_top_p, int flags, uint8_t* accept_mask, float* sel_target_p,
+                               float* sel_draft_p, int64_t* accepted_len, int64_t* token, uint8_t* all_accepted,
+                               void* stream);
 
 /* ---- probability-space operators -----------------------------------------
  * Accept test on stored probability histories; replaces the tensor part of

@@ -31,6 +31,12 @@ def test_argument_errors_come_back_as_codes_without_a_gpu():
     assert lib.duodec_norm_logits(None, 0, 0, None, 0, 0, 0, 16, 1.0, 0, 0.0, None) == 0      # no rows: no-op
     assert lib.duodec_shard_finish(None, 0, 4, 1, None, None, None) == -1                           # world <= 0
     assert lib.duodec_verify_workspace_bytes(64, 4) > 0 and lib.duodec_team_size(32000, 2) >= 1
+    # the no-allocation variant refuses shapes whose scratch exceeds its built-in array before touching the device
+    assert lib.duodec_verify_static_max_bytes() == 12 << 20
+    assert lib.duodec_verify_workspace_bytes(64, 4) <= lib.duodec_verify_static_max_bytes()
+    big = [None, None, 0, 0, 0, 0, 0, 100000, 8, 32000, 32000, None, 0, None, 0, None, 0, 1.0, 0, 0.0, 1.0, 0, 0.0, 0]
+    assert lib.duodec_verify_workspace_bytes(100000, 8) > lib.duodec_verify_static_max_bytes()
+    assert lib.duodec_verify_fused_static(*big, None, None, None, None, None, None, None) == -4
 
 
 def test_kernels_are_registered_torch_library_ops():
