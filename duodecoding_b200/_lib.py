@@ -87,13 +87,28 @@ SIGNATURES = {
     "duodec_shard_accept": (
         c_int,
         [c_void_p, c_int, c_int, c_int, c_void_p, c_i64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
-         c_void_p, c_void_p],
+         c_void_p, c_void_p, c_i64, c_void_p, c_void_p],
     ),
     "duodec_shard_sample": (
         c_int,
         [c_void_p, c_void_p, c_int, c_i64, c_i64, c_i64, c_i64, c_int, c_int, c_int, c_int, c_float, c_float]
-        + [c_void_p, c_void_p, c_i64, c_int, c_void_p, c_void_p, c_void_p],
+        + [c_void_p, c_void_p, c_i64, c_int, c_void_p, c_void_p, c_int, c_void_p],
     ),
+    "duodec_shard_nucleus_levels": (c_int, [c_int, c_float, c_float]),
+    "duodec_shard_nucleus_level": (
+        c_int,
+        [c_void_p, c_void_p, c_int, c_i64, c_i64, c_i64, c_i64, c_int, c_int, c_int, c_int, c_float, c_float]
+        + [c_float, c_float, c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p],
+    ),
+    "duodec_shard_nucleus_reduce": (
+        c_int, [c_void_p, c_int, c_int, c_int, c_int, c_float, c_float, c_void_p, c_int, c_int, c_void_p, c_void_p]),
+    "duodec_shard_nucleus_tie": (
+        c_int,
+        [c_void_p, c_void_p, c_int, c_i64, c_i64, c_i64, c_i64, c_int, c_int, c_int, c_int, c_float, c_float]
+        + [c_void_p, c_void_p, c_int, c_void_p, c_void_p],
+    ),
+    "duodec_shard_nucleus_close": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "duodec_shard_finish": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
 }
 

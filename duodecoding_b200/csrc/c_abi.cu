@@ -13,6 +13,7 @@
 #include "row_kernels.cuh"
 #include "select_kernels.cuh"
 #include "shard_kernels.cuh"
+#include "shard_nucleus.cuh"
 #include "stream_launch.h"
 #include "verify_kernels.cuh"
 
@@ -504,24 +505,26 @@ int duodec_shard_stats(const void* draft, const void* target, int dtype, int64_t
 
 int duodec_shard_accept(const float* gathered_stats, int world, int B, int gamma, const float* r, int64_t r_sb,
                         uint8_t* accept_mask, float* sel_target_p, float* sel_draft_p, int64_t* accepted_len,
-                        uint8_t* all_accepted, void* plan, const duodec_shard_xchg* xchg, void* stream) {
+                        uint8_t* all_accepted, void* plan, const duodec_shard_xchg* xchg, const int64_t* tokens,
+                        int64_t tok_sb, const void* cuts, void* stream) {
   if (world <= 0 || B < 0 || gamma < 0 || gamma > 32) return DUODEC_EINVAL;
   if (B == 0) return 0;
   if (!xchg_ok(xchg) || (xchg && xchg->world != world)) return DUODEC_EINVAL;
+  if (cuts && ((gamma > 0 && !tokens) || xchg)) return DUODEC_EINVAL;  // the filter runs on gathered statistics
   if ((!gathered_stats && !xchg) || !accepted_len || !all_accepted || !plan ||
       (gamma > 0 && (!r || !accept_mask || !sel_target_p || !sel_draft_p)))
     return DUODEC_EINVAL;
   shard_accept_kernel<<<B, 32, 0, static_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<const float4*>(gathered_stats), world, B, gamma, r, r_sb, accept_mask, sel_target_p,
       sel_draft_p, reinterpret_cast<long long*>(accepted_len), all_accepted, static_cast<ShardPlan*>(plan),
-      xchg_of(xchg));
+      xchg_of(xchg), reinterpret_cast<const long long*>(tokens), tok_sb, static_cast<const ShardCut*>(cuts));
   return int(cudaGetLastError());
 }
 
 int duodec_shard_sample(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss, int64_t t_sb,
                         int64_t t_ss, int B, int gamma, int Vs, int v_begin, float temperature,
                         float draft_temperature, const void* plan, const float* noise, int64_t noise_sb,
-                        int nslice, void* partial, const duodec_shard_xchg* xchg, void* stream) {
+                        int nslice, void* partial, const duodec_shard_xchg* xchg, int filtered, void* stream) {
   if (!shard_rows_ok(draft, target, dtype, B, gamma, Vs)) return DUODEC_EINVAL;
   if (B == 0) return 0;
   if (!xchg_ok(xchg) || !plan || !noise || (!partial && !xchg) || nslice <= 0 || nslice > 65535 || B > 65535)
@@ -529,12 +532,88 @@ int duodec_shard_sample(const void* draft, const void* target, int dtype, int64_
   const ShardXchg X = xchg_of(xchg);
   const ShardRows S{draft, target, d_sb, d_ss, t_sb, t_ss, B, gamma, Vs, v_begin, temperature, draft_temperature};
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const dim3 grid{unsigned(nslice), unsigned(B), 1u};
+  const ShardPlan* pl = static_cast<const ShardPlan*>(plan);
+  ShardPartial* out = static_cast<ShardPartial*>(partial);
+  if (dtype == DUODEC_F32) {
+    if (filtered) shard_sample_kernel<float, true><<<grid, kThreads, 0, st>>>(S, pl, noise, noise_sb, out, X);
+    else shard_sample_kernel<float, false><<<grid, kThreads, 0, st>>>(S, pl, noise, noise_sb, out, X);
+  } else {
+    if (filtered) shard_sample_kernel<__nv_bfloat16, true><<<grid, kThreads, 0, st>>>(S, pl, noise, noise_sb, out, X);
+    else shard_sample_kernel<__nv_bfloat16, false><<<grid, kThreads, 0, st>>>(S, pl, noise, noise_sb, out, X);
+  }
+  return int(cudaGetLastError());
+}
+
+// ---- top-p under vocabulary sharding (shard_nucleus.cuh)
+int duodec_shard_nucleus_levels(int dtype, float temperature, float draft_temperature) {
+  return (dtype == DUODEC_BF16 && temperature == 1.0f && draft_temperature == 1.0f) ? 2 : 4;
+}
+
+int duodec_shard_nucleus_level(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss,
+                               int64_t t_sb, int64_t t_ss, int B, int gamma, int Vs, int v_begin, float temperature,
+                               float draft_temperature, float top_p, float draft_top_p, const float* gathered_stats,
+                               int world, void* sel, int level, void* hist, void* stream) {
+  if (!shard_rows_ok(draft, target, dtype, B, gamma, Vs) || temperature <= 0.0f || draft_temperature <= 0.0f)
+    return DUODEC_EINVAL;
+  if (B == 0) return 0;
+  if (!gathered_stats || world <= 0 || !sel || !hist || level < 0 || level > 3) return DUODEC_EINVAL;
+  const ShardRows S{draft, target, d_sb, d_ss, t_sb, t_ss, B, gamma, Vs, v_begin, temperature, draft_temperature};
+  const int rows = B * (2 * gamma + 1);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const float4* gs = reinterpret_cast<const float4*>(gathered_stats);
   if (dtype == DUODEC_F32)
-    shard_sample_kernel<float><<<dim3(unsigned(nslice), unsigned(B)), kThreads, 0, st>>>(
-        S, static_cast<const ShardPlan*>(plan), noise, noise_sb, static_cast<ShardPartial*>(partial), X);
+    shard_nuc_level_kernel<float><<<rows, kThreads, 0, st>>>(S, gs, world, top_p, draft_top_p,
+                                                             static_cast<ShardSel*>(sel), level,
+                                                             static_cast<unsigned char*>(hist));
   else
-    shard_sample_kernel<__nv_bfloat16><<<dim3(unsigned(nslice), unsigned(B)), kThreads, 0, st>>>(
-        S, static_cast<const ShardPlan*>(plan), noise, noise_sb, static_cast<ShardPartial*>(partial), X);
+    shard_nuc_level_kernel<__nv_bfloat16><<<rows, kThreads, 0, st>>>(S, gs, world, top_p, draft_top_p,
+                                                                     static_cast<ShardSel*>(sel), level,
+                                                                     static_cast<unsigned char*>(hist));
+  return int(cudaGetLastError());
+}
+
+int duodec_shard_nucleus_reduce(const void* gathered_hist, int world, int rank, int B, int gamma, float top_p,
+                                float draft_top_p, void* sel, int level, int levels, int32_t* quota, void* stream) {
+  if (world <= 0 || rank < 0 || rank >= world || B < 0 || gamma < 0) return DUODEC_EINVAL;
+  if (B == 0) return 0;
+  if (!gathered_hist || !sel || !quota || (levels != 2 && levels != 4) || level < 0 || level >= levels)
+    return DUODEC_EINVAL;
+  const int rows = B * (2 * gamma + 1);
+  shard_nuc_reduce_kernel<<<rows, kNucBins, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const unsigned char*>(gathered_hist), world, rows, gamma, top_p, draft_top_p,
+      static_cast<ShardSel*>(sel), level, levels, rank, quota);
+  return int(cudaGetLastError());
+}
+
+int duodec_shard_nucleus_tie(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss, int64_t t_sb,
+                             int64_t t_ss, int B, int gamma, int Vs, int v_begin, float temperature,
+                             float draft_temperature, const void* sel, const int32_t* quota, int levels,
+                             int32_t* cand, void* stream) {
+  if (!shard_rows_ok(draft, target, dtype, B, gamma, Vs) || temperature <= 0.0f || draft_temperature <= 0.0f)
+    return DUODEC_EINVAL;
+  if (B == 0) return 0;
+  if (!sel || !quota || !cand || (levels != 2 && levels != 4)) return DUODEC_EINVAL;
+  const ShardRows S{draft, target, d_sb, d_ss, t_sb, t_ss, B, gamma, Vs, v_begin, temperature, draft_temperature};
+  const int rows = B * (2 * gamma + 1);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dtype == DUODEC_F32)
+    shard_nuc_tie_kernel<float><<<rows, kThreads, 0, st>>>(S, static_cast<const ShardSel*>(sel), quota, levels, cand);
+  else
+    shard_nuc_tie_kernel<__nv_bfloat16><<<rows, kThreads, 0, st>>>(S, static_cast<const ShardSel*>(sel), quota, levels,
+                                                                   cand);
+  return int(cudaGetLastError());
+}
+
+int duodec_shard_nucleus_close(const void* sel, const float* gathered_stats, const int32_t* gathered_cand, int world,
+                               int B, int gamma, int levels, void* cuts, void* stream) {
+  if (world <= 0 || B < 0 || gamma < 0) return DUODEC_EINVAL;
+  if (B == 0) return 0;
+  if (!sel || !gathered_stats || !gathered_cand || !cuts || (levels != 2 && levels != 4)) return DUODEC_EINVAL;
+  const int rows = B * (2 * gamma + 1);
+  shard_nuc_close_kernel<<<(rows + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const ShardSel*>(sel), reinterpret_cast<const float4*>(gathered_stats), gathered_cand, world, rows,
+      levels, static_cast<ShardCut*>(cuts));
   return int(cudaGetLastError());
 }
 

@@ -224,10 +224,26 @@ __global__ void __launch_bounds__(kThreads) shard_stats_kernel(const __grid_cons
     xchg_publish(X, kXFlags1, kXCnt1, gridDim.x, X.off_stats, (long long)gridDim.x * 16, (long long)job * 16, 16);
 }
 
-struct ShardPlan {  // per sequence, written by shard_accept_kernel
-  float Mp, Zp, Mq, Zq;
-  int n, bonus, pad0, pad1;
+// A row's nucleus filter (shard_nucleus.cuh): entry (x, i) is kept iff x > xstar or (x == xstar and i <= istar)
+struct __align__(16) ShardCut {
+  float xstar;  // boundary value (scaled logit); -inf: everything is kept
+  int istar;    // entries equal to xstar are kept up to this GLOBAL index
+  float Zk;     // kept mass relative to the row maximum: p_i = exp(x_i - M) / Zk
+  int state;    // 0 filtered, 1 everything kept (no crossing), 2 no filter on this row kind
 };
+__device__ __forceinline__ bool cut_keeps(float x, long long gi, float xstar, int istar) {
+  return x > xstar || (x == xstar && gi <= (long long)istar);
+}
+
+struct __align__(16) ShardPlan {  // per sequence, written by shard_accept_kernel
+  float Mp, Zp, Mq, Zq;
+  int n, bonus;
+  float xsp;  // the filter of the row pair the token is drawn from (-inf / INT_MAX: none)
+  int isp;
+  float xsq;
+  int isq, pad0, pad1;
+};
+static_assert(sizeof(ShardPlan) == 48, "ShardPlan is exchanged with the host as 48 opaque bytes");
 
 // merged (M, Z, token logit) of one row from the G gathered partials
 __device__ __forceinline__ void shard_merge(const float4* gathered, int G, int rows, int job, float& M, float& Z,
@@ -245,7 +261,8 @@ __device__ __forceinline__ void shard_merge(const float4* gathered, int G, int r
 // one warp per sequence (gamma <= 32)
 __global__ void shard_accept_kernel(const float4* gathered, int G, int B, int gamma, const float* r, long long r_sb,
                                     unsigned char* accept_mask, float* sel_p, float* sel_q, long long* accepted_len,
-                                    unsigned char* all_accepted, ShardPlan* plan, const ShardXchg X) {
+                                    unsigned char* all_accepted, ShardPlan* plan, const ShardXchg X,
+                                    const long long* tokens, long long tok_sb, const ShardCut* cuts) {
   if (X.peers != nullptr) {
     xchg_wait(X, kXFlags1);
     gathered = reinterpret_cast<const float4*>(static_cast<const unsigned char*>(X.peers[X.rank]) + X.off_stats);
@@ -258,6 +275,13 @@ __global__ void shard_accept_kernel(const float4* gathered, int G, int B, int ga
     bool hq, hp;
     shard_merge(gathered, G, rows, base + 2 * lane, Mq, Zq, xq, hq);
     shard_merge(gathered, G, rows, base + 2 * lane + 1, Mp, Zp, xp, hp);
+    if (cuts != nullptr) {  // nucleus rows: the kept mass normalises, a filtered-out token has probability 0
+      const ShardCut cq = cuts[base + 2 * lane], cp = cuts[base + 2 * lane + 1];
+      const long long tk = tokens[(long long)b * tok_sb + lane];
+      Zq = cq.Zk, Zp = cp.Zk;
+      hq = hq && cut_keeps(xq, tk, cq.xstar, cq.istar);
+      hp = hp && cut_keeps(xp, tk, cp.xstar, cp.istar);
+    }
     const float q = hq ? __fdiv_rn(expf(xq - Mq), Zq) : 0.0f;
     const float p = hp ? __fdiv_rn(expf(xp - Mp), Zp) : 0.0f;
     accept = r[(long long)b * r_sb + lane] <= __fdiv_rn(p, q);  // raw IEEE division
@@ -273,9 +297,19 @@ __global__ void shard_accept_kernel(const float4* gathered, int G, int B, int ga
     float x;
     bool h;
     pl.n = n, pl.bonus = (n == gamma), pl.pad0 = pl.pad1 = 0;
-    shard_merge(gathered, G, rows, base + (pl.bonus ? 2 * gamma : 2 * n + 1), pl.Mp, pl.Zp, x, h);
+    const int prow = base + (pl.bonus ? 2 * gamma : 2 * n + 1), qrow = base + 2 * n;
+    shard_merge(gathered, G, rows, prow, pl.Mp, pl.Zp, x, h);
     pl.Mq = 0.0f, pl.Zq = 1.0f;
-    if (!pl.bonus) shard_merge(gathered, G, rows, base + 2 * n, pl.Mq, pl.Zq, x, h);
+    if (!pl.bonus) shard_merge(gathered, G, rows, qrow, pl.Mq, pl.Zq, x, h);
+    pl.xsp = pl.xsq = -INFINITY, pl.isp = pl.isq = 0x7fffffff;
+    if (cuts != nullptr) {
+      const ShardCut cp = cuts[prow];
+      pl.Zp = cp.Zk, pl.xsp = cp.xstar, pl.isp = cp.istar;
+      if (!pl.bonus) {
+        const ShardCut cq = cuts[qrow];
+        pl.Zq = cq.Zk, pl.xsq = cq.xstar, pl.isq = cq.istar;
+      }
+    }
     plan[b] = pl;
     accepted_len[b] = n;
     all_accepted[b] = (unsigned char)pl.bonus;
@@ -300,7 +334,7 @@ struct OpMaxKey2 {
 
 // grid (nslice, B): block (s, b) covers an eighth-aligned part of the local slice of the row pair
 // named by the plan and writes partial[b * nslice + s]
-template <class TIn>
+template <class TIn, bool kCut>
 __global__ void __launch_bounds__(kThreads) shard_sample_kernel(const __grid_constant__ ShardRows S,
                                                                 const ShardPlan* plan, const float* noise,
                                                                 long long noise_sb, ShardPartial* out,
@@ -321,8 +355,15 @@ __global__ void __launch_bounds__(kThreads) shard_sample_kernel(const __grid_con
   // branch-free per entry; a thread meets its indices in increasing order, so strict ">" keeps the lowest
   // index of a tie (same arithmetic as the fused path's sample kernel: __fdividef race keys)
   auto one = [&](float xp, float xq, float e, int i) {
-    float d = ex2f(fmaf(scale_logit(xp, S.t_temp), kShardLog2e, -mp)) * rZp;
-    if (!pl.bonus) d -= ex2f(fmaf(scale_logit(xq, S.d_temp), kShardLog2e, -mq)) * rZq;
+    const float xps = scale_logit(xp, S.t_temp);
+    float d = ex2f(fmaf(xps, kShardLog2e, -mp)) * rZp;
+    if (kCut) d = cut_keeps(xps, S.v_begin + i, pl.xsp, pl.isp) ? d : 0.0f;
+    if (!pl.bonus) {
+      const float xqs = scale_logit(xq, S.d_temp);
+      float dq = ex2f(fmaf(xqs, kShardLog2e, -mq)) * rZq;
+      if (kCut) dq = cut_keeps(xqs, S.v_begin + i, pl.xsq, pl.isq) ? dq : 0.0f;
+      d -= dq;
+    }
     const bool pos = d > 0.0f;
     mass += pos ? d : 0.0f;
     const float k = pos ? __fdividef(d, e) : -1.0f;

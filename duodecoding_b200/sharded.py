@@ -11,6 +11,12 @@ tensor-parallel LM head leaves behind - and the step needs two small exchanges (
     gather   all ranks' partials: 24 B per sequence and rank              all_gather_into_tensor
     finish   token of every sequence                                      kernel  duodec_shard_finish
 
+With ``top_p > 0`` a distributed radix select of every row's nucleus boundary runs between the first gather and
+``accept`` (csrc/shard_nucleus.cuh): per level (two for bf16 rows at temperature 1, four otherwise) a 256-bin
+(mass, count) histogram of the slice, an all-gather of the bins and a reduction to the next key prefix; then the
+index cut among equal values (one more 4-byte all-gather) - ``2 + levels + 1`` exchanges per step.  Masses are
+fixed-point integers, so the kept set of a row is the same for every world size.
+
 Every rank ends with the same accept masks, lengths and tokens.  The kernels are reached through a
 ``backend`` object; the product backend is the C ABI (CUDA only - there is no CPU path).  Tests
 inject a CPU restatement from ``oracle/`` to exercise the partition / exchange / merge logic under
@@ -41,7 +47,7 @@ class _CudaBackend:
     def __init__(self):
         from . import _lib, ops
         self.lib, self.ops, self.check = _lib.lib, ops, _lib.check
-        self.PLAN, self.PARTIAL = 32, 24
+        self.PLAN, self.PARTIAL, self.HIST, self.SEL, self.CUT = 48, 24, 3072, 32, 16
 
     def _rows(self, t):
         return (t.data_ptr(), t.stride(0), t.stride(1)) if t is not None and t.numel() else (None, 0, 0)
@@ -61,7 +67,7 @@ class _CudaBackend:
                                                    self.ops._stream()), "duodec_shard_stats")
         return stats
 
-    def accept(self, gathered, B, gamma, r, out=None, plan=None, xchg=None, world=None):
+    def accept(self, gathered, B, gamma, r, out=None, plan=None, xchg=None, world=None, tokens=None, cuts=None):
         dev = r.device if gathered is None else gathered.device
         if out is None:
             out = {
@@ -81,6 +87,9 @@ class _CudaBackend:
                                                     out["selected_target_p"].data_ptr(),
                                                     out["selected_draft_p"].data_ptr(), out["accepted_len"].data_ptr(),
                                                     out["all_accepted"].data_ptr(), plan.data_ptr(), xchg,
+                                                    tokens.data_ptr() if cuts is not None and gamma else None,
+                                                    tokens.stride(0) if cuts is not None and gamma else 0,
+                                                    cuts.data_ptr() if cuts is not None else None,
                                                     self.ops._stream()), "duodec_shard_accept")
         return out, plan
 
@@ -88,7 +97,8 @@ class _CudaBackend:
     def nslice(B, Vs):
         return max(1, min(-(-Vs // 4096), -(-592 // max(B, 1))))  # >= 4 blocks per SM in total
 
-    def sample_partial(self, draft, target, plan, noise, v_begin, t_temp, d_temp, gamma, partial=None, xchg=None):
+    def sample_partial(self, draft, target, plan, noise, v_begin, t_temp, d_temp, gamma, partial=None, xchg=None,
+                       filtered=False):
         B = target.shape[0]
         nslice = self.nslice(B, target.shape[-1])
         if partial is None and xchg is None:
@@ -100,8 +110,62 @@ class _CudaBackend:
                                                     target.shape[-1], int(v_begin), float(t_temp), float(d_temp),
                                                     plan.data_ptr(), noise.data_ptr(), noise.stride(0), nslice,
                                                     partial.data_ptr() if partial is not None else None, xchg,
-                                                    self.ops._stream()), "duodec_shard_sample")
+                                                    1 if filtered else 0, self.ops._stream()), "duodec_shard_sample")
         return partial
+
+    # ---- top-p under sharding (csrc/shard_nucleus.cuh)
+    def nucleus_levels(self, target, t_temp, d_temp):
+        return int(self.lib.duodec_shard_nucleus_levels(self.ops._code(target), float(t_temp), float(d_temp)))
+
+    def nucleus_level(self, draft, target, gamma, v_begin, t_temp, d_temp, top_p, d_top_p, gstats, sel, level, hist=None):
+        B = target.shape[0]
+        rows = B * (2 * gamma + 1)
+        dev = target.device
+        if sel is None:
+            sel = torch.zeros((rows, self.SEL), dtype=torch.uint8, device=dev)
+        if hist is None:
+            hist = torch.empty((rows, self.HIST), dtype=torch.uint8, device=dev)
+        dp, dsb, dss = self._rows(draft)
+        tp, tsb, tss = self._rows(target)
+        with torch.cuda.device(dev):
+            self.check(self.lib.duodec_shard_nucleus_level(dp, tp, self.ops._code(target), dsb, dss, tsb, tss, B, gamma,
+                                                           target.shape[-1], int(v_begin), float(t_temp), float(d_temp),
+                                                           float(top_p), float(d_top_p), gstats.data_ptr(),
+                                                           gstats.shape[0], sel.data_ptr(), int(level), hist.data_ptr(),
+                                                           self.ops._stream()), "duodec_shard_nucleus_level")
+        return sel, hist
+
+    def nucleus_reduce(self, ghist, rank, B, gamma, top_p, d_top_p, sel, level, levels, quota=None):
+        if quota is None:
+            quota = torch.zeros((B * (2 * gamma + 1),), dtype=torch.int32, device=sel.device)
+        with torch.cuda.device(sel.device):
+            self.check(self.lib.duodec_shard_nucleus_reduce(ghist.data_ptr(), ghist.shape[0], int(rank), B, gamma,
+                                                            float(top_p), float(d_top_p), sel.data_ptr(), int(level),
+                                                            int(levels), quota.data_ptr(), self.ops._stream()),
+                       "duodec_shard_nucleus_reduce")
+        return sel, quota
+
+    def nucleus_tie(self, draft, target, gamma, v_begin, t_temp, d_temp, sel, quota, levels, cand=None):
+        B = target.shape[0]
+        if cand is None:
+            cand = torch.empty((B * (2 * gamma + 1),), dtype=torch.int32, device=target.device)
+        dp, dsb, dss = self._rows(draft)
+        tp, tsb, tss = self._rows(target)
+        with torch.cuda.device(target.device):
+            self.check(self.lib.duodec_shard_nucleus_tie(dp, tp, self.ops._code(target), dsb, dss, tsb, tss, B, gamma,
+                                                         target.shape[-1], int(v_begin), float(t_temp), float(d_temp),
+                                                         sel.data_ptr(), quota.data_ptr(), int(levels), cand.data_ptr(),
+                                                         self.ops._stream()), "duodec_shard_nucleus_tie")
+        return cand
+
+    def nucleus_close(self, sel, gstats, gcand, B, gamma, levels, cuts=None):
+        if cuts is None:
+            cuts = torch.empty((B * (2 * gamma + 1), self.CUT), dtype=torch.uint8, device=sel.device)
+        with torch.cuda.device(sel.device):
+            self.check(self.lib.duodec_shard_nucleus_close(sel.data_ptr(), gstats.data_ptr(), gcand.data_ptr(),
+                                                           gstats.shape[0], B, gamma, int(levels), cuts.data_ptr(),
+                                                           self.ops._stream()), "duodec_shard_nucleus_close")
+        return cuts
 
     def finish(self, gathered, B, token=None, xchg=None, world=None, nslice=None):
         if token is None:
@@ -169,6 +233,33 @@ class ShardedVerifier:
     def exchanges_per_step(self) -> int:
         return 2 if self.world > 1 else 0
 
+    def _nucleus(self, draft, target, tokens, gstats, t_temp, d_temp, top_p, d_top_p, buf=None):
+        """The rows' nucleus filters (x*, i*, kept mass) from the gathered statistics: `levels` rounds of local
+        histogram -> all-gather -> reduction, then the index cut among equal values (one more all-gather)."""
+        B, gamma = tokens.shape
+        be = self.backend
+        nb = None
+        if buf is not None:
+            nb = buf.get("nucleus")
+            if nb is None:
+                rows, W, dev = B * (2 * gamma + 1), self.world, target.device
+                e = lambda shape, dt: torch.empty(shape, dtype=dt, device=dev)  # noqa: E731
+                nb = {"sel": torch.zeros((rows, be.SEL), dtype=torch.uint8, device=dev),
+                      "hist": e((rows, be.HIST), torch.uint8), "ghist": e((W, rows, be.HIST), torch.uint8),
+                      "quota": torch.zeros((rows,), dtype=torch.int32, device=dev), "cand": e((rows,), torch.int32),
+                      "gcand": e((W, rows), torch.int32), "cuts": e((rows, be.CUT), torch.uint8)}
+                buf["nucleus"] = nb
+        g = (lambda k: nb[k]) if nb is not None else (lambda k: None)
+        levels = be.nucleus_levels(target, t_temp, d_temp)
+        sel, quota = g("sel"), g("quota")
+        for level in range(levels):
+            sel, hist = be.nucleus_level(draft, target, gamma, self.v_begin, t_temp, d_temp, top_p, d_top_p, gstats, sel,
+                                         level, g("hist"))
+            sel, quota = be.nucleus_reduce(self._all_gather(hist, g("ghist")), self.rank, B, gamma, top_p, d_top_p,
+                                           sel, level, levels, quota)
+        cand = be.nucleus_tie(draft, target, gamma, self.v_begin, t_temp, d_temp, sel, quota, levels, g("cand"))
+        return be.nucleus_close(sel, gstats, self._all_gather(cand, g("gcand")), B, gamma, levels, g("cuts"))
+
     def _symmetric(self, B: int, gamma: int, Vs: int, dev: torch.device):
         """Peer-mapped exchange buffer of this shape (torch symmetric memory: CUDA VMM handles exchanged over the
         process group, every rank maps every peer's buffer) and the duodec_shard_xchg that describes it."""
@@ -203,7 +294,7 @@ class ShardedVerifier:
             e = lambda shape, dt: torch.empty(shape, dtype=dt, device=dev)  # noqa: E731
             buf = {
                 "stats": e((rows, 4), torch.float32), "gstats": e((W, rows, 4), torch.float32),
-                "plan": e((B, 32), torch.uint8), "partial": e((B, nslice, 24), torch.uint8),
+                "plan": e((B, getattr(self.backend, "PLAN", 48)), torch.uint8), "partial": e((B, nslice, 24), torch.uint8),
                 "gpartial": e((W, B, nslice, 24), torch.uint8), "token": e((B,), torch.int64),
                 "out": {"accept_mask": e((B, gamma), torch.bool), "selected_target_p": e((B, gamma), torch.float32),
                         "selected_draft_p": e((B, gamma), torch.float32), "accepted_len": e((B,), torch.int64),
@@ -212,14 +303,32 @@ class ShardedVerifier:
             self._bufs[key] = buf
         return buf
 
-    def _step(self, draft, target, tokens, r, noise, temperature, d_temp, buf=None):
+    def _step(self, draft, target, tokens, r, noise, temperature, d_temp, buf=None, top_p=0.0, d_top_p=0.0):
         B, gamma = tokens.shape
         be = self.backend
+        nucleus = top_p > 0.0 or d_top_p > 0.0
         if buf is None:  # injected test backends: plain allocating calls
             stats = be.row_stats(draft, target, tokens, self.v_begin, temperature, d_temp)
-            out, plan = be.accept(self._all_gather(stats), B, gamma, r)
-            partial = be.sample_partial(draft, target, plan, noise, self.v_begin, temperature, d_temp, gamma)
+            gstats = self._all_gather(stats)
+            if nucleus:
+                cuts = self._nucleus(draft, target, tokens, gstats, temperature, d_temp, top_p, d_top_p)
+                out, plan = be.accept(gstats, B, gamma, r, tokens=tokens, cuts=cuts)
+                partial = be.sample_partial(draft, target, plan, noise, self.v_begin, temperature, d_temp, gamma,
+                                            filtered=True)
+            else:
+                out, plan = be.accept(gstats, B, gamma, r)
+                partial = be.sample_partial(draft, target, plan, noise, self.v_begin, temperature, d_temp, gamma)
             out["token"] = be.finish(self._all_gather(partial), B)
+            return out
+        if nucleus:  # (always over gathered statistics: the fused exchange has no filter)
+            stats = be.row_stats(draft, target, tokens, self.v_begin, temperature, d_temp, stats=buf["stats"])
+            gstats = self._all_gather(stats, buf["gstats"])
+            cuts = self._nucleus(draft, target, tokens, gstats, temperature, d_temp, top_p, d_top_p, buf)
+            out, plan = be.accept(gstats, B, gamma, r, out=buf["out"], plan=buf["plan"], tokens=tokens, cuts=cuts)
+            partial = be.sample_partial(draft, target, plan, noise, self.v_begin, temperature, d_temp, gamma,
+                                        partial=buf["partial"], filtered=True)
+            out = dict(out)
+            out["token"] = be.finish(self._all_gather(partial, buf["gpartial"]), B, token=buf["token"])
             return out
         if self.fused and self.world > 1:
             import ctypes
@@ -273,7 +382,8 @@ class ShardedVerifier:
 
     def verify(self, draft: torch.Tensor, target: torch.Tensor, tokens: torch.Tensor, r: torch.Tensor,
                noise: torch.Tensor, temperature: float = 1.0, draft_temperature: Optional[float] = None,
-               graph: Optional[bool] = None) -> Dict[str, torch.Tensor]:
+               graph: Optional[bool] = None, top_p: float = 0.0,
+               draft_top_p: Optional[float] = None) -> Dict[str, torch.Tensor]:
         """draft [B, >=gamma, Vs], target [B, >=gamma+1, Vs], noise [B, Vs]: this rank's slices;
         tokens [B, gamma] (global ids), r [B, gamma]: replicated.  Returns the dict of verify_fused (tensors
         owned by the verifier: valid until the next call with the same shapes).
@@ -282,29 +392,31 @@ class ShardedVerifier:
         per set of input buffers (the second call with the same tensors replays it; `graph=False` disables)."""
         B, gamma = tokens.shape
         d_temp = temperature if draft_temperature is None else draft_temperature
+        top_p = float(top_p or 0.0)
+        d_top_p = top_p if draft_top_p is None else float(draft_top_p or 0.0)
         if target.shape[-1] != self.v_end - self.v_begin:
             raise ValueError("target slice width does not match this rank's vocabulary slice")
         if not isinstance(self.backend, _CudaBackend):
-            return self._step(draft, target, tokens, r, noise, temperature, d_temp)
+            return self._step(draft, target, tokens, r, noise, temperature, d_temp, None, top_p, d_top_p)
         buf = self._buffers(B, gamma, target.shape[-1], target.device)
         if graph is None:
             graph = self.use_graphs
         if not graph or gamma == 0:
-            return self._step(draft, target, tokens, r, noise, temperature, d_temp, buf)
+            return self._step(draft, target, tokens, r, noise, temperature, d_temp, buf, top_p, d_top_p)
         key = (draft.data_ptr(), target.data_ptr(), tokens.data_ptr(), r.data_ptr(), noise.data_ptr(),
                tuple(draft.stride()), tuple(target.stride()), B, gamma, target.shape[-1], float(temperature),
-               float(d_temp))
+               float(d_temp), top_p, d_top_p)
         ent = self._graphs.get(key)
         if ent is None:
             # first call with these buffers: one eager step (also the warm-up NCCL wants), then the capture
-            out = self._step(draft, target, tokens, r, noise, temperature, d_temp, buf)
+            out = self._step(draft, target, tokens, r, noise, temperature, d_temp, buf, top_p, d_top_p)
             torch.cuda.current_stream().synchronize()
             g = torch.cuda.CUDAGraph()
             side = torch.cuda.Stream(device=target.device)
             side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(side):
                 with torch.cuda.graph(g, stream=side):
-                    out = self._step(draft, target, tokens, r, noise, temperature, d_temp, buf)
+                    out = self._step(draft, target, tokens, r, noise, temperature, d_temp, buf, top_p, d_top_p)
             torch.cuda.current_stream().wait_stream(side)
             if len(self._graphs) >= 16:
                 self._graphs.pop(next(iter(self._graphs)))

@@ -182,12 +182,12 @@ int duodec_kv_truncate(int32_t* seq_len, const int64_t* end_pos_vec, int64_t end
  * Every rank holds the slice [v_begin, v_begin + Vs) of all draft / target rows (strides of the
  * LOCAL slices).  The step is stats -> all-gather -> accept -> sample -> all-gather -> finish; the
  * two all-gathers are the caller's (NCCL over NVLink in duodecoding_b200/sharded.py).  Replaces
- * the same reference code as duodec_verify_fused, without top-k / top-p.
+ * the same reference code as duodec_verify_fused, without top-k; top-p through the duodec_shard_nucleus_* calls below.
  *   stats    [B*(2*gamma+1), 4] float32 per rank: slice max, sum exp(x - max), token logit, flag
- *   plan     [B] 32-byte records (device scratch between accept and sample)
+ *   plan     [B] 48-byte records (device scratch between accept and sample)
  *   partial  [B, nslice] 24-byte records per rank (the slice is cut in nslice parts for occupancy):
  *            residual mass, best race key, zero-mass fallback key; gathered as [world, B, nslice] */
-#define DUODEC_SHARD_PLAN_BYTES 32
+#define DUODEC_SHARD_PLAN_BYTES 48
 #define DUODEC_SHARD_PARTIAL_BYTES 24
 /* Optional fused exchange (NULL: the caller gathers, e.g. with NCCL).  `peers` is a DEVICE array of `world`
  * base pointers of peer-mapped (symmetric) buffers, own buffer at [rank]; every buffer starts with a 1 KB
@@ -209,13 +209,45 @@ int duodec_shard_stats(const void* draft, const void* target, int dtype, int64_t
                        void* stream);
 int duodec_shard_accept(const float* gathered_stats, int world, int B, int gamma, const float* r, int64_t r_sb,
                         uint8_t* accept_mask, float* sel_target_p, float* sel_draft_p, int64_t* accepted_len,
-                        uint8_t* all_accepted, void* plan, const duodec_shard_xchg* xchg, void* stream);
+                        uint8_t* all_accepted, void* plan, const duodec_shard_xchg* xchg, const int64_t* tokens,
+                        int64_t tok_sb, const void* cuts, void* stream);
 int duodec_shard_sample(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss, int64_t t_sb,
                         int64_t t_ss, int B, int gamma, int Vs, int v_begin, float temperature,
                         float draft_temperature, const void* plan, const float* noise, int64_t noise_sb,
-                        int nslice, void* partial, const duodec_shard_xchg* xchg, void* stream);
+                        int nslice, void* partial, const duodec_shard_xchg* xchg, int filtered, void* stream);
 int duodec_shard_finish(const void* gathered_partials, int world, int B, int nslice, int64_t* token,
                         const duodec_shard_xchg* xchg, void* stream);
+
+/* Top-p under vocabulary sharding (reference: top_k_top_p_filter, src/utils.py:650-683, as applied by
+ * norm_logits, :686-709): a distributed radix select of the nucleus boundary over the order-preserving key of the
+ * scaled logit, 8 bits per level, between exchange 1 and duodec_shard_accept.  Masses are 40-bit fixed point
+ * relative to the row maximum and summed as integers: the answer does not depend on the world size.
+ *   levels  = duodec_shard_nucleus_levels(dtype, T, draft T): 2 (bf16 rows at temperature 1) or 4
+ *   for level in 0 .. levels-1:
+ *     duodec_shard_nucleus_level   -> hist [rows, DUODEC_SHARD_HIST_BYTES] of this rank
+ *     (all-gather hist -> [world, rows, DUODEC_SHARD_HIST_BYTES])
+ *     duodec_shard_nucleus_reduce  -> sel [rows, DUODEC_SHARD_SEL_BYTES] updated; at the last level quota [rows]
+ *   duodec_shard_nucleus_tie       -> cand [rows] int32: global index of this rank's last kept tie
+ *   (all-gather cand -> [world, rows])
+ *   duodec_shard_nucleus_close     -> cuts [rows, DUODEC_SHARD_CUT_BYTES]: (x*, i*, kept mass, state)
+ * then duodec_shard_accept(..., tokens, tok_sb, cuts, ...) and duodec_shard_sample(..., filtered = 1, ...).
+ * top_p / draft_top_p <= 0 leave that model's rows unfiltered.  Not available with the fused exchange. */
+#define DUODEC_SHARD_HIST_BYTES 3072
+#define DUODEC_SHARD_SEL_BYTES 32
+#define DUODEC_SHARD_CUT_BYTES 16
+int duodec_shard_nucleus_levels(int dtype, float temperature, float draft_temperature);
+int duodec_shard_nucleus_level(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss,
+                               int64_t t_sb, int64_t t_ss, int B, int gamma, int Vs, int v_begin, float temperature,
+                               float draft_temperature, float top_p, float draft_top_p, const float* gathered_stats,
+                               int world, void* sel, int level, void* hist, void* stream);
+int duodec_shard_nucleus_reduce(const void* gathered_hist, int world, int rank, int B, int gamma, float top_p,
+                                float draft_top_p, void* sel, int level, int levels, int32_t* quota, void* stream);
+int duodec_shard_nucleus_tie(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss, int64_t t_sb,
+                             int64_t t_ss, int B, int gamma, int Vs, int v_begin, float temperature,
+                             float draft_temperature, const void* sel, const int32_t* quota, int levels,
+                             int32_t* cand, void* stream);
+int duodec_shard_nucleus_close(const void* sel, const float* gathered_stats, const int32_t* gathered_cand, int world,
+                               int B, int gamma, int levels, void* cuts, void* stream);
 
 /* ---- transfer_top_k under vocabulary sharding (merge of per-shard top-k candidates) ------------------
  * Replaces utils.rebuild_topk_probs (src/utils.py:751-777) / communication._apply_top_k_compression

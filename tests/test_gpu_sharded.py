@@ -44,6 +44,68 @@ def test_shard_kernels_match_unsharded_oracle(world, dtype):
         torch.testing.assert_close(got["selected_draft_p"].cpu(), want["selected_draft_p"], rtol=1e-5, atol=1e-9)
 
 
+def _run_top_p(world, dl, tl, toks, r, noise, T, top_p, d_top_p, dev):
+    """The nucleus flow of ShardedVerifier._step with the all-gathers emulated by stacking: every emulated rank
+    keeps its own selection state, as the real ranks do."""
+    from duodecoding_b200.sharded import _CudaBackend, shard_bounds
+    be = _CudaBackend()
+    B, gamma = toks.shape
+    V = tl.shape[-1]
+    toks_d, r_d = toks.to(dev), r.to(dev)
+    sl = [shard_bounds(V, g, world) for g in range(world)]
+    parts = [(dl[..., a:b].to(dev), tl[..., a:b].to(dev), noise[..., a:b].contiguous().to(dev), a) for a, b in sl]
+    gstats = torch.stack([be.row_stats(d, t, toks_d, a, T, T) for d, t, _, a in parts])
+    levels = be.nucleus_levels(parts[0][1], T, T)
+    sels, quotas = [None] * world, [None] * world
+    for level in range(levels):
+        hists = []
+        for g, (d, t, _, a) in enumerate(parts):
+            sels[g], h = be.nucleus_level(d, t, gamma, a, T, T, top_p, d_top_p, gstats, sels[g], level)
+            hists.append(h)
+        ghist = torch.stack(hists)
+        for g in range(world):
+            sels[g], quotas[g] = be.nucleus_reduce(ghist, g, B, gamma, top_p, d_top_p, sels[g], level, levels, quotas[g])
+    for g in range(1, world):
+        assert torch.equal(sels[g], sels[0])  # every rank reaches the same selection state
+    gcand = torch.stack([be.nucleus_tie(d, t, gamma, a, T, T, sels[g], quotas[g], levels)
+                         for g, (d, t, _, a) in enumerate(parts)])
+    cuts = be.nucleus_close(sels[0], gstats, gcand, B, gamma, levels)
+    out, plan = be.accept(gstats, B, gamma, r_d, tokens=toks_d, cuts=cuts)
+    partials = torch.stack([be.sample_partial(d, t, plan, nz, a, T, T, gamma, filtered=True) for d, t, nz, a in parts])
+    out["token"] = be.finish(partials, B)
+    torch.cuda.synchronize()
+    return out, cuts, levels
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_shard_top_p_matches_unsharded_oracle_for_every_world_size(dtype):
+    """Top-p under vocabulary sharding (shard_nucleus.cuh) against the unsharded oracle (src/utils.py:650-709,
+    src/decoding_ops.py:109-220): lengths, tokens and masks exact, selected probabilities up to one boundary entry
+    (cf. NUCLEUS_RTOL in test_gpu_parity.py); the filter itself is bit-identical for 1, 2, 3 and 8 ranks."""
+    dev = torch.device("cuda:0")
+    for seed, sigma, T, top_p, d_top_p in [(1, 0.5, 1.0, 0.9, 0.9), (2, 1.5, 1.0, 0.5, 0.95), (3, 1.0, 0.7, 0.9, 0.9),
+                                            (4, 1.0, 1.0, 0.9, 0.0), (5, 1.0, 1.0, 1.0, 0.3)]:
+        dl, tl, toks, r, noise = _case(seed, 6, 4, 6000, sigma)
+        if dtype == torch.bfloat16:  # coarse values: thousands of exact ties, the index cut decides
+            dl, tl = (dl * 0.5).to(dtype), (tl * 0.5).to(dtype)
+        want = oracle.fused_verify(dl.float(), tl.float(), toks, r, noise, T, 0, top_p, T, 0, d_top_p)
+        ref_cuts = None
+        for world in (1, 2, 3, 8):
+            got, cuts, levels = _run_top_p(world, dl, tl, toks, r, noise, T, top_p, d_top_p, dev)
+            assert levels == (2 if dtype == torch.bfloat16 and T == 1.0 else 4)
+            what = (seed, world)
+            assert torch.equal(got["accepted_len"].cpu(), want["accepted_len"]), what
+            assert torch.equal(got["token"].cpu(), want["token"]), what
+            assert torch.equal(got["accept_mask"].cpu(), want["accept_mask"]), what
+            torch.testing.assert_close(got["selected_target_p"].cpu(), want["selected_target_p"], rtol=5e-4, atol=1e-9)
+            torch.testing.assert_close(got["selected_draft_p"].cpu(), want["selected_draft_p"], rtol=5e-4, atol=1e-9)
+            c = cuts.view(torch.int32).clone()  # [rows, 4]: x* bits, i*, kept-mass bits, state
+            c[c[:, 3] == 2, 2] = 0  # (rows without a filter carry the float sum of the partial sums)
+            if ref_cuts is None:
+                ref_cuts = c
+            assert torch.equal(c, ref_cuts), what  # integer masses: one answer for every partition
+
+
 def test_sharded_verifier_world1_and_edge_cases():
     from duodecoding_b200.sharded import ShardedVerifier
     dev = torch.device("cuda:0")
@@ -52,6 +114,12 @@ def test_sharded_verifier_world1_and_edge_cases():
     got = sv.verify(dl.to(dev), tl.to(dev), toks.to(dev), r.to(dev), noise.to(dev), 1.0)
     want = oracle.fused_verify(dl, tl, toks, r, noise, 1.0, 0, 0.0)
     assert torch.equal(got["token"].cpu(), want["token"]) and torch.equal(got["accepted_len"].cpu(), want["accepted_len"])
+    for _ in range(2):  # top-p through the verifier (second call: the captured graph)
+        got = sv.verify(dl.to(dev), tl.to(dev), toks.to(dev), r.to(dev), noise.to(dev), 1.0, top_p=0.9)
+        want_p = oracle.fused_verify(dl, tl, toks, r, noise, 1.0, 0, 0.9)
+        assert torch.equal(got["token"].cpu(), want_p["token"])
+        assert torch.equal(got["accepted_len"].cpu(), want_p["accepted_len"])
+        torch.testing.assert_close(got["selected_target_p"].cpu(), want_p["selected_target_p"], rtol=5e-4, atol=1e-9)
     # identical models: every draft accepted, bonus token from the last target row
     got = sv.verify(tl[:, :2].to(dev), tl.to(dev), toks.to(dev), torch.full((3, 2), 0.999, device=dev), noise.to(dev))
     assert got["accepted_len"].tolist() == [2, 2, 2] and got["all_accepted"].all()
