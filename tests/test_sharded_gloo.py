@@ -39,6 +39,18 @@ def _worker(rank, world, port, ret):
             ok &= torch.equal(got["accepted_len"], want["accepted_len"]) and torch.equal(got["token"], want["token"])
             ok &= torch.equal(got["accept_mask"], want["accept_mask"]) and sv.collectives == 2
             ok &= torch.allclose(got["selected_target_p"], want["selected_target_p"], rtol=1e-5, atol=1e-9)
+        # top-p under sharding: stats + 4 levels + index cut + partials = 7 exchanges, same answer as the unsharded oracle
+        for seed, sigma, T, top_p, d_top_p in [(3, 0.5, 1.0, 0.9, 0.9), (4, 1.5, 0.7, 0.5, 0.0)]:
+            B, gamma, V = 5, 4, 1003
+            dl, tl, toks, r, noise = _case(seed, B, gamma, V, sigma)
+            sv = ShardedVerifier(V, backend=OracleShardBackend())
+            got = sv.verify(sv.slice_of(dl), sv.slice_of(tl), toks, r, sv.slice_of(noise), T, top_p=top_p,
+                            draft_top_p=d_top_p)
+            want = oracle.fused_verify(dl, tl, toks, r, noise, T, 0, top_p, T, 0, d_top_p)
+            ok &= torch.equal(got["accepted_len"], want["accepted_len"]) and torch.equal(got["token"], want["token"])
+            ok &= torch.equal(got["accept_mask"], want["accept_mask"]) and sv.collectives == 7
+            ok &= torch.allclose(got["selected_target_p"], want["selected_target_p"], rtol=5e-4, atol=1e-9)
+            ok &= torch.allclose(got["selected_draft_p"], want["selected_draft_p"], rtol=5e-4, atol=1e-9)
         ret[rank] = bool(ok)
     finally:
         dist.destroy_process_group()
