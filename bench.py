@@ -558,11 +558,13 @@ def run_ours(args):
 
 
 # ----------------------------------------------------------------------------- C5: vocabulary-sharded verify
-def c5_measure(dev, world, rank, dist, K, W):
+def c5_measure(dev, world, rank, dist, K, W, top_p=0.0):
     """BASELINE.json config 5: B=256, gamma=6, V=151936, bf16, no filter, vocabulary sharded over the ranks
     (strong scaling: total work fixed, every rank holds V/N columns of every row).  Every rank builds the same
     full tensors from a shared seed and keeps its columns; rank 0 also verifies the full tensors on one GPU and
-    requires the sharded result to be identical (`checked`).  Returns the sub-record (None off rank 0)."""
+    requires the sharded result to be identical (`checked`).  Returns the sub-record (None off rank 0).
+    `top_p` > 0 (bench.py --workload c5 --top-p 0.9): the same step with the nucleus filter on both models - the
+    distributed radix select of duodecoding_b200/csrc/shard_nucleus.cuh (four 4-bit levels for bf16 rows at T = 1)."""
     import duodecoding_b200.ops as ops
     from duodecoding_b200.sharded import ShardedVerifier
 
@@ -573,20 +575,20 @@ def c5_measure(dev, world, rank, dist, K, W):
     for si in range(2):
         tl = (torch.randn(Bc, Gc + 1, Vc, device=dev, generator=g) * 3).to(torch.bfloat16)
         dl = (tl[:, :Gc].float() + torch.randn(Bc, Gc, Vc, device=dev, generator=g)).to(torch.bfloat16)
-        q = ops.norm_logits(dl, 1.0, 0, 0.0)
+        q = ops.norm_logits(dl, 1.0, 0, top_p)
         e = torch.empty(Bc * Gc, Vc, device=dev).exponential_(1.0, generator=g)
         toks = ops.sample_rows(q.reshape(Bc * Gc, Vc), e).reshape(Bc, Gc)  # drafted from q: both branches occur
         del q, e
         r = torch.rand(Bc, Gc, device=dev, generator=g)
         noise = torch.empty(Bc, Vc, device=dev).exponential_(1.0, generator=g)
         if si == 0 and rank == 0:
-            full0 = ops.verify_fused(dl, tl, toks, r, noise, 1.0, 0, 0.0)
+            full0 = ops.verify_fused(dl, tl, toks, r, noise, 1.0, 0, top_p)
             full0 = {k: v.clone() for k, v in full0.items()}
         sets.append((sv.slice_of(dl).contiguous(), sv.slice_of(tl).contiguous(), toks, r,
                      sv.slice_of(noise).contiguous()))
         del tl, dl, noise
     torch.cuda.empty_cache()
-    out = sv.verify(*sets[0], 1.0)
+    out = sv.verify(*sets[0], 1.0, top_p=top_p)
     torch.cuda.synchronize()
     checked = False
     if rank == 0:
@@ -594,7 +596,7 @@ def c5_measure(dev, world, rank, dist, K, W):
         if not checked:
             raise SystemExit("bench.py: the sharded C5 step differs from the single-GPU result - refusing to time it")
     for i in range(W):
-        out = sv.verify(*sets[i % 2], 1.0)
+        out = sv.verify(*sets[i % 2], 1.0, top_p=top_p)
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -602,7 +604,7 @@ def c5_measure(dev, world, rank, dist, K, W):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for i in range(K):
-        out = sv.verify(*sets[i % 2], 1.0)
+        out = sv.verify(*sets[i % 2], 1.0, top_p=top_p)
     e1.record()
     torch.cuda.synchronize()
     if world > 1:
@@ -613,17 +615,20 @@ def c5_measure(dev, world, rank, dist, K, W):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dt = float(t.item())
     mean_acc = float(out["accepted_len"].float().mean().item())
-    timings = sv.phase_times(sets[0], 1.0) if hasattr(sv, "phase_times") else None
+    timings = sv.phase_times(sets[0], 1.0) if hasattr(sv, "phase_times") and not top_p else None
+    nuc_x = 5 if top_p else 0  # bf16 rows at T = 1: four levels + the index cut
     if rank != 0:
         return None
     alg = 2 * Bc * (Gc + 1) * Vc * 2
     peak, peak_src = hbm_peak()
     ach = alg / world / (dt / K) / 1e9
     return {
-        "workload": "C5 vocabulary-sharded verify: B=256, gamma+1=7, V=151936, bf16 logits, T=1.0, no filter",
+        "workload": "C5 vocabulary-sharded verify: B=256, gamma+1=7, V=151936, bf16 logits, T=1.0, "
+                    + (f"top_p={top_p} on both models (distributed radix select)" if top_p else "no filter"),
+        "top_p": top_p, "launches_per_step": 4 + (10 if top_p else 0),
         "nranks": world, "scaling": "strong", "ms_per_step": dt / K * 1e3, "value": Bc * (Gc + 1) * K / dt,
         "unit": UNIT, "steps": K, "checked": checked, "mean_accepted_len": mean_acc,
-        "exchanges_per_step": sv.exchanges_per_step if hasattr(sv, "exchanges_per_step") else (2 if world > 1 else 0),
+        "exchanges_per_step": (sv.exchanges_per_step + nuc_x) if world > 1 else 0,
         "exchange": getattr(sv, "exchange_kind", "nccl all_gather_into_tensor"),
         "phase_us": timings,
         "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
@@ -641,7 +646,7 @@ def run_c5(args):
     dev = torch.device("cuda", local)
     dist = init_dist(dev, world)
     clocks = ClockSampler(local) if rank == 0 else None
-    rec = c5_measure(dev, world, rank, dist, args.steps, max(args.warmup, 3))
+    rec = c5_measure(dev, world, rank, dist, args.steps, max(args.warmup, 3), float(args.top_p or 0.0))
     clk = clocks.stop() if clocks is not None else None
     if rank == 0:
         line = {
@@ -653,7 +658,7 @@ def run_c5(args):
                        "mean_accepted_len": rec["mean_accepted_len"], "checked": rec["checked"],
                        "phase_us": rec["phase_us"], "l2": "per-rank inputs larger than L2 or rotated",
                        "timing": "CUDA events around K steps"},
-            "clocks": clk, "gpu_launches": 4 * args.steps,
+            "clocks": clk, "gpu_launches": rec["launches_per_step"] * args.steps,
             "e2e": {"value": rec["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
                     "note": "the logit slices are produced on the device by the sharded LM head: no host leg"},
             "roofline": rec["roofline"], "cpu_baseline": None,
@@ -824,6 +829,7 @@ def main():
                     help="c2: BASELINE config 2 (default, batch per rank); c3: B=32 bf16 (--temperature 0|1); "
                          "c4: two-stage tridecoding verification; c5: vocabulary-sharded config 5")
     ap.add_argument("--temperature", type=float, default=None, help="c3 only: 0 (greedy) or 1")
+    ap.add_argument("--top-p", type=float, default=0.0, help="c5 only: nucleus filter on both models (sharded top-p)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-check", action="store_true", help="skip the oracle check of one step before timing")
     ap.add_argument("--no-c5", action="store_true", help="N > 1: skip the vocabulary-sharded c5 sub-record")

@@ -547,7 +547,7 @@ int duodec_shard_sample(const void* draft, const void* target, int dtype, int64_
 
 // ---- top-p under vocabulary sharding (shard_nucleus.cuh)
 int duodec_shard_nucleus_levels(int dtype, float temperature, float draft_temperature) {
-  return (dtype == DUODEC_BF16 && temperature == 1.0f && draft_temperature == 1.0f) ? 2 : 4;
+  return (dtype == DUODEC_BF16 && temperature == 1.0f && draft_temperature == 1.0f) ? 4 : 8;
 }
 
 int duodec_shard_nucleus_level(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss,
@@ -557,19 +557,24 @@ int duodec_shard_nucleus_level(const void* draft, const void* target, int dtype,
   if (!shard_rows_ok(draft, target, dtype, B, gamma, Vs) || temperature <= 0.0f || draft_temperature <= 0.0f)
     return DUODEC_EINVAL;
   if (B == 0) return 0;
-  if (!gathered_stats || world <= 0 || !sel || !hist || level < 0 || level > 3) return DUODEC_EINVAL;
+  if (!gathered_stats || world <= 0 || !sel || !hist || level < 0 || level > 7) return DUODEC_EINVAL;
+  if (Vs > kNucMaxPerThread * kThreads) return DUODEC_ETOOBIG;  // packed per-thread (mass, count) columns
   const ShardRows S{draft, target, d_sb, d_ss, t_sb, t_ss, B, gamma, Vs, v_begin, temperature, draft_temperature};
   const int rows = B * (2 * gamma + 1);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const float4* gs = reinterpret_cast<const float4*>(gathered_stats);
-  if (dtype == DUODEC_F32)
-    shard_nuc_level_kernel<float><<<rows, kThreads, 0, st>>>(S, gs, world, top_p, draft_top_p,
-                                                             static_cast<ShardSel*>(sel), level,
-                                                             static_cast<unsigned char*>(hist));
-  else
-    shard_nuc_level_kernel<__nv_bfloat16><<<rows, kThreads, 0, st>>>(S, gs, world, top_p, draft_top_p,
-                                                                     static_cast<ShardSel*>(sel), level,
-                                                                     static_cast<unsigned char*>(hist));
+  if (dtype == DUODEC_F32) {
+    cudaError_t e = ensure_smem(reinterpret_cast<const void*>(shard_nuc_level_kernel<float>), kNucLevelSmem);
+    if (e != cudaSuccess) return int(e);
+    shard_nuc_level_kernel<float><<<rows, kThreads, kNucLevelSmem, st>>>(S, gs, world, top_p, draft_top_p,
+                                                                         static_cast<ShardSel*>(sel), level,
+                                                                         static_cast<unsigned char*>(hist));
+  } else {
+    cudaError_t e = ensure_smem(reinterpret_cast<const void*>(shard_nuc_level_kernel<__nv_bfloat16>), kNucLevelSmem);
+    if (e != cudaSuccess) return int(e);
+    shard_nuc_level_kernel<__nv_bfloat16><<<rows, kThreads, kNucLevelSmem, st>>>(
+        S, gs, world, top_p, draft_top_p, static_cast<ShardSel*>(sel), level, static_cast<unsigned char*>(hist));
+  }
   return int(cudaGetLastError());
 }
 
@@ -577,10 +582,10 @@ int duodec_shard_nucleus_reduce(const void* gathered_hist, int world, int rank, 
                                 float draft_top_p, void* sel, int level, int levels, int32_t* quota, void* stream) {
   if (world <= 0 || rank < 0 || rank >= world || B < 0 || gamma < 0) return DUODEC_EINVAL;
   if (B == 0) return 0;
-  if (!gathered_hist || !sel || !quota || (levels != 2 && levels != 4) || level < 0 || level >= levels)
+  if (!gathered_hist || !sel || !quota || (levels != 4 && levels != 8) || level < 0 || level >= levels)
     return DUODEC_EINVAL;
   const int rows = B * (2 * gamma + 1);
-  shard_nuc_reduce_kernel<<<rows, kNucBins, 0, static_cast<cudaStream_t>(stream)>>>(
+  shard_nuc_reduce_kernel<<<(rows + 3) / 4, 128, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const unsigned char*>(gathered_hist), world, rows, gamma, top_p, draft_top_p,
       static_cast<ShardSel*>(sel), level, levels, rank, quota);
   return int(cudaGetLastError());
@@ -593,7 +598,7 @@ int duodec_shard_nucleus_tie(const void* draft, const void* target, int dtype, i
   if (!shard_rows_ok(draft, target, dtype, B, gamma, Vs) || temperature <= 0.0f || draft_temperature <= 0.0f)
     return DUODEC_EINVAL;
   if (B == 0) return 0;
-  if (!sel || !quota || !cand || (levels != 2 && levels != 4)) return DUODEC_EINVAL;
+  if (!sel || !quota || !cand || (levels != 4 && levels != 8)) return DUODEC_EINVAL;
   const ShardRows S{draft, target, d_sb, d_ss, t_sb, t_ss, B, gamma, Vs, v_begin, temperature, draft_temperature};
   const int rows = B * (2 * gamma + 1);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -609,7 +614,7 @@ int duodec_shard_nucleus_close(const void* sel, const float* gathered_stats, con
                                int B, int gamma, int levels, void* cuts, void* stream) {
   if (world <= 0 || B < 0 || gamma < 0) return DUODEC_EINVAL;
   if (B == 0) return 0;
-  if (!sel || !gathered_stats || !gathered_cand || !cuts || (levels != 2 && levels != 4)) return DUODEC_EINVAL;
+  if (!sel || !gathered_stats || !gathered_cand || !cuts || (levels != 4 && levels != 8)) return DUODEC_EINVAL;
   const int rows = B * (2 * gamma + 1);
   shard_nuc_close_kernel<<<(rows + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const ShardSel*>(sel), reinterpret_cast<const float4*>(gathered_stats), gathered_cand, world, rows,

@@ -12,8 +12,8 @@ tensor-parallel LM head leaves behind - and the step needs two small exchanges (
     finish   token of every sequence                                      kernel  duodec_shard_finish
 
 With ``top_p > 0`` a distributed radix select of every row's nucleus boundary runs between the first gather and
-``accept`` (csrc/shard_nucleus.cuh): per level (two for bf16 rows at temperature 1, four otherwise) a 256-bin
-(mass, count) histogram of the slice, an all-gather of the bins and a reduction to the next key prefix; then the
+``accept`` (csrc/shard_nucleus.cuh): per level (four for bf16 rows at temperature 1, eight otherwise) a 16-bin
+(mass, count) histogram of the slice, an all-gather of the bins (192 B per row) and a reduction to the next key prefix; then the
 index cut among equal values (one more 4-byte all-gather) - ``2 + levels + 1`` exchanges per step.  Masses are
 fixed-point integers, so the kept set of a row is the same for every world size.
 
@@ -47,7 +47,7 @@ class _CudaBackend:
     def __init__(self):
         from . import _lib, ops
         self.lib, self.ops, self.check = _lib.lib, ops, _lib.check
-        self.PLAN, self.PARTIAL, self.HIST, self.SEL, self.CUT = 48, 24, 3072, 32, 16
+        self.PLAN, self.PARTIAL, self.HIST, self.SEL, self.CUT = 48, 24, 192, 32, 16
 
     def _rows(self, t):
         return (t.data_ptr(), t.stride(0), t.stride(1)) if t is not None and t.numel() else (None, 0, 0)

@@ -220,9 +220,9 @@ int duodec_shard_finish(const void* gathered_partials, int world, int B, int nsl
 
 /* Top-p under vocabulary sharding (reference: top_k_top_p_filter, src/utils.py:650-683, as applied by
  * norm_logits, :686-709): a distributed radix select of the nucleus boundary over the order-preserving key of the
- * scaled logit, 8 bits per level, between exchange 1 and duodec_shard_accept.  Masses are 40-bit fixed point
+ * scaled logit, 4 bits per level, between exchange 1 and duodec_shard_accept.  Masses are 40-bit fixed point
  * relative to the row maximum and summed as integers: the answer does not depend on the world size.
- *   levels  = duodec_shard_nucleus_levels(dtype, T, draft T): 2 (bf16 rows at temperature 1) or 4
+ *   levels  = duodec_shard_nucleus_levels(dtype, T, draft T): 4 (bf16 rows at temperature 1) or 8
  *   for level in 0 .. levels-1:
  *     duodec_shard_nucleus_level   -> hist [rows, DUODEC_SHARD_HIST_BYTES] of this rank
  *     (all-gather hist -> [world, rows, DUODEC_SHARD_HIST_BYTES])
@@ -232,7 +232,7 @@ int duodec_shard_finish(const void* gathered_partials, int world, int B, int nsl
  *   duodec_shard_nucleus_close     -> cuts [rows, DUODEC_SHARD_CUT_BYTES]: (x*, i*, kept mass, state)
  * then duodec_shard_accept(..., tokens, tok_sb, cuts, ...) and duodec_shard_sample(..., filtered = 1, ...).
  * top_p / draft_top_p <= 0 leave that model's rows unfiltered.  Not available with the fused exchange. */
-#define DUODEC_SHARD_HIST_BYTES 3072
+#define DUODEC_SHARD_HIST_BYTES 192
 #define DUODEC_SHARD_SEL_BYTES 32
 #define DUODEC_SHARD_CUT_BYTES 16
 int duodec_shard_nucleus_levels(int dtype, float temperature, float draft_temperature);

@@ -81,7 +81,7 @@ def _run_top_p(world, dl, tl, toks, r, noise, T, top_p, d_top_p, dev):
 def test_shard_top_p_matches_unsharded_oracle_for_every_world_size(dtype):
     """Top-p under vocabulary sharding (shard_nucleus.cuh) against the unsharded oracle (src/utils.py:650-709,
     src/decoding_ops.py:109-220): lengths, tokens and masks exact, selected probabilities up to one boundary entry
-    (cf. NUCLEUS_RTOL in test_gpu_parity.py); the filter itself is bit-identical for 1, 2, 3 and 8 ranks."""
+    (cf. NUCLEUS_RTOL in test_gpu_parity.py); the filter itself is bit-identical for 1, 2, 3 and 8 ranks."""  # noqa
     dev = torch.device("cuda:0")
     for seed, sigma, T, top_p, d_top_p in [(1, 0.5, 1.0, 0.9, 0.9), (2, 1.5, 1.0, 0.5, 0.95), (3, 1.0, 0.7, 0.9, 0.9),
                                             (4, 1.0, 1.0, 0.9, 0.0), (5, 1.0, 1.0, 1.0, 0.3)]:
@@ -92,7 +92,7 @@ def test_shard_top_p_matches_unsharded_oracle_for_every_world_size(dtype):
         ref_cuts = None
         for world in (1, 2, 3, 8):
             got, cuts, levels = _run_top_p(world, dl, tl, toks, r, noise, T, top_p, d_top_p, dev)
-            assert levels == (2 if dtype == torch.bfloat16 and T == 1.0 else 4)
+            assert levels == (4 if dtype == torch.bfloat16 and T == 1.0 else 8)
             what = (seed, world)
             assert torch.equal(got["accepted_len"].cpu(), want["accepted_len"]), what
             assert torch.equal(got["token"].cpu(), want["token"]), what
