@@ -46,6 +46,7 @@ SIGNATURES = {
         + [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]  # outputs
         + [c_void_p, c_size_t, c_void_p],  # workspace, stream
     ),
+    "duodec_token_ranks": (c_int, [c_void_p, c_int, c_i64, c_int, c_int, c_void_p, c_i64, c_void_p, c_void_p]),
     "duodec_verify_static_max_bytes": (c_size_t, []),
     "duodec_verify_fused_static": (
         c_int,

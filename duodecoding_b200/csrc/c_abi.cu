@@ -668,6 +668,22 @@ int duodec_shard_topk_apply(const void* x, int dtype, int64_t in_stride, void* o
   return int(cudaGetLastError());
 }
 
+int duodec_token_ranks(const void* probs, int dtype, int64_t row_stride, int rows, int V, const int64_t* tokens,
+                       int64_t tok_stride, int32_t* out, void* stream) {
+  if (rows < 0 || V <= 0) return DUODEC_EINVAL;
+  if (rows == 0) return 0;
+  if (!probs || !tokens || !out || (dtype != DUODEC_F32 && dtype != DUODEC_BF16)) return DUODEC_EINVAL;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dtype == DUODEC_F32)
+    token_rank_kernel<float><<<rows, kThreads, 0, st>>>(static_cast<const float*>(probs), row_stride, V,
+                                                        reinterpret_cast<const long long*>(tokens), tok_stride, out);
+  else
+    token_rank_kernel<__nv_bfloat16><<<rows, kThreads, 0, st>>>(static_cast<const __nv_bfloat16*>(probs), row_stride,
+                                                                V, reinterpret_cast<const long long*>(tokens),
+                                                                tok_stride, out);
+  return int(cudaGetLastError());
+}
+
 int duodec_uncertainty_tokens(const void* logits, int dtype, int V, const float* temps, const float* noise,
                               int64_t noise_stride, int M, int64_t* tokens, void* stream) {
   if (V <= 0 || M < 0) return DUODEC_EINVAL;

@@ -67,4 +67,34 @@ __global__ void __launch_bounds__(256) compressed_vocab_kernel(const float* __re
   if ((above + below) / denominator <= theta) atomicMin(k_out, k);
 }
 
+// Rank bookkeeping of the accepted tokens (_record_accepted_token_ranks, /root/reference/src/baselines.py:121-168:
+// per token a `(probs > p).sum().item()`, a sorted torch.topk of the row and a `.nonzero()` - three host syncs and
+// a sort per accepted token).  One block per accepted position: the number of entries greater than the token's
+// probability and the number of EQUAL entries at a lower index (the canonical order of the sorted top-k) - the
+// caller reads both counts of every position back in one copy.
+template <class TIn>
+__global__ void __launch_bounds__(kThreads) token_rank_kernel(const TIn* __restrict__ probs, long long row_stride,
+                                                              int V, const long long* __restrict__ tokens,
+                                                              long long tok_stride, int* __restrict__ out) {
+  __shared__ Xchg xc;
+  const int rowi = blockIdx.x;
+  const TIn* row = probs + (long long)rowi * row_stride;
+  const long long tok = tokens[(long long)rowi * tok_stride];
+  int greater = 0, before = 0;
+  if (tok >= 0 && tok < V) {
+    const float pt = to_f32(row[tok]);
+    for (int i = threadIdx.x; i < V; i += kThreads) {
+      const float p = to_f32(row[i]);
+      greater += (p > pt);
+      before += (p == pt && i < tok);
+    }
+  }
+  greater = block_allreduce(greater, OpSumI(), &xc);
+  before = block_allreduce(before, OpSumI(), &xc);
+  if (threadIdx.x == 0) {
+    out[2 * rowi] = (tok >= 0 && tok < V) ? greater : -1;
+    out[2 * rowi + 1] = before;
+  }
+}
+
 }  // namespace duodec

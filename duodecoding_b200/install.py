@@ -14,7 +14,7 @@ from __future__ import annotations
 import importlib
 from typing import Dict, List, Tuple
 
-from . import communication, decoding_ops, model_gpu, proposal_utils, utils
+from . import baselines, communication, decoding_ops, model_gpu, proposal_utils, utils
 
 _PLAN = {
     "utils": (utils, ["top_k_top_p_filter", "norm_logits", "sample", "max_fn", "rebuild_topk_probs",
@@ -27,6 +27,9 @@ _PLAN = {
                                     "rebuild_topk_uniform_probs"]),
     "proposal_utils": (proposal_utils, ["proposal_top_k", "build_draft_probs_override", "stage_prob_history"]),
     "model_gpu": (model_gpu, ["KVCacheModel", "norm_logits", "sample", "rebuild_topk_uniform_probs"]),
+    # (src.baselines imports optional packages: skipped when it does not import)
+    "baselines": (baselines, ["_compute_token_vocab_rank", "_compute_transfer_topk_rank",
+                              "_record_accepted_token_ranks"]),
 }
 _SAVED: List[Tuple[object, str, object]] = []
 

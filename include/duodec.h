@@ -266,6 +266,15 @@ int duodec_shard_topk_apply(const void* x, int dtype, int64_t in_stride, void* o
                             int Vs, int v_begin, const float* tau, const int32_t* istar, const float* fill,
                             const float* total, void* stream);
 
+/* Rank bookkeeping of accepted tokens: _compute_token_vocab_rank / _compute_transfer_topk_rank /
+ * _record_accepted_token_ranks, src/baselines.py:121-168 (per token: a count with .item(), a sorted torch.topk
+ * and a .nonzero()).  Row i of `probs` (rows x V, row_stride elements apart) and tokens[i * tok_stride]:
+ *   out[2*i]   = number of entries greater than the token's probability (vocab rank - 1); -1 for an invalid id
+ *   out[2*i+1] = number of entries EQUAL to it at a lower index (sorted top-k rank = out[2*i] + out[2*i+1] + 1,
+ *                equal values in index order - torch.topk leaves that order unspecified) */
+int duodec_token_ranks(const void* probs, int dtype, int64_t row_stride, int rows, int V, const int64_t* tokens,
+                       int64_t tok_stride, int32_t* out, void* stream);
+
 /* ---- CUHLM helpers (CommunicationSimulator) --------------------------------------------
  * duodec_uncertainty_tokens: calculate_uncertainty (src/communication.py:541-575) - for each of M
  *   temperatures temps[m] > 0 one draw from softmax(logits / temps[m]) of ONE row logits[V], as

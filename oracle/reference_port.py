@@ -31,6 +31,9 @@ import torch
 import torch.nn.functional as F
 
 __all__ = [
+    "token_vocab_rank",
+    "transfer_topk_rank",
+    "record_accepted_token_ranks",
     "filter_logits",
     "norm_logits",
     "sample",
@@ -509,3 +512,38 @@ def compressed_vocab_size(uncertainty: float, current_probs: torch.Tensor, vocab
         if numerator / denominator <= theta:
             return k
     return min(default_size, vocab_size // 100)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# Rank bookkeeping of accepted tokens
+def token_vocab_rank(probs: torch.Tensor, token_id: int) -> int:
+    """src/baselines.py:121-123: 1 + number of entries greater than the token's probability."""
+    return int((probs > probs[..., token_id]).sum().item()) + 1
+
+
+def transfer_topk_rank(probs: torch.Tensor, token_id: int, transfer_top_k: Optional[int], vocab_rank: int):
+    """src/baselines.py:126-141: (in top-k, 1-based position in the sorted top-k); equal values in index order
+    (topk_canonical - torch.topk leaves that order unspecified)."""
+    V = probs.shape[-1]
+    if transfer_top_k is None or transfer_top_k <= 0 or transfer_top_k >= V:
+        return True, vocab_rank
+    _, idx = topk_canonical(probs.reshape(1, V), min(int(transfer_top_k), V))
+    hit = (idx[0] == token_id).nonzero(as_tuple=False)
+    if hit.numel() == 0:
+        return False, 0
+    return True, int(hit[0].item()) + 1
+
+
+def record_accepted_token_ranks(*, stage_probs, x, prefix_len, accepted_count, transfer_top_k, vocab_rank_history,
+                                in_transfer_topk_history, transfer_topk_rank_history) -> None:
+    """src/baselines.py:144-168."""
+    if stage_probs is None or accepted_count <= 0:
+        return
+    for i in range(accepted_count):
+        token_id = int(x[:, prefix_len + i].item())
+        probs = stage_probs[0, prefix_len + i - 1, :]
+        vr = token_vocab_rank(probs, token_id)
+        ok, tr = transfer_topk_rank(probs, token_id, transfer_top_k, vr)
+        vocab_rank_history.append(vr)
+        in_transfer_topk_history.append(ok)
+        transfer_topk_rank_history.append(tr)

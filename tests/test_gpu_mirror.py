@@ -440,3 +440,52 @@ def test_cuhlm_helpers_match_reference_goldens_and_oracle(mods, dev):
         assert comm.compressed_vocab_size(unc, probs.to(dev), V, theta, 5) == want_k
     assert comm.CUHLM.calculate_uncertainty(None) == 1.0
     assert comm.CUHLM(vocab_size=10)._calculate_compressed_vocab_size(0.5, probs[:7].to(dev)) == 1  # length mismatch rule
+
+
+def test_rank_helpers_match_reference_goldens_and_oracle(dev):
+    """duodecoding_b200.baselines (one kernel + one read-back for all accepted positions) against the reference
+    outputs in tests/golden/ranks_v1.npz and, on rows full of equal values, against the oracle's canonical order."""
+    import os
+
+    import numpy as np
+
+    import oracle
+    from duodecoding_b200 import baselines as B
+
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "ranks_v1.npz"))
+    for ci in sorted({k.split("/")[1] for k in z.files}):
+        pre = f"ranks/{ci}/"
+        prefix, accepted, k = (int(v) for v in z[pre + "params"])
+        probs, x = torch.from_numpy(z[pre + "probs"]).to(dev), torch.from_numpy(z[pre + "x"]).to(dev)
+        vr, it, tr = [7], [True], [7]  # the histories are appended to
+        B._record_accepted_token_ranks(stage_probs=probs, x=x, prefix_len=prefix, accepted_count=accepted,
+                                       transfer_top_k=k, vocab_rank_history=vr, in_transfer_topk_history=it,
+                                       transfer_topk_rank_history=tr)
+        assert vr[1:] == z[pre + "vocab_rank"].tolist() and it[1:] == z[pre + "in_topk"].tolist(), ci
+        assert tr[1:] == z[pre + "topk_rank"].tolist(), ci
+        if accepted:
+            tok = int(x[0, prefix])
+            rank = B._compute_token_vocab_rank(probs[0, prefix - 1], tok)
+            assert rank == vr[1]
+            assert B._compute_transfer_topk_rank(probs[0, prefix - 1], tok, k, rank) == (it[1], tr[1])
+    # equal values (bf16 grid), bf16 storage, a strided history, k at the tie
+    g = torch.Generator().manual_seed(5)
+    pf = torch.softmax((torch.randn(1, 9, 4096, generator=g) * 2).bfloat16().float(), -1)
+    for probs in (pf, pf.bfloat16()):
+        x = torch.randint(0, 4096, (1, 10), generator=g)
+        x[0, 3] = int(torch.argsort(pf[0, 2], descending=True, stable=True)[40])
+        for k in (None, 41, 40, 300):
+            want = ([], [], [])
+            oracle.record_accepted_token_ranks(stage_probs=probs.float(), x=x, prefix_len=2, accepted_count=6,
+                                               transfer_top_k=k, vocab_rank_history=want[0],
+                                               in_transfer_topk_history=want[1], transfer_topk_rank_history=want[2])
+            got = ([], [], [])
+            B._record_accepted_token_ranks(stage_probs=probs.to(dev), x=x.to(dev), prefix_len=2, accepted_count=6,
+                                           transfer_top_k=k, vocab_rank_history=got[0],
+                                           in_transfer_topk_history=got[1], transfer_topk_rank_history=got[2])
+            assert got == want, (probs.dtype, k)
+    none = ([], [], [])
+    B._record_accepted_token_ranks(stage_probs=None, x=x.to(dev), prefix_len=2, accepted_count=3, transfer_top_k=8,
+                                   vocab_rank_history=none[0], in_transfer_topk_history=none[1],
+                                   transfer_topk_rank_history=none[2])
+    assert none == ([], [], [])

@@ -142,3 +142,25 @@ def test_cuhlm_oracle_is_pinned_to_the_reference():
         probs = torch.from_numpy(z[pre + "probs"])
         got = oracle.compressed_vocab_size(float(unc), probs, len(probs), float(theta), None if draft < 0 else int(draft))
         assert got == int(z[pre + "k"][0]), (ci, got)
+
+
+def test_rank_helpers_oracle_is_pinned_to_the_reference():
+    """The oracle's restatement of the rank bookkeeping (src/baselines.py:121-168) against outputs of the unmodified
+    reference functions (tests/golden/ranks_v1.npz, written by oracle/gen_golden_ranks.py)."""
+    import numpy as np
+    import os
+    import torch
+    import oracle as O
+
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "ranks_v1.npz"))
+    cases = sorted({k.split("/")[1] for k in z.files})
+    assert len(cases) == 6
+    for ci in cases:
+        pre = f"ranks/{ci}/"
+        prefix, accepted, k = (int(v) for v in z[pre + "params"])
+        vr, it, tr = [], [], []
+        O.record_accepted_token_ranks(stage_probs=torch.from_numpy(z[pre + "probs"]), x=torch.from_numpy(z[pre + "x"]),
+                                      prefix_len=prefix, accepted_count=accepted, transfer_top_k=k,
+                                      vocab_rank_history=vr, in_transfer_topk_history=it, transfer_topk_rank_history=tr)
+        assert vr == z[pre + "vocab_rank"].tolist() and it == z[pre + "in_topk"].tolist(), ci
+        assert tr == z[pre + "topk_rank"].tolist(), ci
