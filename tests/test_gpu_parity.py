@@ -601,3 +601,18 @@ def test_verify_fused_on_two_streams_does_not_share_a_workspace(ops, dev):
                 assert torch.equal(got[k], serial[s][k]), (s, k)
             # (each workspace carries its own exponent-offset hint: a boundary entry may flip, cf. NUCLEUS_RTOL)
             torch.testing.assert_close(got["selected_target_p"], serial[s]["selected_target_p"], rtol=NUCLEUS_RTOL, atol=1e-9)
+
+
+def test_bf16_reference_goldens_decisions_agree_outside_bf16_rounding(ops, dev):
+    """tests/golden/bf16_v1.npz holds what the UNMODIFIED reference computes IN BFLOAT16 (its models' dtype,
+    src/engine.py:261): bf16 logits / T, bf16 softmax, bf16 p/q, bf16 comparison.  The kernels read the same bf16
+    logits and compute in fp32 (canonicalisations): selected probabilities agree to bf16 precision, and
+    every accept decision agrees unless |p/q - r| lies inside bf16 rounding of the ratio."""
+    from tests.bf16_check import check_against_bf16_goldens
+
+    def run(dl, tl, toks, r, T, top_k, top_p):
+        noise = torch.ones(toks.shape[0], tl.shape[-1], device=dev)
+        got = ops.verify_fused(dl.to(dev), tl.to(dev), toks.to(dev), r.to(dev), noise, T, top_k, top_p)
+        return {k: v.cpu() for k, v in got.items()}
+
+    check_against_bf16_goldens(run)

@@ -164,3 +164,17 @@ def test_rank_helpers_oracle_is_pinned_to_the_reference():
                                       vocab_rank_history=vr, in_transfer_topk_history=it, transfer_topk_rank_history=tr)
         assert vr == z[pre + "vocab_rank"].tolist() and it == z[pre + "in_topk"].tolist(), ci
         assert tr == z[pre + "topk_rank"].tolist(), ci
+
+
+def test_bf16_reference_goldens_vs_fp32_oracle():
+    """The canonicalisation "bf16 rows are evaluated in fp32" pinned on the CPU: the fp32 oracle on the bf16 logits of
+    tests/golden/bf16_v1.npz agrees with the reference's own bf16 arithmetic to bf16 precision, and in every decision
+    outside bf16 rounding of p/q."""
+    import torch
+    import oracle as O
+    from tests.bf16_check import check_against_bf16_goldens
+
+    def run(dl, tl, toks, r, T, top_k, top_p):
+        return O.fused_verify(dl.float(), tl.float(), toks, r, torch.ones(toks.shape[0], tl.shape[-1]), T, top_k, top_p)
+
+    check_against_bf16_goldens(run)
