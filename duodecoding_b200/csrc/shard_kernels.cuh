@@ -193,10 +193,23 @@ __global__ void __launch_bounds__(kThreads) shard_stats_kernel(const __grid_cons
     }
   };
   if (row_vec8(row, S.Vs)) {
-    for (int i = threadIdx.x * 8; i < S.Vs; i += kThreads * 8) {
-      float x[8];
-      load8<TIn>(row + i, x);
-      push8(x);
+    // kStatBatch groups of eight entries per trip: all their loads are issued before the first is consumed (a
+    // slice of V / 8 is under five groups per thread: one trip, every load of the row in flight at once)
+    constexpr int kStatBatch = 5;
+    for (int i0 = threadIdx.x * 8; i0 < S.Vs; i0 += kThreads * 8 * kStatBatch) {
+      float x[kStatBatch][8];
+#pragma unroll
+      for (int k = 0; k < kStatBatch; ++k) {
+        const int i = i0 + k * kThreads * 8;
+        if (i < S.Vs) {
+          load8<TIn>(row + i, x[k]);
+        } else {
+#pragma unroll
+          for (int u = 0; u < 8; ++u) x[k][u] = -INFINITY;  // (contributes nothing)
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < kStatBatch; ++k) push8(x[k]);
     }
   } else {
     for (int i = threadIdx.x; i < S.Vs; i += kThreads) {

@@ -48,3 +48,19 @@ cuts = timed("close", lambda: be.nucleus_close(sel, gstats, cand.unsqueeze(0), B
 out, plan = timed("accept", lambda: be.accept(gstats, B, G, r, tokens=toks, cuts=cuts))
 part = timed("sample (filtered)", lambda: be.sample_partial(dl, tl, plan, noise, 0, T, T, G, filtered=True))
 timed("finish", lambda: be.finish(part.unsqueeze(0), B))
+
+# the whole step (one CUDA graph) on this slice as a world-1 problem: the compute floor of one rank
+from duodecoding_b200.sharded import ShardedVerifier
+
+sv = ShardedVerifier(Vs, rank=0, world=1)
+for name, kw in (("step, no filter", {}), ("step, top_p=0.9", {"top_p": P})):
+    for _ in range(3):
+        sv.verify(dl, tl, toks, r, noise, T, **kw)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(20):
+        sv.verify(dl, tl, toks, r, noise, T, **kw)
+    e1.record()
+    torch.cuda.synchronize()
+    print(f"{name:28s} {e0.elapsed_time(e1) * 1e3 / 20:9.1f} us (graph replay)", flush=True)
