@@ -24,6 +24,8 @@
 // gathered data locally.  No NCCL call, no extra launch; a step is four kernels in one CUDA graph.
 #pragma once
 
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace duodec {
@@ -175,11 +177,15 @@ __global__ void __launch_bounds__(kThreads) shard_stats_kernel(const __grid_cons
   const TIn* row = shard_row<TIn>(S, b, j, is_target);
   const float temp = is_target ? S.t_temp : S.d_temp;
   MaxSum acc{-INFINITY, 0.0f};
+  // the temperature test is hoisted out of the entry loops (kUnit: temperature 1, no division): a per-entry
+  // `T == 1 ? x : x / T` keeps a branch and an inlined IEEE division per entry in the loop body
+  auto body = [&](auto unit_tag) {
+  constexpr bool kUnit = decltype(unit_tag)::value;
   auto push8 = [&](float (&x)[8]) {
-    float vm = x[0];
+    float vm = -INFINITY;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      x[i] = scale_logit(x[i], temp);
+      if (!kUnit) x[i] = __fdiv_rn(x[i], temp);
       vm = fmaxf(vm, x[i]);
     }
     if (vm > acc.m) {
@@ -220,6 +226,9 @@ __global__ void __launch_bounds__(kThreads) shard_stats_kernel(const __grid_cons
       push8(x);
     }
   }
+  };
+  if (temp == 1.0f) body(std::true_type{});
+  else body(std::false_type{});
   if (!(acc.s == acc.s)) acc.s = 0.0f;  // -inf - -inf on a thread that saw nothing
   acc = block_allreduce(acc, OpMaxSum(), &xc);
   if (threadIdx.x == 0) {
@@ -367,38 +376,50 @@ __global__ void __launch_bounds__(kThreads) shard_sample_kernel(const __grid_con
   int bidx = 0x7fffffff, bdi = 0x7fffffff;
   // branch-free per entry; a thread meets its indices in increasing order, so strict ">" keeps the lowest
   // index of a tie (same arithmetic as the fused path's sample kernel: __fdividef race keys)
-  auto one = [&](float xp, float xq, float e, int i) {
-    const float xps = scale_logit(xp, S.t_temp);
-    float d = ex2f(fmaf(xps, kShardLog2e, -mp)) * rZp;
-    if (kCut) d = cut_keeps(xps, S.v_begin + i, pl.xsp, pl.isp) ? d : 0.0f;
-    if (!pl.bonus) {
-      const float xqs = scale_logit(xq, S.d_temp);
-      float dq = ex2f(fmaf(xqs, kShardLog2e, -mq)) * rZq;
-      if (kCut) dq = cut_keeps(xqs, S.v_begin + i, pl.xsq, pl.isq) ? dq : 0.0f;
-      d -= dq;
-    }
-    const bool pos = d > 0.0f;
-    mass += pos ? d : 0.0f;
-    const float k = pos ? __fdividef(d, e) : -1.0f;
-    const bool bk = k > bkey;
-    bkey = bk ? k : bkey, bidx = bk ? i : bidx;
-    const float dz = (fabsf(d) < INFINITY) ? d : 0.0f;  // NaN and +-inf count as 0
-    const bool bd = dz > bdv;
-    bdv = bd ? dz : bdv, bdi = bd ? i : bdi;
-  };
-  const bool vec = row_vec8(prow, S.Vs) && row_vec8(qrow, S.Vs) && (reinterpret_cast<uintptr_t>(nz) & 31) == 0;
-  if (vec) {
-    for (int i = lo + threadIdx.x * 8; i < hi; i += kThreads * 8) {
-      float xp[8], xq[8], e[8];
-      load8<TIn>(prow + i, xp);
-      if (!pl.bonus) load8<TIn>(qrow + i, xq);
-      load8<float>(nz + i, e);
+  // the temperature tests and the bonus / residual choice are uniform over the block: hoisted out of the entry loop
+  auto body = [&](auto unit_tag, auto bonus_tag) {
+    constexpr bool kUnit = decltype(unit_tag)::value, kBonus = decltype(bonus_tag)::value;
+    auto one = [&](float xp, float xq, float e, int i) {
+      const float xps = kUnit ? xp : __fdiv_rn(xp, S.t_temp);
+      float d = ex2f(fmaf(xps, kShardLog2e, -mp)) * rZp;
+      if (kCut) d = cut_keeps(xps, S.v_begin + i, pl.xsp, pl.isp) ? d : 0.0f;
+      if (!kBonus) {
+        const float xqs = kUnit ? xq : __fdiv_rn(xq, S.d_temp);
+        float dq = ex2f(fmaf(xqs, kShardLog2e, -mq)) * rZq;
+        if (kCut) dq = cut_keeps(xqs, S.v_begin + i, pl.xsq, pl.isq) ? dq : 0.0f;
+        d -= dq;
+      }
+      const bool pos = d > 0.0f;
+      mass += pos ? d : 0.0f;
+      const float k = pos ? __fdividef(d, e) : -1.0f;
+      const bool bk = k > bkey;
+      bkey = bk ? k : bkey, bidx = bk ? i : bidx;
+      const float dz = (fabsf(d) < INFINITY) ? d : 0.0f;  // NaN and +-inf count as 0
+      const bool bd = dz > bdv;
+      bdv = bd ? dz : bdv, bdi = bd ? i : bdi;
+    };
+    const bool vec = row_vec8(prow, S.Vs) && row_vec8(qrow, S.Vs) && (reinterpret_cast<uintptr_t>(nz) & 31) == 0;
+    if (vec) {
+      for (int i = lo + threadIdx.x * 8; i < hi; i += kThreads * 8) {
+        float xp[8], xq[8], e[8];
+        load8<TIn>(prow + i, xp);
+        if (!kBonus) load8<TIn>(qrow + i, xq);
+        load8<float>(nz + i, e);
 #pragma unroll
-      for (int u = 0; u < 8; ++u) one(xp[u], pl.bonus ? 0.0f : xq[u], e[u], i + u);
+        for (int u = 0; u < 8; ++u) one(xp[u], kBonus ? 0.0f : xq[u], e[u], i + u);
+      }
+    } else {
+      for (int i = lo + threadIdx.x; i < hi; i += kThreads)
+        one(to_f32(prow[i]), kBonus ? 0.0f : to_f32(qrow[i]), nz[i], i);
     }
+  };
+  const bool unit = S.t_temp == 1.0f && S.d_temp == 1.0f;  // (mixed temperatures take the dividing variant: x / 1 == x)
+  if (unit) {
+    if (pl.bonus) body(std::true_type{}, std::true_type{});
+    else body(std::true_type{}, std::false_type{});
   } else {
-    for (int i = lo + threadIdx.x; i < hi; i += kThreads)
-      one(to_f32(prow[i]), pl.bonus ? 0.0f : to_f32(qrow[i]), nz[i], i);
+    if (pl.bonus) body(std::false_type{}, std::true_type{});
+    else body(std::false_type{}, std::false_type{});
   }
   const unsigned long long key =
       bidx == 0x7fffffff ? 0ull

@@ -101,8 +101,10 @@ __global__ void __launch_bounds__(kThreads) shard_nuc_level_kernel(const __grid_
   if (st.state == 0) {
     const float mo = st.M * kShardLog2e;
     const int shift = 32 - kNucBits * (level + 1);
+    auto body = [&](auto unit_tag) {  // (the temperature test hoisted out of the entry loop, as in shard_stats_kernel)
+    constexpr bool kUnit = decltype(unit_tag)::value;
     auto one = [&](float raw) {
-      const float x = scale_logit(raw, temp);
+      const float x = kUnit ? raw : __fdiv_rn(raw, temp);
       const unsigned key = nuc_key(x);
       // branch-free: an entry outside the prefix adds 0 to its column (a divergent read-modify-write per entry
       // measured 20x slower than the uniform one)
@@ -120,6 +122,9 @@ __global__ void __launch_bounds__(kThreads) shard_nuc_level_kernel(const __grid_
     } else {
       for (int i = tid; i < S.Vs; i += kThreads) one(to_f32(row[i]));
     }
+    };
+    if (temp == 1.0f) body(std::true_type{});
+    else body(std::false_type{});
   }
   __syncthreads();
   // warp w sums bin w over the threads (kWarps == kNucBins)
