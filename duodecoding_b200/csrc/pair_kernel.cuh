@@ -95,7 +95,7 @@ __device__ __forceinline__ void barh(int h) {  // named barrier of one half (imm
   __syncwarp();                                                                               \
   if (lane == 0) mbar_arrive(&ps->empty[h][slot]);                                            \
   ++seq;
-#ifdef PAIR_ONEBRANCH
+#ifndef PAIR_GROUP_BRANCHES  // (default since the A/B of round 2: -0.5 us per C2 step)
 // one branch per stage: only the row's last stage can be ragged
 #define PAIR_EACH(F)                                                                          \
   if (i00 + 3 * kHT * 4 < V) {                                                                \
@@ -523,7 +523,7 @@ __global__ void __launch_bounds__(kPT, 2) row_pair_kernel(const __grid_constant_
     *a1 = s1;                                                       \
   }
 #define FP_HIST4(v) FP_HIST2(v.x, v.y) FP_HIST2(v.z, v.w)
-#ifdef PAIR_RMW2
+#ifndef PAIR_RMW1  // (default: two entries per histogram round, -0.2 us per C2 step)
         PAIR_EACH4(FP_HIST4)
 #else
         PAIR_EACH(FP_HIST)
