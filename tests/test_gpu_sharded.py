@@ -154,3 +154,47 @@ def test_sharded_topk_candidate_merge_matches_unsharded_rebuild(world, dtype):
         got = torch.cat([rk.apply(x, rk.merge(gv, gi, k)) for rk, x in zip(ranks, parts)], -1).cpu().float()
         # (atol: with k = V - 1 the single hole takes 1 - sum(kept), a cancellation of order 1 ulp of 1.0)
         torch.testing.assert_close(got, want, rtol=1e-5 if dtype == torch.float32 else 1e-2, atol=2e-7)
+
+
+def test_shard_top_p_adversarial_rows_keep_the_oracles_support():
+    """The filters (x*, i*) of the distributed select, decoded into kept sets, against the support of the oracle's
+    top-p filter (float64 reference of src/utils.py:669-681) on rows built to stress it: all entries equal (the index
+    cut runs across the ranks), two plateaus, -inf entries, one dominant entry, a tiny and a near-1 top_p."""
+    dev = torch.device("cuda:0")
+    B, gamma, V = 2, 3, 4104
+    g = torch.Generator().manual_seed(12)
+    tl = torch.randn(B, gamma + 1, V, generator=g) * 3
+    tl[0, 0] = 0.25                                   # uniform: the first ceil(top_p * V) indices are kept
+    tl[0, 1, : V // 2], tl[0, 1, V // 2:] = 1.5, -0.5  # two plateaus
+    tl[0, 2, ::3] = float("-inf")                      # a third of the row masked out upstream
+    tl[0, 3] = -5.0
+    tl[0, 3, 1234] = 20.0                              # one dominant entry
+    tl[1, 0] = (tl[1, 0] * 4).round() / 4              # coarse grid: many ties at the boundary
+    dl = tl[:, :gamma] + 0.5 * torch.randn(B, gamma, V, generator=g)
+    toks = torch.randint(0, V, (B, gamma), generator=g)
+    r = torch.rand(B, gamma, generator=g)
+    noise = torch.empty(B, V).exponential_(1, generator=g)
+    idx = torch.arange(V)
+    for top_p in (0.9, 0.02, 0.999):
+        for world in (1, 3, 8):
+            _, cuts, _ = _run_top_p(world, dl, tl, toks, r, noise, 1.0, top_p, top_p, dev)
+            c = cuts.cpu().view(torch.int32).reshape(B, 2 * gamma + 1, 4)
+            for b in range(B):
+                for j in range(gamma + 1):
+                    row = tl[b, j]
+                    cut = c[b, 2 * j + 1 if j < gamma else 2 * gamma]
+                    xs, istar = cut[:1].view(torch.float32).item(), int(cut[1])
+                    got = (row > xs) | ((row == xs) & (idx <= istar))
+                    want = torch.isfinite(oracle.filter_logits(row.double().unsqueeze(0), 0, top_p)[0])
+                    diff = int((got != want).sum())
+                    # the float64 oracle and the 40-bit fixed-point sums may disagree on entries at the boundary
+                    # whose inclusion changes the kept mass by less than 1e-6
+                    assert diff <= 2, (top_p, world, b, j, diff, int(got.sum()), int(want.sum()))
+                    if diff:
+                        p = torch.softmax(row.double(), 0)
+                        assert float(p[got != want].sum()) < 1e-3 and abs(float(p[got].sum()) - float(p[want].sum())) < 1e-3
+                    # equal values are kept lowest index first
+                    ties = row == xs
+                    if bool(ties.any()) and xs > float("-inf"):
+                        kept_ties = idx[ties & got]
+                        assert len(kept_ties) >= 1 and bool((idx[ties][: len(kept_ties)] == kept_ties).all())
