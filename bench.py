@@ -569,7 +569,7 @@ def c5_measure(dev, world, rank, dist, K, W, top_p=0.0):
     from duodecoding_b200.sharded import ShardedVerifier
 
     Bc, Gc, Vc = 256, 6, 151936
-    sv = ShardedVerifier(Vc, rank=rank, world=world)
+    sv = ShardedVerifier(Vc, rank=rank, world=world, fused_exchange=os.environ.get("DUODEC_C5_EXCHANGE") or False)
     g = torch.Generator(device=dev).manual_seed(4321)  # the same full tensors on every rank
     sets, full0 = [], None
     for si in range(2):

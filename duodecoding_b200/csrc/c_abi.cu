@@ -627,8 +627,9 @@ int duodec_shard_finish(const void* gathered_partials, int world, int B, int nsl
   if (world <= 0 || B < 0 || nslice <= 0) return DUODEC_EINVAL;
   if (B == 0) return 0;
   if (!xchg_ok(xchg) || (xchg && xchg->world != world) || (!gathered_partials && !xchg) || !token) return DUODEC_EINVAL;
-  const int blocks = xchg ? 1 : (B + 127) / 128;  // the fused exchange closes the step in one block
-  shard_finish_kernel<<<blocks, xchg ? 256 : 128, 0, static_cast<cudaStream_t>(stream)>>>(
+  const bool one = xchg && xchg->mode != 2;  // the flag protocol closes the step in one block
+  const int blocks = one ? 1 : (B + 127) / 128;
+  shard_finish_kernel<<<blocks, one ? 256 : 128, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const ShardPartial*>(gathered_partials), world, B, nslice, reinterpret_cast<long long*>(token),
       xchg_of(xchg));
   return int(cudaGetLastError());

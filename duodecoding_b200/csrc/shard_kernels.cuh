@@ -77,8 +77,21 @@ struct ShardXchg {
   void* const* peers;  // device array of `world` base pointers (own base at [rank]); nullptr: no fused exchange
   int rank, world;
   long long off_stats, off_partial;  // byte offsets of gstats [world][rows] float4 / gpartial [world][B * nslice]
-  int mode;  // 0: every block stores its result into every peer; 1: the last block copies the rank's slab to the peers
+  int mode;  // 0: every block stores its result into every peer; 1: the last block copies the rank's slab to the peers;
+             // 2 ("pull"): results stay in the rank's OWN buffer, the caller puts a barrier over all ranks between the
+             // producing and the consuming kernel (torch symmetric memory: hdl.barrier()), and the consumers read every
+             // peer's slab in place over NVLink - no copy, no flag protocol in the kernels
 };
+constexpr int kXPull = 2;
+// slab of rank g inside the gather area at byte offset `off`: in pull mode it lives in rank g's own buffer
+__device__ __forceinline__ const unsigned char* xchg_area(const ShardXchg& X, int g, long long off) {
+  return static_cast<const unsigned char*>(X.peers[X.mode == kXPull ? g : X.rank]) + off;
+}
+__device__ __forceinline__ float4 ld_peer_f4(const float4* p) {  // peer memory: never from a stale L1 line
+  float4 v;
+  asm volatile("ld.volatile.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+}
 __device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
   unsigned v;
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -242,7 +255,7 @@ __global__ void __launch_bounds__(kThreads) shard_stats_kernel(const __grid_cons
     else  // the rank's own slab of the gather area, slot [rank][job]
       reinterpret_cast<float4*>(static_cast<unsigned char*>(X.peers[X.rank]) + X.off_stats)[(long long)X.rank * gridDim.x + job] = v;
   }
-  if (X.peers != nullptr)
+  if (X.peers != nullptr && X.mode != kXPull)
     xchg_publish(X, kXFlags1, kXCnt1, gridDim.x, X.off_stats, (long long)gridDim.x * 16, (long long)job * 16, 16);
 }
 
@@ -269,10 +282,23 @@ static_assert(sizeof(ShardPlan) == 48, "ShardPlan is exchanged with the host as 
 
 // merged (M, Z, token logit) of one row from the G gathered partials
 __device__ __forceinline__ void shard_merge(const float4* gathered, int G, int rows, int job, float& M, float& Z,
-                                            float& tokx, bool& has) {
-  M = -INFINITY;
+                                            float& tokx, bool& has, const ShardXchg* pull = nullptr) {
+  constexpr int kMaxG = 32;
+  M = -INFINITY, Z = 0.0f, tokx = 0.0f, has = false;
+  if (pull != nullptr && G <= kMaxG) {
+    // every rank's record sits in that rank's own buffer: all G loads are issued before the first is used
+    float4 q[kMaxG];
+#pragma unroll 8
+    for (int g = 0; g < G; ++g)
+      q[g] = ld_peer_f4(reinterpret_cast<const float4*>(xchg_area(*pull, g, pull->off_stats)) + (long long)g * rows + job);
+    for (int g = 0; g < G; ++g) M = fmaxf(M, q[g].x);
+    for (int g = 0; g < G; ++g) {
+      if (q[g].x > -INFINITY) Z += q[g].y * expf(q[g].x - M);
+      if (q[g].w != 0.0f) tokx = q[g].z, has = true;
+    }
+    return;
+  }
   for (int g = 0; g < G; ++g) M = fmaxf(M, gathered[(long long)g * rows + job].x);
-  Z = 0.0f, tokx = 0.0f, has = false;
   for (int g = 0; g < G; ++g) {  // rank order: the same sum on every rank
     const float4 q = gathered[(long long)g * rows + job];
     if (q.x > -INFINITY) Z += q.y * expf(q.x - M);
@@ -285,7 +311,8 @@ __global__ void shard_accept_kernel(const float4* gathered, int G, int B, int ga
                                     unsigned char* accept_mask, float* sel_p, float* sel_q, long long* accepted_len,
                                     unsigned char* all_accepted, ShardPlan* plan, const ShardXchg X,
                                     const long long* tokens, long long tok_sb, const ShardCut* cuts) {
-  if (X.peers != nullptr) {
+  const ShardXchg* pull = (X.peers != nullptr && X.mode == kXPull) ? &X : nullptr;
+  if (X.peers != nullptr && pull == nullptr) {
     xchg_wait(X, kXFlags1);
     gathered = reinterpret_cast<const float4*>(static_cast<const unsigned char*>(X.peers[X.rank]) + X.off_stats);
   }
@@ -295,8 +322,8 @@ __global__ void shard_accept_kernel(const float4* gathered, int G, int B, int ga
   if (lane < gamma) {
     float Mq, Zq, xq, Mp, Zp, xp;
     bool hq, hp;
-    shard_merge(gathered, G, rows, base + 2 * lane, Mq, Zq, xq, hq);
-    shard_merge(gathered, G, rows, base + 2 * lane + 1, Mp, Zp, xp, hp);
+    shard_merge(gathered, G, rows, base + 2 * lane, Mq, Zq, xq, hq, pull);
+    shard_merge(gathered, G, rows, base + 2 * lane + 1, Mp, Zp, xp, hp, pull);
     if (cuts != nullptr) {  // nucleus rows: the kept mass normalises, a filtered-out token has probability 0
       const ShardCut cq = cuts[base + 2 * lane], cp = cuts[base + 2 * lane + 1];
       const long long tk = tokens[(long long)b * tok_sb + lane];
@@ -320,9 +347,9 @@ __global__ void shard_accept_kernel(const float4* gathered, int G, int B, int ga
     bool h;
     pl.n = n, pl.bonus = (n == gamma), pl.pad0 = pl.pad1 = 0;
     const int prow = base + (pl.bonus ? 2 * gamma : 2 * n + 1), qrow = base + 2 * n;
-    shard_merge(gathered, G, rows, prow, pl.Mp, pl.Zp, x, h);
+    shard_merge(gathered, G, rows, prow, pl.Mp, pl.Zp, x, h, pull);
     pl.Mq = 0.0f, pl.Zq = 1.0f;
-    if (!pl.bonus) shard_merge(gathered, G, rows, qrow, pl.Mq, pl.Zq, x, h);
+    if (!pl.bonus) shard_merge(gathered, G, rows, qrow, pl.Mq, pl.Zq, x, h, pull);
     pl.xsp = pl.xsq = -INFINITY, pl.isp = pl.isq = 0x7fffffff;
     if (cuts != nullptr) {
       const ShardCut cp = cuts[prow];
@@ -439,14 +466,15 @@ __global__ void __launch_bounds__(kThreads) shard_sample_kernel(const __grid_con
       reinterpret_cast<ShardPartial*>(static_cast<unsigned char*>(X.peers[X.rank]) + X.off_partial)
           [((long long)X.rank * gridDim.y + b) * nslice + blockIdx.x] = p;
   }
-  if (X.peers != nullptr)
+  if (X.peers != nullptr && X.mode != kXPull)
     xchg_publish(X, kXFlags2, kXCnt2, gridDim.x * gridDim.y, X.off_partial, (long long)gridDim.x * gridDim.y * 24,
                  ((long long)b * nslice + blockIdx.x) * 24, 24);
 }
 
 __global__ void shard_finish_kernel(const ShardPartial* gathered, int G, int B, int nslice, long long* token,
                                     const ShardXchg X) {
-  if (X.peers != nullptr) {  // (one block in this mode: it closes the step)
+  const bool pull = X.peers != nullptr && X.mode == kXPull;
+  if (X.peers != nullptr && !pull) {  // (one block in this mode: it closes the step)
     xchg_wait(X, kXFlags2);
     gathered = reinterpret_cast<const ShardPartial*>(static_cast<const unsigned char*>(X.peers[X.rank]) + X.off_partial);
   }
@@ -454,7 +482,16 @@ __global__ void shard_finish_kernel(const ShardPartial* gathered, int G, int B, 
     float mass = 0.0f;
     unsigned long long key = 0ull, bd = 0ull;
     for (int g = 0; g < G * nslice; ++g) {  // rank-major, then slice: the same order on every rank
-      const ShardPartial p = gathered[((long long)(g / nslice) * B + b) * nslice + (g % nslice)];
+      const long long at = ((long long)(g / nslice) * B + b) * nslice + (g % nslice);
+      ShardPartial p;
+      if (pull) {  // rank g / nslice keeps its partials in its own buffer
+        const volatile unsigned long long* src = reinterpret_cast<const volatile unsigned long long*>(
+            reinterpret_cast<const ShardPartial*>(xchg_area(X, g / nslice, X.off_partial)) + at);
+        const unsigned long long w0 = src[0];
+        p.mass = __uint_as_float(unsigned(w0)), p.pad = 0u, p.key = src[1], p.bd = src[2];
+      } else {
+        p = gathered[at];
+      }
       mass += p.mass;
       key = p.key > key ? p.key : key;
       bd = p.bd > bd ? p.bd : bd;
@@ -462,7 +499,7 @@ __global__ void shard_finish_kernel(const ShardPartial* gathered, int G, int B, 
     const unsigned long long win = (mass > 0.0f && key != 0ull) ? key : bd;
     token[b] = win == 0ull ? 0 : (long long)(0xffffffffu - unsigned(win & 0xffffffffull));
   }
-  if (X.peers != nullptr) {
+  if (X.peers != nullptr && !pull) {
     __syncthreads();
     if (threadIdx.x == 0) {
       unsigned* step = reinterpret_cast<unsigned*>(static_cast<unsigned char*>(X.peers[X.rank]) + kXStep);

@@ -200,11 +200,16 @@ class ShardedVerifier:
         # profiles/r02_c5_exchange_ab.txt), so it stays opt-in.
         self.collectives = 0
         self.use_graphs = True
-        self.fused = fused_exchange and self.world > 1 and isinstance(backend, _CudaBackend)
+        # `fused_exchange="pull"`: results stay in each rank's symmetric buffer, one symmetric-memory barrier per
+        # exchange, consumers read the peers' slabs in place over NVLink (no copy, no NCCL call).
+        self.fused = bool(fused_exchange) and self.world > 1 and isinstance(backend, _CudaBackend)
+        self.pull = self.fused and fused_exchange == "pull"
         self._bufs: dict = {}
         self._graphs: dict = {}
         self._symm: dict = {}
         self.xchg_mode = 0  # 0: every block pushes its result to the peers; 1: the last block copies the slab
+        if self.pull:
+            self.xchg_mode = 2
 
     def slice_of(self, full: torch.Tensor) -> torch.Tensor:
         """This rank's columns of a [..., V] tensor (what a sharded LM head would have produced)."""
@@ -226,6 +231,8 @@ class ShardedVerifier:
     def exchange_kind(self) -> str:
         if self.world == 1:
             return "none (one rank)"
+        if self.fused and self.pull:
+            return "pull: symmetric-memory barrier, consumers read the peers' buffers in place (no copy, no NCCL)"
         return ("fused: peer stores + release/acquire flags over symmetric memory, inside the kernels" if self.fused
                 else "nccl all_gather_into_tensor (captured in the step's CUDA graph)")
 
@@ -332,11 +339,15 @@ class ShardedVerifier:
             return out
         if self.fused and self.world > 1:
             import ctypes
-            _, _, x, nslice = self._symmetric(B, gamma, target.shape[-1], target.device)
+            _, hdl, x, nslice = self._symmetric(B, gamma, target.shape[-1], target.device)
             xp = ctypes.byref(x)
             be.row_stats(draft, target, tokens, self.v_begin, temperature, d_temp, xchg=xp)
+            if self.pull:
+                hdl.barrier(channel=0)  # every rank's statistics are in its buffer (and visible) past this point
             out, plan = be.accept(None, B, gamma, r, out=buf["out"], plan=buf["plan"], xchg=xp, world=self.world)
             be.sample_partial(draft, target, plan, noise, self.v_begin, temperature, d_temp, gamma, xchg=xp)
+            if self.pull:
+                hdl.barrier(channel=1)
             out = dict(out)
             out["token"] = be.finish(None, B, token=buf["token"], xchg=xp, world=self.world, nslice=nslice)
             return out

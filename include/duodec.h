@@ -200,7 +200,10 @@ typedef struct {
   void* const* peers;
   int rank, world;
   int64_t off_stats, off_partial;
-  int mode; /* 0: every block stores its result into every peer; 1: the last block copies the rank's slab */
+  int mode; /* 0: every block stores its result into every peer; 1: the last block copies the rank's slab;
+             * 2 ("pull"): results stay in the rank's own buffer, the CALLER separates the producing and the consuming
+             * call by a barrier over all ranks (e.g. torch symmetric memory's hdl.barrier() on the same stream) and the
+             * consumers read every peer's slab in place - no flags, the header is unused */
 } duodec_shard_xchg;
 #define DUODEC_SHARD_XCHG_HEADER 1024
 int duodec_shard_stats(const void* draft, const void* target, int dtype, int64_t d_sb, int64_t d_ss, int64_t t_sb,
