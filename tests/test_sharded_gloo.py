@@ -71,3 +71,50 @@ def test_sharded_verify_world2_gloo():
     ret = mp.Manager().dict()
     mp.spawn(_worker, args=(2, port, ret), nprocs=2, join=True)
     assert ret.get(0) is True and ret.get(1) is True
+
+
+def _emulated_top_p(world, dl, tl, toks, r, noise, T, top_p, d_top_p):
+    """ShardedVerifier's nucleus flow with the oracle backend, the all-gathers emulated by stacking."""
+    from oracle.sharded_port import OracleShardBackend
+    be = OracleShardBackend()
+    B, gamma = toks.shape
+    V = tl.shape[-1]
+    parts = [(dl[..., a:b], tl[..., a:b], noise[..., a:b], a) for a, b in (shard_bounds(V, g, world) for g in range(world))]
+    gstats = torch.stack([be.row_stats(d, t, toks, a, T, T) for d, t, _, a in parts])
+    levels = be.nucleus_levels(parts[0][1], T, T)
+    sels, quotas = [None] * world, [None] * world
+    for level in range(levels):
+        hists = []
+        for g, (d, t, _, a) in enumerate(parts):
+            sels[g], h = be.nucleus_level(d, t, gamma, a, T, T, top_p, d_top_p, gstats, sels[g], level)
+            hists.append(h)
+        gh = torch.stack(hists)
+        for g in range(world):
+            sels[g], quotas[g] = be.nucleus_reduce(gh, g, B, gamma, top_p, d_top_p, sels[g], level, levels, quotas[g])
+    gcand = torch.stack([be.nucleus_tie(d, t, gamma, a, T, T, sels[g], quotas[g], levels)
+                         for g, (d, t, _, a) in enumerate(parts)])
+    cuts = be.nucleus_close(sels[0], gstats, gcand, B, gamma, levels)
+    out, plan = be.accept(gstats, B, gamma, r, tokens=toks, cuts=cuts)
+    partials = torch.stack([be.sample_partial(d, t, plan, nz, a, T, T, gamma, filtered=True) for d, t, nz, a in parts])
+    out["token"] = be.finish(partials, B)
+    return out, cuts
+
+
+def test_sharded_top_p_protocol_on_cpu_with_ties():
+    """The radix-select protocol (levels, reduction, index cut across ranks, close) in the oracle backend on rows
+    full of equal values (bf16 grid), for 1, 2, 3 and 5 emulated ranks: the same filter for every partition, and the
+    unsharded oracle's decisions."""
+    for seed, T, top_p, d_top_p in [(11, 1.0, 0.9, 0.9), (12, 0.7, 0.6, 0.0), (13, 1.0, 0.999, 0.3)]:
+        dl, tl, toks, r, noise = _case(seed, 4, 3, 1500, 1.0)
+        dl, tl = (dl * 0.5).bfloat16().float(), (tl * 0.5).bfloat16().float()
+        want = oracle.fused_verify(dl, tl, toks, r, noise, T, 0, top_p, T, 0, d_top_p)
+        ref = None
+        for world in (1, 2, 3, 5):
+            got, cuts = _emulated_top_p(world, dl, tl, toks, r, noise, T, top_p, d_top_p)
+            assert torch.equal(got["accepted_len"], want["accepted_len"]), (seed, world)
+            assert torch.equal(got["token"], want["token"]) and torch.equal(got["accept_mask"], want["accept_mask"])
+            assert torch.allclose(got["selected_target_p"], want["selected_target_p"], rtol=5e-4, atol=1e-9)
+            c = cuts.clone()
+            c[c[:, 3] == 2, 2] = 0  # rows without a filter: the float sum of partial sums depends on the partition
+            ref = c if ref is None else ref
+            assert torch.equal(c, ref), (seed, world)
